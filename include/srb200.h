@@ -1,0 +1,161 @@
+/*
+ * srb200.h -- C ABI of libsrb200.so, the B200 (sm_100a) rasterization backend
+ * that sits under OCSYT/SoftwareRenderer's C# Renderer/Rasterizer/MainWindow/
+ * Texture API.  POD types only: plain pointers, sizes and int status codes.
+ *
+ * The reference has no FFI of its own; each entry point below names the C#
+ * member (file:line under /root/reference) whose BODY it replaces.  The C#
+ * side binds these with [DllImport("srb200")] (csharp/Native.cs,
+ * INTEGRATION.md).  There is no CPU fallback anywhere behind this header:
+ * every call that needs the GPU fails with SRB_ERR_CUDA when there is none.
+ *
+ * Conventions:
+ *   - Matrix4x4 = 16 floats row-major M11..M44, row-vector convention v' = v*M.
+ *   - VertexInput = 12 floats: pos3, uv2, normal3, color4 (Shaders.cs:10-24).
+ *   - colour buffer = float4 per pixel, depth buffer = float per pixel, both
+ *     row-major, top-left origin, index = y*W + x (MainWindow.cs:30-31, 379).
+ *   - stored depth is the reference's negated screen-space depth; the clear
+ *     value is -FLT_MAX (float.MinValue, MainWindow.cs:429-436).
+ *   - status: 0 = ok, <0 = error; srb_last_error() gives the message.
+ *   - srb_draw* may be called from several host threads at once
+ *     (Renderer.cs:444, 479 call RenderMesh from Parallel.ForEach); everything
+ *     else is called from one thread.  Work is deferred to srb_end_frame.
+ */
+#ifndef SRB200_H
+#define SRB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRB_OK             0
+#define SRB_ERR_ARG       -1   /* ArgumentException analogue (Rasterizer.cs:71-74) */
+#define SRB_ERR_CUDA      -2   /* CUDA runtime error or no device */
+#define SRB_ERR_HANDLE    -3   /* unknown mesh/texture handle */
+#define SRB_ERR_STATE     -4   /* call outside begin/end frame etc. */
+#define SRB_ERR_UNSUPPORTED -5 /* non-stock shader delegates: no CPU fallback by design */
+
+/* Rasterizer.CullMode / DepthTest / BlendMode (Rasterizer.cs:25-50), same values. */
+enum { SRB_CULL_NONE = 0, SRB_CULL_BACK = 1, SRB_CULL_FRONT = 2 };
+enum { SRB_DEPTH_DISABLED = 0, SRB_DEPTH_LESS = 1, SRB_DEPTH_LESS_EQUAL = 2, SRB_DEPTH_GREATER = 3,
+       SRB_DEPTH_GREATER_EQUAL = 4, SRB_DEPTH_EQUAL = 5, SRB_DEPTH_NOT_EQUAL = 6, SRB_DEPTH_ALWAYS = 7 };
+enum { SRB_BLEND_NONE = 0, SRB_BLEND_ALPHA = 1, SRB_BLEND_ADDITIVE = 2, SRB_BLEND_MULTIPLY = 3 };
+
+/* srb_begin_frame flags */
+#define SRB_CLEAR_COLOR 1u     /* MainWindow.ClearColorBuffer (MainWindow.cs:400-407) */
+#define SRB_CLEAR_DEPTH 2u     /* MainWindow.ClearDepthBuffer (MainWindow.cs:429-436) */
+
+/* srb_draw flags */
+#define SRB_DRAW_FRUSTUM_CULL 1u  /* run FrustumCuller.IsSphereInFrustum on the device for this draw */
+
+/* pipeline selection (srb_set_pipeline) */
+enum { SRB_PIPELINE_AUTO = 0,      /* visibility path when provably order-independent, else ordered */
+       SRB_PIPELINE_ORDERED = 1,   /* always the submission-ordered path (any state) */
+       SRB_PIPELINE_VISIBILITY = 2 /* force; SRB_ERR_STATE at end_frame if the frame is not eligible */ };
+
+typedef struct SrbContext SrbContext;
+typedef int32_t SrbMesh;      /* >0 valid */
+typedef int32_t SrbTexture;   /* 0 = no texture (sample = 1,1,1,1; Renderer.cs:852), >0 valid */
+
+/* Captured state of the stock shader pair (Renderer.cs:39-44, 848-860) plus
+ * Rasterizer.NearClip (Rasterizer.cs:20) and the numerics switch. */
+typedef struct SrbUniforms {
+    float light_dir[4];       /* xyz = Renderer.LightDirection (normalised by the caller) */
+    float light_color[4];     /* Renderer.LightColor */
+    float fog_color[4];       /* Renderer.FogColor */
+    float fog_start;          /* Renderer.FogStart */
+    float fog_end;            /* Renderer.FogEnd */
+    float near_clip;          /* Rasterizer.NearClip */
+    int32_t numerics_fma;     /* 1 = System.Numerics Transform/Lerp fused (net9.0 on FMA hardware) */
+    int32_t tex_filter;       /* 0 nearest+repeat (Texture.cs:42-63); 1 bilinear+repeat (extension) */
+    int32_t n_extra_lights;   /* extension: 0..4 extra directional lights */
+    int32_t _pad[2];
+    float extra_dir[4][4];
+    float extra_color[4][4];
+} SrbUniforms;
+
+/* One Rasterizer.RenderMesh call (Rasterizer.cs:163-174) for batched submission. */
+typedef struct SrbDrawCmd {
+    SrbMesh    mesh;
+    SrbTexture texture;
+    float model[16];
+    float view[16];
+    float proj[16];
+    float sphere[4];          /* Mesh.SphereBounds cx,cy,cz,r; read when SRB_DRAW_FRUSTUM_CULL */
+    int32_t cull;
+    int32_t depth_test;
+    int32_t blend;
+    uint32_t flags;
+    int32_t submission_index; /* deterministic order key despite racing callers; <0 = call order */
+    int32_t _pad[3];
+} SrbDrawCmd;
+
+typedef struct SrbStats {
+    int64_t draws_submitted;
+    int64_t draws_visible;        /* after the device frustum test */
+    int64_t triangles_submitted;
+    int64_t triangles_setup;      /* survived behind/NaN/area/cull/bbox(/band) */
+    int64_t tile_pairs;           /* (triangle, tile) bin entries */
+    int64_t clipped_triangles;    /* went through the near-plane clipper */
+    int32_t pipeline_used;        /* SRB_PIPELINE_ORDERED or SRB_PIPELINE_VISIBILITY */
+    int32_t kernel_launches;      /* CUDA kernels launched by the last end_frame */
+    float   gpu_ms;               /* device time of the last end_frame (CUDA events) */
+    float   _pad;
+} SrbStats;
+
+/* ---- context / framebuffer: MainWindow buffers (MainWindow.cs:23-31, 298-361) ---- */
+int srb_create(int device, int width, int height, SrbContext** out_ctx);
+int srb_destroy(SrbContext* ctx);
+int srb_resize(SrbContext* ctx, int width, int height);          /* MainWindow.HandleResize :298-361 */
+int srb_get_size(SrbContext* ctx, int* width, int* height);      /* RenderWidth/RenderHeight :25-26 */
+const char* srb_last_error(SrbContext* ctx);                     /* ctx may be NULL for create errors */
+/* Multi-GPU: restrict this context to tile rows [row0,row1) (16-px rows). */
+int srb_set_band(SrbContext* ctx, int tile_row0, int tile_row1);
+int srb_set_pipeline(SrbContext* ctx, int pipeline);
+
+/* ---- resources: Texture (Texture.cs:31-63), Mesh arrays (ModelLoader.cs:42-57) ---- */
+int srb_texture_create(SrbContext* ctx, const uint8_t* rgba8, int width, int height, SrbTexture* out);
+int srb_texture_destroy(SrbContext* ctx, SrbTexture tex);
+int srb_mesh_create(SrbContext* ctx, const float* vertices, int n_vertices,
+                    const uint16_t* indices, int n_indices, SrbMesh* out);
+int srb_mesh_destroy(SrbContext* ctx, SrbMesh mesh);
+
+/* ---- frame: Renderer.RenderScene call pattern (Renderer.cs:404-419) ---- */
+int srb_set_uniforms(SrbContext* ctx, const SrbUniforms* u);
+int srb_begin_frame(SrbContext* ctx, const float clear_rgba[4], uint32_t clear_flags);
+/* Rasterizer.RenderMesh (Rasterizer.cs:163-230), stock shader pair only. */
+int srb_draw(SrbContext* ctx, SrbMesh mesh, const float model[16], const float view[16],
+             const float proj[16], SrbTexture tex, int cull, int depth_test, int blend,
+             int submission_index);
+int srb_submit_draws(SrbContext* ctx, const SrbDrawCmd* cmds, int n);
+/* MainWindow.RenderFrame (MainWindow.cs:209-212): runs the whole pipeline, asynchronously. */
+int srb_end_frame(SrbContext* ctx);
+/* Re-run the pipeline on the draw list already resident on the device (benchmark loop). */
+int srb_replay_frame(SrbContext* ctx);
+int srb_sync(SrbContext* ctx);
+
+/* ---- readback: MainWindow.ColorBuffer/DepthBuffer + accessors (MainWindow.cs:378-436) ---- */
+int srb_read_color(SrbContext* ctx, float* rgba_out);            /* W*H*4 floats */
+int srb_read_depth(SrbContext* ctx, float* depth_out);           /* W*H floats */
+int srb_read_color_rgba8(SrbContext* ctx, uint8_t* rgba8_out);   /* present-format step, MainWindow.cs:234-250 */
+int srb_read_color_rows(SrbContext* ctx, float* rgba_out, int y0, int y1);
+int srb_get_pixel(SrbContext* ctx, int x, int y, float rgba_out[4]);   /* :390-398 */
+int srb_set_pixel(SrbContext* ctx, int x, int y, const float rgba[4]); /* :382-388 */
+int srb_get_depth(SrbContext* ctx, int x, int y, float* depth_out);    /* :419-427 */
+int srb_set_depth(SrbContext* ctx, int x, int y, float depth);         /* :410-416 */
+void* srb_device_color_ptr(SrbContext* ctx);   /* float4[W*H] on the device (headless present) */
+void* srb_device_depth_ptr(SrbContext* ctx);   /* float[W*H] on the device */
+void* srb_stream(SrbContext* ctx);             /* cudaStream_t the pipeline runs on */
+
+/* ---- FrustumCuller.IsSphereInFrustum (FrustumCuller.cs:201-218), batched on the device ---- */
+int srb_frustum_test(SrbContext* ctx, const float* spheres /* n*4 */, const float* models /* n*16 */,
+                     const float view[16], const float proj[16], int n, int32_t* out_visible);
+
+int srb_get_stats(SrbContext* ctx, SrbStats* out);
+int srb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRB200_H */

@@ -1,0 +1,628 @@
+// oracle.cpp -- CPU oracle for the SoftwareRenderer rasterization path.
+//
+// TEST INFRASTRUCTURE ONLY (see oracle.h).  PARITY UNPINNED by upstream: the
+// reference has no tests or golden data and its C# cannot run in this image.
+//
+// Every function cites the reference lines whose semantics it restates.
+// Build: g++ -O2 -ffp-contract=off -fno-fast-math -mfma (one IEEE rounding per
+// scalar op, like RyuJIT scalar code; fused only where fmaf() is written).
+#include "oracle.h"
+
+#include <atomic>
+#include <climits>
+#include <cmath>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+namespace {
+
+constexpr int   kTile = 16;        // Rasterizer.cs:53
+constexpr float kEps  = 1e-6f;     // Rasterizer.cs:52
+
+// ---- System.Numerics restatement (net9.0 BCL; see DESIGN.md "numerics") ----
+struct V2 { float x, y; };
+struct V3 { float x, y, z; };
+struct V4 { float x, y, z, w; };
+
+// .NET 9 float->int: saturating, NaN -> 0.
+inline int sat_int(float f) {
+    if (f != f) return 0;
+    if (f >= 2147483648.0f) return INT_MAX;
+    if (f <= -2147483648.0f) return INT_MIN;
+    return (int)f;
+}
+
+// MathF.Max / MathF.Min: NaN-propagating.
+inline float net_max(float a, float b) { if (a != a) return a; if (b != b) return b; return a > b ? a : b; }
+inline float net_min(float a, float b) { if (a != a) return a; if (b != b) return b; return a < b ? a : b; }
+// Math.Clamp(float): NaN passes through.
+inline float net_clamp(float v, float lo, float hi) { if (v < lo) return lo; if (v > hi) return hi; return v; }
+
+// Vector4.Transform(v, M): row-vector times matrix, accumulated row by row.
+// fma=1: MultiplyAddEstimate chain (net9 on FMA hardware); fma=0: mul then add.
+inline V4 transform4(V4 v, const float* m, bool fma) {
+    float r[4];
+    for (int c = 0; c < 4; ++c) {
+        float acc = m[0 + c] * v.x;
+        if (fma) {
+            acc = fmaf(m[4 + c], v.y, acc);
+            acc = fmaf(m[8 + c], v.z, acc);
+            acc = fmaf(m[12 + c], v.w, acc);
+        } else {
+            acc = acc + m[4 + c] * v.y;
+            acc = acc + m[8 + c] * v.z;
+            acc = acc + m[12 + c] * v.w;
+        }
+        r[c] = acc;
+    }
+    return {r[0], r[1], r[2], r[3]};
+}
+
+// Vector3.TransformNormal(n, M): upper 3x3 only.
+inline V3 transform_normal(V3 n, const float* m, bool fma) {
+    float r[3];
+    for (int c = 0; c < 3; ++c) {
+        float acc = m[0 + c] * n.x;
+        if (fma) {
+            acc = fmaf(m[4 + c], n.y, acc);
+            acc = fmaf(m[8 + c], n.z, acc);
+        } else {
+            acc = acc + m[4 + c] * n.y;
+            acc = acc + m[8 + c] * n.z;
+        }
+        r[c] = acc;
+    }
+    return {r[0], r[1], r[2]};
+}
+
+inline float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+
+// Vector3.Normalize: value / value.Length()
+inline V3 normalize3(V3 v) {
+    float len = sqrtf(dot3(v, v));
+    return {v.x / len, v.y / len, v.z / len};
+}
+
+// Vector{2,3,4}.Lerp component: a*(1-t) + b*t, fused as fma(a, 1-t, b*t) under the switch.
+inline float lerp1(float a, float b, float t, bool fma) {
+    float omt = 1.0f - t;
+    float bt = b * t;
+    return fma ? fmaf(a, omt, bt) : a * omt + bt;
+}
+
+// ---- Shaders.VertexOutput restricted to what the stock shaders touch ----
+struct VOut {
+    V4 clip;      // ClipPosition
+    V4 color;     // Color
+    V2 uv;        // TexCoord
+    V3 normal;    // Normal (object space, passed through)
+    V2 screen;    // ScreenCoords
+    V3 wn;        // Data["WorldNormal"]
+};
+
+// Renderer.VertexShader (Renderer.cs:830-846).
+inline VOut vertex_shader(const float* vin, const float* M, const float* V, const float* P, bool fma) {
+    VOut o;
+    V4 world = transform4({vin[0], vin[1], vin[2], 1.0f}, M, fma);
+    V4 view  = transform4(world, V, fma);
+    o.clip   = transform4(view, P, fma);
+    V3 n     = {vin[5], vin[6], vin[7]};
+    o.wn     = normalize3(transform_normal(n, M, fma));
+    o.uv     = {vin[3], vin[4]};
+    o.color  = {vin[8], vin[9], vin[10], vin[11]};
+    o.normal = n;
+    o.screen = {0.0f, 0.0f};
+    return o;
+}
+
+// Shaders.Lerp (Shaders.cs:49-95) with interpolate=true; WorldNormal is
+// Vector3.Lerp'ed and NOT renormalised; ScreenCoords stays default.
+inline VOut vout_lerp(const VOut& a, const VOut& b, float t, bool fma) {
+    VOut o;
+    o.clip   = {lerp1(a.clip.x, b.clip.x, t, fma), lerp1(a.clip.y, b.clip.y, t, fma),
+                lerp1(a.clip.z, b.clip.z, t, fma), lerp1(a.clip.w, b.clip.w, t, fma)};
+    o.uv     = {lerp1(a.uv.x, b.uv.x, t, fma), lerp1(a.uv.y, b.uv.y, t, fma)};
+    o.color  = {lerp1(a.color.x, b.color.x, t, fma), lerp1(a.color.y, b.color.y, t, fma),
+                lerp1(a.color.z, b.color.z, t, fma), lerp1(a.color.w, b.color.w, t, fma)};
+    o.normal = {lerp1(a.normal.x, b.normal.x, t, fma), lerp1(a.normal.y, b.normal.y, t, fma),
+                lerp1(a.normal.z, b.normal.z, t, fma)};
+    o.wn     = {lerp1(a.wn.x, b.wn.x, t, fma), lerp1(a.wn.y, b.wn.y, t, fma),
+                lerp1(a.wn.z, b.wn.z, t, fma)};
+    o.screen = {0.0f, 0.0f};
+    return o;
+}
+
+// ClipTriangleAgainstNearPlane (Rasterizer.cs:95-160): Sutherland-Hodgman
+// against z >= NearClip*w, then a fan.  Returns the number of triangles.
+inline int clip_near(const VOut in[3], float nearClip, bool fma, VOut out[2][3]) {
+    VOut poly[6];
+    int n = 0;
+    for (int i = 0; i < 3; ++i) {
+        const VOut& cur = in[i];
+        const VOut& nxt = in[(i + 1) % 3];
+        bool curIn = cur.clip.z >= nearClip * cur.clip.w;
+        bool nxtIn = nxt.clip.z >= nearClip * nxt.clip.w;
+        if (curIn) poly[n++] = cur;
+        if (curIn != nxtIn) {
+            float z0 = cur.clip.z, w0 = cur.clip.w, z1 = nxt.clip.z, w1 = nxt.clip.w;
+            float denom = (z1 - z0) - nearClip * (w1 - w0);
+            float t;
+            if (fabsf(denom) < kEps) {
+                t = 0.5f;
+            } else {
+                t = (z0 - nearClip * w0) / (nearClip * (w1 - w0) - (z1 - z0));
+                t = net_clamp(t, 0.0f, 1.0f);
+            }
+            poly[n++] = vout_lerp(cur, nxt, t, fma);
+        }
+    }
+    if (n < 3) return 0;
+    int nt = 0;
+    for (int i = 1; i < n - 1 && nt < 2; ++i, ++nt) {
+        out[nt][0] = poly[0];
+        out[nt][1] = poly[i];
+        out[nt][2] = poly[i + 1];
+    }
+    return nt;
+}
+
+// Texture.Sample (Texture.cs:42-63): nearest, repeat.
+inline V4 tex_nearest(const uint8_t* px, int tw, int th, float uu, float vv) {
+    float u = uu - (float)sat_int(uu);
+    float v = vv - (float)sat_int(vv);
+    u += (u < 0) ? 1.0f : 0.0f;
+    v += (v < 0) ? 1.0f : 0.0f;
+    int x = sat_int(u * (float)tw) % tw;
+    int y = sat_int(v * (float)th) % th;
+    if (x < 0) x += tw;
+    if (y < 0) y += th;
+    const uint8_t* p = px + 4 * ((size_t)y * tw + x);
+    const float inv255 = 1.0f / 255.0f;
+    return {p[0] * inv255, p[1] * inv255, p[2] * inv255, p[3] * inv255};
+}
+
+// EXTENSION (not in the reference; BASELINE.json config 5): bilinear, repeat
+// wrap, texel centres at +0.5, fp32 lerp of the four x(1/255) texels.
+inline V4 tex_bilinear(const uint8_t* px, int tw, int th, float uu, float vv) {
+    float u = uu - floorf(uu);
+    float v = vv - floorf(vv);
+    float fx = u * (float)tw - 0.5f;
+    float fy = v * (float)th - 0.5f;
+    float x0f = floorf(fx), y0f = floorf(fy);
+    float ax = fx - x0f, ay = fy - y0f;
+    int x0 = sat_int(x0f) % tw; if (x0 < 0) x0 += tw;
+    int y0 = sat_int(y0f) % th; if (y0 < 0) y0 += th;
+    int x1 = (x0 + 1) % tw, y1 = (y0 + 1) % th;
+    const float inv255 = 1.0f / 255.0f;
+    float out[4];
+    for (int c = 0; c < 4; ++c) {
+        float t00 = px[4 * ((size_t)y0 * tw + x0) + c] * inv255;
+        float t10 = px[4 * ((size_t)y0 * tw + x1) + c] * inv255;
+        float t01 = px[4 * ((size_t)y1 * tw + x0) + c] * inv255;
+        float t11 = px[4 * ((size_t)y1 * tw + x1) + c] * inv255;
+        float top = t00 + (t10 - t00) * ax;
+        float bot = t01 + (t11 - t01) * ax;
+        out[c] = top + (bot - top) * ay;
+    }
+    return {out[0], out[1], out[2], out[3]};
+}
+
+// Renderer.FragmentShader (Renderer.cs:848-860).
+inline V4 fragment_shader(V3 wn, V4 color, V2 uv, float clipZ, const OrcDraw& d, const OrcUniforms& U) {
+    bool fma = U.numerics_fma != 0;
+    V3 negL = {-U.light_dir[0], -U.light_dir[1], -U.light_dir[2]};
+    float diffuse = net_max(0.25f, dot3(wn, negL));
+    V4 tex = {1.0f, 1.0f, 1.0f, 1.0f};
+    if (d.tex_rgba8)
+        tex = U.tex_filter == 1 ? tex_bilinear(d.tex_rgba8, d.tex_w, d.tex_h, uv.x, uv.y)
+                                : tex_nearest(d.tex_rgba8, d.tex_w, d.tex_h, uv.x, uv.y);
+    V4 base = {color.x * tex.x, color.y * tex.y, color.z * tex.z, color.w * tex.w};
+    float fog = net_clamp((U.fog_end - clipZ) / (U.fog_end - U.fog_start), 0.0f, 1.0f);
+    fog = fog * fog * (3.0f - 2.0f * fog);
+    float k = 0.1f + 0.9f * diffuse;
+    V4 lit = {base.x * k * U.light_color[0], base.y * k * U.light_color[1],
+              base.z * k * U.light_color[2], base.w * k * U.light_color[3]};
+    // EXTENSION: extra directional lights add Color*max(0, N.-Dir)*base (no ambient floor).
+    for (int i = 0; i < U.n_extra_lights && i < 4; ++i) {
+        V3 nd = {-U.extra_dir[i][0], -U.extra_dir[i][1], -U.extra_dir[i][2]};
+        float di = net_max(0.0f, dot3(wn, nd));
+        lit.x = lit.x + base.x * di * U.extra_color[i][0];
+        lit.y = lit.y + base.y * di * U.extra_color[i][1];
+        lit.z = lit.z + base.z * di * U.extra_color[i][2];
+    }
+    // Vector4.Lerp(FogColor, lit, fog)
+    V4 fin = {lerp1(U.fog_color[0], lit.x, fog, fma), lerp1(U.fog_color[1], lit.y, fog, fma),
+              lerp1(U.fog_color[2], lit.z, fog, fma), 0.0f};
+    return {fin.x, fin.y, fin.z, base.w};
+}
+
+// Rasterizer.Blend (Rasterizer.cs:58-65).
+inline V4 blend(V4 s, V4 d, int mode) {
+    switch (mode) {
+        case 1: {  // Alpha: src*src.W + dst*(1-src.W), all four channels
+            float a = s.w, ia = 1.0f - s.w;
+            return {s.x * a + d.x * ia, s.y * a + d.y * ia, s.z * a + d.z * ia, s.w * a + d.w * ia};
+        }
+        case 2: {  // Additive: Vector4.Min(src+dst, One)
+            // Vector4.Min is a per-lane (x < y) ? x : y select on the sum.
+            float x = s.x + d.x, y = s.y + d.y, z = s.z + d.z, w = s.w + d.w;
+            return {x < 1.0f ? x : 1.0f, y < 1.0f ? y : 1.0f, z < 1.0f ? z : 1.0f, w < 1.0f ? w : 1.0f};
+        }
+        case 3: return {s.x * d.x, s.y * d.y, s.z * d.z, s.w * d.w};
+        default: return s;
+    }
+}
+
+// GetDepthTestFunction (Rasterizer.cs:542-559); note the flipped compares.
+inline bool depth_pass(int test, float nd, float od) {
+    switch (test) {
+        case 1: return nd > od;                     // Less
+        case 2: return nd >= od;                    // LessEqual
+        case 3: return nd < od;                     // Greater
+        case 4: return nd <= od;                    // GreaterEqual
+        case 5: return fabsf(nd - od) < kEps;       // Equal
+        case 6: return fabsf(nd - od) >= kEps;      // NotEqual
+        default: return true;                       // Disabled, Always
+    }
+}
+
+inline float edge_fn(V2 a, V2 b, V2 c) {            // Rasterizer.cs:561-563
+    return (c.x - a.x) * (b.y - a.y) - (c.y - a.y) * (b.x - a.x);
+}
+
+}  // namespace
+
+// ===========================================================================
+// Window (MainWindow.cs:23-31, 378-436) and the triangle pipeline
+// ===========================================================================
+struct OrcWindow {
+    int W, H;
+    std::vector<V4> color;
+    std::vector<float> depth;
+    OrcStats stats;
+};
+
+namespace {
+
+// Post-DrawTriangle state of one triangle (Rasterizer.cs:365-398, 411-452).
+struct SetupTri {
+    V2 s[3];          // screen coords of outputs {v2, v1, v0}
+    float d[3];       // depths[i] = (ndc.z + 1) * 0.5
+    float cz[3], cw[3];
+    V4 col[3];
+    V2 uv[3];
+    V3 wn[3];
+    float invArea;
+    float a01, b01, a12, b12, a20, b20;
+    int minX, maxX, minY, maxY;
+    int draw;
+};
+
+// DrawTriangle + head of RasterizeTriangle (Rasterizer.cs:342-452).
+// Returns false when the triangle is rejected before the pixel loops.
+inline bool setup_triangle(const VOut& v0, const VOut& v1, const VOut& v2, int W, int H,
+                           int cull, SetupTri& t) {
+    const VOut* o[3] = {&v2, &v1, &v0};               // :367
+    for (int i = 0; i < 3; ++i) {
+        float invW = 1.0f / o[i]->clip.w;
+        float nx = o[i]->clip.x * invW, ny = o[i]->clip.y * invW, nz = o[i]->clip.z * invW;
+        if (std::isnan(nx) || std::isnan(ny) || std::isnan(nz) ||
+            std::isinf(nx) || std::isinf(ny) || std::isinf(nz))
+            return false;                             // :378-380
+        t.s[i].x = (nx * 0.5f + 0.5f) * (float)W;     // :383-386
+        t.s[i].y = (1.0f - (ny * 0.5f + 0.5f)) * (float)H;
+        t.d[i]   = (nz + 1.0f) * 0.5f;                // :388
+        t.cz[i] = o[i]->clip.z; t.cw[i] = o[i]->clip.w;
+        t.col[i] = o[i]->color; t.uv[i] = o[i]->uv; t.wn[i] = o[i]->wn;
+    }
+    if (v0.clip.w == 0 || v1.clip.w == 0 || v2.clip.w == 0) return false;   // :393
+    float area = edge_fn(t.s[0], t.s[1], t.s[2]);     // :396, :411
+    if (area == 0) return false;
+    bool front = area < 0;                            // :414
+    if ((cull == 1 && !front) || (cull == 2 && front)) return false;
+    t.invArea = 1.0f / area;                          // :427
+    float minXf = net_min(net_min(t.s[0].x, t.s[1].x), t.s[2].x);
+    float maxXf = net_max(net_max(t.s[0].x, t.s[1].x), t.s[2].x);
+    float minYf = net_min(net_min(t.s[0].y, t.s[1].y), t.s[2].y);
+    float maxYf = net_max(net_max(t.s[0].y, t.s[1].y), t.s[2].y);
+    int a = sat_int(floorf(minXf)), b = sat_int(ceilf(maxXf));
+    int c = sat_int(floorf(minYf)), e = sat_int(ceilf(maxYf));
+    t.minX = a > 0 ? a : 0;                           // :437-440
+    t.maxX = b < W - 1 ? b : W - 1;
+    t.minY = c > 0 ? c : 0;
+    t.maxY = e < H - 1 ? e : H - 1;
+    if (t.minX > t.maxX || t.minY > t.maxY) return false;
+    t.a01 = t.s[0].y - t.s[1].y; t.b01 = t.s[1].x - t.s[0].x;   // :445-447
+    t.a12 = t.s[1].y - t.s[2].y; t.b12 = t.s[2].x - t.s[1].x;
+    t.a20 = t.s[2].y - t.s[0].y; t.b20 = t.s[0].x - t.s[2].x;
+    return true;
+}
+
+// Interpolate + InterpolateData (Rasterizer.cs:566-707), stock varyings only.
+// Object Normal, ScreenCoords, Barycentric and clip x/y/w are unobservable
+// through the stock fragment shader and are not computed.
+inline void interpolate(const SetupTri& t, float w0, float w1, float w2,
+                        V3& wn, V4& col, V2& uv, float& clipZ) {
+    float ra = w0 / t.cw[0], rb = w1 / t.cw[1], rc = w2 / t.cw[2];   // :576-578
+    float sum = ra + rb + rc;
+    float w = 1.0f / sum;
+    float wa = ra * w, wb = rb * w, wc = rc * w;
+    clipZ = ((t.cz[0] * ra + t.cz[1] * rb) + t.cz[2] * rc) * w;       // :588-591
+    uv.x = ((t.uv[0].x * ra + t.uv[1].x * rb) + t.uv[2].x * rc) * w;  // :593-596
+    uv.y = ((t.uv[0].y * ra + t.uv[1].y * rb) + t.uv[2].y * rc) * w;
+    col.x = ((t.col[0].x * ra + t.col[1].x * rb) + t.col[2].x * rc) * w;   // :615-618
+    col.y = ((t.col[0].y * ra + t.col[1].y * rb) + t.col[2].y * rc) * w;
+    col.z = ((t.col[0].z * ra + t.col[1].z * rb) + t.col[2].z * rc) * w;
+    col.w = ((t.col[0].w * ra + t.col[1].w * rb) + t.col[2].w * rc) * w;
+    V3 n = {(t.wn[0].x * wa + t.wn[1].x * wb) + t.wn[2].x * wc,      // :680-688
+            (t.wn[0].y * wa + t.wn[1].y * wb) + t.wn[2].y * wc,
+            (t.wn[0].z * wa + t.wn[1].z * wb) + t.wn[2].z * wc};
+    float l2 = dot3(n, n);
+    if (l2 > 1e-6f) {
+        float inv = 1.0f / sqrtf(l2);
+        n = {n.x * inv, n.y * inv, n.z * inv};
+    }
+    wn = n;
+}
+
+struct LocalStats { int64_t tested = 0, shaded = 0; };
+
+// Pixel loops of RasterizeTriangle for one tile (Rasterizer.cs:466-536).
+inline void raster_tile(OrcWindow& win, const SetupTri& t, const OrcDraw& d, const OrcUniforms& U,
+                        int tileX, int tileY, LocalStats& st) {
+    const int W = win.W, H = win.H;
+    int tsx = tileX * kTile, tsy = tileY * kTile;
+    int tex_ = tsx + kTile - 1; if (tex_ > W - 1) tex_ = W - 1;
+    int tey = tsy + kTile - 1; if (tey > H - 1) tey = H - 1;
+    int startX = t.minX > tsx ? t.minX : tsx, endX = t.maxX < tex_ ? t.maxX : tex_;
+    int startY = t.minY > tsy ? t.minY : tsy, endY = t.maxY < tey ? t.maxY : tey;
+    if (startX > endX || startY > endY) return;
+    float fx = (float)startX, fy = (float)startY;
+    float w0Row = t.a12 * (fx - t.s[1].x) + t.b12 * (fy - t.s[1].y);   // :481-483
+    float w1Row = t.a20 * (fx - t.s[2].x) + t.b20 * (fy - t.s[2].y);
+    float w2Row = t.a01 * (fx - t.s[0].x) + t.b01 * (fy - t.s[0].y);
+    const bool needsDepth = d.depth_test != 0;
+    const bool canEarlyOut = d.blend == 0;
+    for (int y = startY; y <= endY; ++y) {
+        float w0 = w0Row, w1 = w1Row, w2 = w2Row;
+        for (int x = startX; x <= endX; ++x) {
+            bool inside = (w0 >= 0 && w1 >= 0 && w2 >= 0) || (w0 <= 0 && w1 <= 0 && w2 <= 0);
+            if (inside) {
+                ++st.tested;
+                float w0f = w0 * t.invArea, w1f = w1 * t.invArea, w2f = w2 * t.invArea;
+                float depth = t.d[0] * w0f + t.d[1] * w1f + t.d[2] * w2f;      // :502
+                size_t idx = (size_t)y * W + x;
+                float old = win.depth[idx];
+                if (depth_pass(d.depth_test, depth, old)) {
+                    ++st.shaded;
+                    V3 wn; V4 col; V2 uv; float cz;
+                    interpolate(t, w0f, w1f, w2f, wn, col, uv, cz);
+                    V4 c = fragment_shader(wn, col, uv, cz, d, U);
+                    if (c.w > 0.0f) {                                         // :511
+                        win.color[idx] = blend(c, win.color[idx], d.blend);
+                        if (needsDepth) win.depth[idx] = depth;
+                    } else if (canEarlyOut) {
+                        break;                                                // :520-523
+                    }
+                }
+            }
+            w0 += t.a12; w1 += t.a20; w2 += t.a01;                            // :527-529
+        }
+        w0Row += t.b12; w1Row += t.b20; w2Row += t.b01;                       // :532-534
+    }
+}
+
+// Body of the Parallel.For lambda in RenderMesh (Rasterizer.cs:200-229):
+// shade three corners, behind tests, optional near clip, setup.
+inline int process_triangle(const OrcDraw& d, const OrcUniforms& U, int tri, int W, int H,
+                            int drawIndex, SetupTri out[2]) {
+    bool fma = U.numerics_fma != 0;
+    VOut v[3];
+    for (int k = 0; k < 3; ++k) {
+        int vi = d.indices[tri * 3 + k];
+        v[k] = vertex_shader(d.vertices + (size_t)vi * 12, d.model, d.view, d.proj, fma);
+    }
+    bool b0 = v[0].clip.w <= 0, b1 = v[1].clip.w <= 0, b2 = v[2].clip.w <= 0;
+    if (b0 && b1 && b2) return 0;
+    int n = 0;
+    if (b0 || b1 || b2) {
+        VOut tris[2][3];
+        int nt = clip_near(v, U.near_clip, fma, tris);
+        for (int i = 0; i < nt; ++i)
+            if (setup_triangle(tris[i][0], tris[i][1], tris[i][2], W, H, d.cull, out[n])) {
+                out[n].draw = drawIndex; ++n;
+            }
+    } else if (setup_triangle(v[0], v[1], v[2], W, H, d.cull, out[0])) {
+        out[0].draw = drawIndex; n = 1;
+    }
+    return n;
+}
+
+}  // namespace
+
+extern "C" {
+
+OrcWindow* orc_create(int width, int height) {
+    if (width <= 0 || height <= 0) return nullptr;       // Rasterizer.cs:71-74
+    OrcWindow* w = new OrcWindow();
+    w->W = width; w->H = height;
+    w->color.assign((size_t)width * height, V4{0, 0, 0, 0});
+    w->depth.assign((size_t)width * height, 0.0f);
+    std::memset(&w->stats, 0, sizeof(w->stats));
+    return w;
+}
+void orc_destroy(OrcWindow* w) { delete w; }
+int orc_width(const OrcWindow* w) { return w->W; }
+int orc_height(const OrcWindow* w) { return w->H; }
+float* orc_color(OrcWindow* w) { return &w->color[0].x; }
+float* orc_depth(OrcWindow* w) { return w->depth.data(); }
+
+void orc_clear_color(OrcWindow* w, const float rgba[4]) {
+    V4 c = {rgba[0], rgba[1], rgba[2], rgba[3]};
+    for (auto& p : w->color) p = c;
+}
+void orc_clear_depth(OrcWindow* w) {
+    for (auto& p : w->depth) p = -3.402823466e+38f;     // float.MinValue
+    std::memset(&w->stats, 0, sizeof(w->stats));
+}
+void orc_get_stats(const OrcWindow* w, OrcStats* out) { *out = w->stats; }
+
+void orc_render_mesh(OrcWindow* w, const OrcDraw* d, const OrcUniforms* u) {
+    if (w->W <= 0 || w->H <= 0) return;                  // :176
+    int ntri = d->n_indices / 3;
+    LocalStats st;
+    for (int tri = 0; tri < ntri; ++tri) {
+        SetupTri ts[2];
+        int n = process_triangle(*d, *u, tri, w->W, w->H, 0, ts);
+        w->stats.triangles_in++;
+        for (int i = 0; i < n; ++i) {
+            const SetupTri& t = ts[i];
+            w->stats.triangles_drawn++;
+            int tminx = t.minX / kTile, tmaxx = t.maxX / kTile;      // :449-452
+            int tminy = t.minY / kTile, tmaxy = t.maxY / kTile;
+            for (int ty = tminy; ty <= tmaxy; ++ty)
+                for (int tx = tminx; tx <= tmaxx; ++tx)
+                    raster_tile(*w, t, *d, *u, tx, ty, st);
+        }
+    }
+    w->stats.fragments_tested += st.tested;
+    w->stats.fragments_shaded += st.shaded;
+}
+
+void orc_render_frame_mt(OrcWindow* w, const OrcDraw* draws, int n_draws, const OrcUniforms* u,
+                         int n_threads, int tile_row0, int tile_row1) {
+    if (w->W <= 0 || w->H <= 0 || n_draws <= 0) return;
+    if (n_threads < 1) n_threads = 1;
+    const int W = w->W, H = w->H;
+    const int tilesY = (H + kTile - 1) / kTile;
+    if (tile_row0 < 0) tile_row0 = 0;
+    if (tile_row1 > tilesY) tile_row1 = tilesY;
+
+    // Phase A: triangle processing, parallel over contiguous chunks of the
+    // global (draw, triangle) sequence; chunk order == submission order.
+    std::vector<int64_t> triBase(n_draws + 1, 0);
+    for (int i = 0; i < n_draws; ++i) triBase[i + 1] = triBase[i] + draws[i].n_indices / 3;
+    const int64_t total = triBase[n_draws];
+    const int nChunks = n_threads * 8;
+    std::vector<std::vector<SetupTri>> chunks(nChunks);
+    std::atomic<int> nextChunk{0};
+    auto phaseA = [&]() {
+        for (;;) {
+            int c = nextChunk.fetch_add(1);
+            if (c >= nChunks) break;
+            int64_t lo = total * c / nChunks, hi = total * (c + 1) / nChunks;
+            int di = 0;
+            while (di < n_draws && triBase[di + 1] <= lo) ++di;
+            auto& out = chunks[c];
+            for (int64_t g = lo; g < hi; ++g) {
+                while (triBase[di + 1] <= g) ++di;
+                SetupTri ts[2];
+                int n = process_triangle(draws[di], *u, (int)(g - triBase[di]), W, H, di, ts);
+                for (int i = 0; i < n; ++i) out.push_back(ts[i]);
+            }
+        }
+    };
+    {
+        std::vector<std::thread> th;
+        for (int i = 1; i < n_threads; ++i) th.emplace_back(phaseA);
+        phaseA();
+        for (auto& t : th) t.join();
+    }
+    // Row buckets in submission order.
+    std::vector<const SetupTri*> all;
+    for (auto& c : chunks) for (auto& t : c) all.push_back(&t);
+    std::vector<std::vector<uint32_t>> rows(tilesY);
+    for (size_t i = 0; i < all.size(); ++i) {
+        int a = all[i]->minY / kTile, b = all[i]->maxY / kTile;
+        for (int r = a; r <= b; ++r)
+            if (r >= tile_row0 && r < tile_row1) rows[r].push_back((uint32_t)i);
+    }
+    // Phase B: each thread owns whole tile rows.
+    std::atomic<int> nextRow{tile_row0};
+    std::atomic<int64_t> tested{0}, shaded{0};
+    auto phaseB = [&]() {
+        LocalStats st;
+        for (;;) {
+            int r = nextRow.fetch_add(1);
+            if (r >= tile_row1) break;
+            for (uint32_t i : rows[r]) {
+                const SetupTri& t = *all[i];
+                int tminx = t.minX / kTile, tmaxx = t.maxX / kTile;
+                for (int tx = tminx; tx <= tmaxx; ++tx)
+                    raster_tile(*w, t, draws[t.draw], *u, tx, r, st);
+            }
+        }
+        tested += st.tested; shaded += st.shaded;
+    };
+    {
+        std::vector<std::thread> th;
+        for (int i = 1; i < n_threads; ++i) th.emplace_back(phaseB);
+        phaseB();
+        for (auto& t : th) t.join();
+    }
+    w->stats.triangles_in += total;
+    w->stats.triangles_drawn += (int64_t)all.size();
+    w->stats.fragments_tested += tested.load();
+    w->stats.fragments_shaded += shaded.load();
+}
+
+void orc_texture_sample(const uint8_t* rgba8, int tw, int th, float u, float v, int filter, float out[4]) {
+    V4 r = filter == 1 ? tex_bilinear(rgba8, tw, th, u, v) : tex_nearest(rgba8, tw, th, u, v);
+    out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+}
+
+void orc_vertex_shader(const float vtx[12], const float model[16], const float view[16],
+                       const float proj[16], int numerics_fma, float out_clip[4], float out_wn[3]) {
+    VOut o = vertex_shader(vtx, model, view, proj, numerics_fma != 0);
+    out_clip[0] = o.clip.x; out_clip[1] = o.clip.y; out_clip[2] = o.clip.z; out_clip[3] = o.clip.w;
+    out_wn[0] = o.wn.x; out_wn[1] = o.wn.y; out_wn[2] = o.wn.z;
+}
+
+int orc_clip_near(const float clip_in[12], float near_clip, int numerics_fma, float out_clip[24]) {
+    VOut v[3];
+    std::memset(v, 0, sizeof(v));
+    for (int i = 0; i < 3; ++i)
+        v[i].clip = {clip_in[4 * i], clip_in[4 * i + 1], clip_in[4 * i + 2], clip_in[4 * i + 3]};
+    VOut tris[2][3];
+    int n = clip_near(v, near_clip, numerics_fma != 0, tris);
+    for (int t = 0; t < n; ++t)
+        for (int k = 0; k < 3; ++k) {
+            float* o = out_clip + (t * 3 + k) * 4;
+            o[0] = tris[t][k].clip.x; o[1] = tris[t][k].clip.y;
+            o[2] = tris[t][k].clip.z; o[3] = tris[t][k].clip.w;
+        }
+    return n;
+}
+
+// FrustumCuller.IsSphereInFrustum (FrustumCuller.cs:153-224, 19-35).
+int orc_sphere_in_frustum(const float sphere[4], const float M[16], const float V[16],
+                          const float P[16], int numerics_fma) {
+    bool fma = numerics_fma != 0;
+    V4 wc4 = transform4({sphere[0], sphere[1], sphere[2], 1.0f}, M, fma);   // Vector3.Transform
+    V3 c = {wc4.x, wc4.y, wc4.z};
+    float s0 = sqrtf(M[0] * M[0] + M[1] * M[1] + M[2] * M[2]);
+    float s1 = sqrtf(M[4] * M[4] + M[5] * M[5] + M[6] * M[6]);
+    float s2 = sqrtf(M[8] * M[8] + M[9] * M[9] + M[10] * M[10]);
+    float r = sphere[3] * net_max(net_max(s0, s1), s2);
+    float VP[16];                                        // Matrix4x4.Multiply(view, proj)
+    for (int i = 0; i < 4; ++i) {
+        V4 row = transform4({V[4 * i], V[4 * i + 1], V[4 * i + 2], V[4 * i + 3]}, P, fma);
+        VP[4 * i] = row.x; VP[4 * i + 1] = row.y; VP[4 * i + 2] = row.z; VP[4 * i + 3] = row.w;
+    }
+    // column k of VP (0-based): M1k..M4k = VP[k], VP[4+k], VP[8+k], VP[12+k]
+    auto plane_ok = [&](int k, float sign) {
+        float x = VP[3] + sign * VP[k], y = VP[7] + sign * VP[4 + k];
+        float z = VP[11] + sign * VP[8 + k], d = VP[15] + sign * VP[12 + k];
+        float mag = sqrtf(x * x + y * y + z * z);        // NormalizePlane
+        V3 n = {x / mag, y / mag, z / mag};
+        float dist = d / mag;
+        n = normalize3(n);                               // Plane ctor renormalises (:26)
+        return dot3(n, c) + dist > -r;                   // TestSphereAgainstPlane
+    };
+    // order: Left, Right, Top, Bottom, Near, Far (:211-216)
+    return plane_ok(0, 1.0f) && plane_ok(0, -1.0f) && plane_ok(1, 1.0f) && plane_ok(1, -1.0f) &&
+           plane_ok(2, 1.0f) && plane_ok(2, -1.0f);
+}
+
+}  // extern "C"

@@ -1,0 +1,227 @@
+// srb_device.cuh -- device-side data layout and exact-arithmetic helpers.
+//
+// Everything that feeds coverage or depth is written with explicit
+// round-to-nearest intrinsics (__fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn), which
+// ptxas never contracts into FMA, so the results are the same IEEE single
+// operations RyuJIT emits for the reference's scalar C# (SURVEY.md A.5-A.7).
+// The TU is additionally compiled with -fmad=false.  Fused operations appear
+// only where System.Numerics fuses (numerics_fma switch).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/srb200.h"
+
+namespace srb {
+
+constexpr int kTile = 16;                 // Rasterizer.cs:53
+constexpr float kEps = 1e-6f;             // Rasterizer.cs:52
+constexpr float kClearDepth = -3.402823466e+38f;   // float.MinValue, MainWindow.cs:434
+
+// ---- per-frame draw record (device copy of one RenderMesh call) ----
+struct DrawRec {
+    float model[16];
+    float view[16];
+    float proj[16];
+    float sphere[4];
+    const float4*   vtx;      // mesh vertices, 3 float4 per vertex (48 B, Shaders.cs:10-24)
+    const uint16_t* idx;
+    const uchar4*   tex;      // nullptr = untextured
+    int32_t n_vertices;
+    int32_t n_triangles;
+    int32_t vbase;            // first slot in the transformed-vertex arrays
+    int32_t tbase;            // first global triangle id
+    int32_t tex_w, tex_h;
+    int32_t cull, depth_test, blend;
+    uint32_t flags;
+    int32_t visible;          // written by the frustum kernel
+    int32_t _pad;
+};
+
+// ---- triangle setup record, 64 B, slot = 2*global_triangle + fan ----
+// s = screen coords of outputs {v2,v1,v0} (Rasterizer.cs:367,383-386),
+// d = depths (:388), cz/cw = clip z/w of the same three corners.
+struct __align__(16) TriRec {
+    float s0x, s0y, s1x, s1y;
+    float s2x, s2y, d0, d1;
+    float d2, cz0, cz1, cz2;
+    float cw0, cw1, cw2;
+    uint32_t meta;            // bit31: clipped (low bits = side-buffer index); else draw id
+};
+static_assert(sizeof(TriRec) == 64, "TriRec must be 64 B");
+
+// Varyings of a near-clipped triangle (Shaders.Lerp outputs), 3 corners in output order.
+struct __align__(16) ClipAttr {
+    float uv[3][2];
+    float col[3][4];
+    float wn[3][3];
+    int32_t draw;
+};
+
+// Compact list entry for accepted triangles: seq + tile range.
+struct __align__(16) TriRef {
+    uint32_t seq;             // 2*global_triangle + fan
+    uint32_t tx;              // tminx | tmaxx << 16
+    uint32_t ty;              // tminy | tmaxy << 16
+    uint32_t _pad;
+};
+
+// ---- .NET semantics helpers ----
+__device__ __forceinline__ float net_max(float a, float b) {   // MathF.Max: NaN-propagating
+    if (a != a) return a;
+    if (b != b) return b;
+    return a > b ? a : b;
+}
+__device__ __forceinline__ float net_min(float a, float b) {
+    if (a != a) return a;
+    if (b != b) return b;
+    return a < b ? a : b;
+}
+__device__ __forceinline__ float net_clamp(float v, float lo, float hi) {   // Math.Clamp
+    if (v < lo) return lo;
+    if (v > hi) return hi;
+    return v;
+}
+// .NET 9 float->int conversion saturates and maps NaN to 0: exactly cvt.rzi.s32.f32.
+__device__ __forceinline__ int sat_int(float f) { return __float2int_rz(f); }
+
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+
+// Vector4.Transform(v, M), row-vector convention, one output column.
+template <bool FMA>
+__device__ __forceinline__ float xform_col(float x, float y, float z, float w, const float* m, int c) {
+    float acc = mul(m[c], x);
+    if (FMA) {
+        acc = __fmaf_rn(m[4 + c], y, acc);
+        acc = __fmaf_rn(m[8 + c], z, acc);
+        acc = __fmaf_rn(m[12 + c], w, acc);
+    } else {
+        acc = add(acc, mul(m[4 + c], y));
+        acc = add(acc, mul(m[8 + c], z));
+        acc = add(acc, mul(m[12 + c], w));
+    }
+    return acc;
+}
+template <bool FMA>
+__device__ __forceinline__ float4 transform4(float4 v, const float* m) {
+    return make_float4(xform_col<FMA>(v.x, v.y, v.z, v.w, m, 0), xform_col<FMA>(v.x, v.y, v.z, v.w, m, 1),
+                       xform_col<FMA>(v.x, v.y, v.z, v.w, m, 2), xform_col<FMA>(v.x, v.y, v.z, v.w, m, 3));
+}
+// Vector3.TransformNormal(n, M), one output column.
+template <bool FMA>
+__device__ __forceinline__ float xform_normal_col(float x, float y, float z, const float* m, int c) {
+    float acc = mul(m[c], x);
+    if (FMA) {
+        acc = __fmaf_rn(m[4 + c], y, acc);
+        acc = __fmaf_rn(m[8 + c], z, acc);
+    } else {
+        acc = add(acc, mul(m[4 + c], y));
+        acc = add(acc, mul(m[8 + c], z));
+    }
+    return acc;
+}
+__device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return add(add(mul(ax, bx), mul(ay, by)), mul(az, bz));
+}
+// Vector{2,3,4}.Lerp per component.
+__device__ __forceinline__ float lerp1(float a, float b, float t, bool fma) {
+    float omt = sub(1.0f, t);
+    float bt = mul(b, t);
+    return fma ? __fmaf_rn(a, omt, bt) : add(mul(a, omt), bt);
+}
+
+// Rasterizer.EdgeFunction (Rasterizer.cs:561-563).
+__device__ __forceinline__ float edge_fn(float ax, float ay, float bx, float by, float cx, float cy) {
+    return sub(mul(sub(cx, ax), sub(by, ay)), mul(sub(cy, ay), sub(bx, ax)));
+}
+
+// Monotone map float -> uint32 (greater float <=> greater uint); -0 canonicalised to +0.
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    uint32_t u = __float_as_uint(f + 0.0f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t o) {
+    uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+    return __uint_as_float(u);
+}
+
+// GetDepthTestFunction (Rasterizer.cs:542-559), flipped compares included.
+__device__ __forceinline__ bool depth_pass(int test, float nd, float od) {
+    switch (test) {
+        case SRB_DEPTH_LESS: return nd > od;
+        case SRB_DEPTH_LESS_EQUAL: return nd >= od;
+        case SRB_DEPTH_GREATER: return nd < od;
+        case SRB_DEPTH_GREATER_EQUAL: return nd <= od;
+        case SRB_DEPTH_EQUAL: return fabsf(sub(nd, od)) < kEps;
+        case SRB_DEPTH_NOT_EQUAL: return fabsf(sub(nd, od)) >= kEps;
+        default: return true;
+    }
+}
+
+// Rasterizer.Blend (Rasterizer.cs:58-65).
+__device__ __forceinline__ float4 blend_px(float4 s, float4 d, int mode) {
+    switch (mode) {
+        case SRB_BLEND_ALPHA: {
+            float a = s.w, ia = sub(1.0f, s.w);
+            return make_float4(add(mul(s.x, a), mul(d.x, ia)), add(mul(s.y, a), mul(d.y, ia)),
+                               add(mul(s.z, a), mul(d.z, ia)), add(mul(s.w, a), mul(d.w, ia)));
+        }
+        case SRB_BLEND_ADDITIVE: {
+            float x = add(s.x, d.x), y = add(s.y, d.y), z = add(s.z, d.z), w = add(s.w, d.w);
+            return make_float4(x < 1.0f ? x : 1.0f, y < 1.0f ? y : 1.0f, z < 1.0f ? z : 1.0f, w < 1.0f ? w : 1.0f);
+        }
+        case SRB_BLEND_MULTIPLY:
+            return make_float4(mul(s.x, d.x), mul(s.y, d.y), mul(s.z, d.z), mul(s.w, d.w));
+        default: return s;
+    }
+}
+
+// Per-triangle raster constants derived from a TriRec (Rasterizer.cs:427-447).
+struct TriEq {
+    float a01, b01, a12, b12, a20, b20;
+    float invArea;
+    int minX, maxX, minY, maxY;
+};
+__device__ __forceinline__ void tri_bbox(const TriRec& r, int W, int H, int& minX, int& maxX, int& minY, int& maxY) {
+    float minXf = net_min(net_min(r.s0x, r.s1x), r.s2x);
+    float maxXf = net_max(net_max(r.s0x, r.s1x), r.s2x);
+    float minYf = net_min(net_min(r.s0y, r.s1y), r.s2y);
+    float maxYf = net_max(net_max(r.s0y, r.s1y), r.s2y);
+    minX = max(sat_int(floorf(minXf)), 0);            // :437-440
+    maxX = min(sat_int(ceilf(maxXf)), W - 1);
+    minY = max(sat_int(floorf(minYf)), 0);
+    maxY = min(sat_int(ceilf(maxYf)), H - 1);
+}
+__device__ __forceinline__ TriEq tri_eq(const TriRec& r, int W, int H) {
+    TriEq e;
+    float area = edge_fn(r.s0x, r.s0y, r.s1x, r.s1y, r.s2x, r.s2y);
+    e.invArea = fdiv(1.0f, area);
+    e.a01 = sub(r.s0y, r.s1y); e.b01 = sub(r.s1x, r.s0x);   // :445-447
+    e.a12 = sub(r.s1y, r.s2y); e.b12 = sub(r.s2x, r.s1x);
+    e.a20 = sub(r.s2y, r.s0y); e.b20 = sub(r.s0x, r.s2x);
+    tri_bbox(r, W, H, e.minX, e.maxX, e.minY, e.maxY);
+    return e;
+}
+// Row bases at (startX, startY) by the direct formula (Rasterizer.cs:481-483).
+__device__ __forceinline__ void row_base(const TriRec& r, const TriEq& e, int startX, int startY,
+                                         float& w0, float& w1, float& w2) {
+    float fx = (float)startX, fy = (float)startY;
+    w0 = add(mul(e.a12, sub(fx, r.s1x)), mul(e.b12, sub(fy, r.s1y)));
+    w1 = add(mul(e.a20, sub(fx, r.s2x)), mul(e.b20, sub(fy, r.s2y)));
+    w2 = add(mul(e.a01, sub(fx, r.s0x)), mul(e.b01, sub(fy, r.s0y)));
+}
+// centerInside (Rasterizer.cs:493-494): inclusive on every edge, either sign.
+__device__ __forceinline__ bool inside3(float w0, float w1, float w2) {
+    return (w0 >= 0 && w1 >= 0 && w2 >= 0) || (w0 <= 0 && w1 <= 0 && w2 <= 0);
+}
+// depth at a covered pixel (Rasterizer.cs:498-502).
+__device__ __forceinline__ float frag_depth(float d0, float d1, float d2, float invArea,
+                                            float w0, float w1, float w2,
+                                            float& w0f, float& w1f, float& w2f) {
+    w0f = mul(w0, invArea); w1f = mul(w1, invArea); w2f = mul(w2, invArea);
+    return add(add(mul(d0, w0f), mul(d1, w1f)), mul(d2, w2f));
+}
+
+}  // namespace srb

@@ -1,0 +1,258 @@
+// srb_geometry.cuh -- frustum test, vertex stage, triangle setup + near clip,
+// tile binning (count / scan / fill).  Included by srb_kernels.cu only.
+#pragma once
+#include "srb_device.cuh"
+
+namespace srb {
+
+// Frame-level parameters shared by all kernels.
+struct FrameParams {
+    int W, H;
+    int tilesX, tilesY;
+    int bandRow0, bandRow1;       // tile rows rendered by this context [row0,row1)
+    int nDraws;
+    int totalV, totalT;
+    uint32_t pairCap;             // capacity of the bin array
+    uint32_t clipCap;             // capacity of the ClipAttr side buffer
+    float clearColor[4];
+    int loadColor, loadDepth;     // 1 = keep existing framebuffer contents (no clear this frame)
+    int depthMode;                // visibility path: the frame's common depth test
+};
+
+// Device-side counters of one frame.
+struct Counters {
+    uint32_t nRefs;               // accepted triangles (compact list length)
+    uint32_t nPairs;              // total (triangle,tile) pairs (from the scan)
+    uint32_t nClipped;            // ClipAttr entries used
+    uint32_t nClippedTris;        // triangles that entered the clipper
+    uint32_t overflow;            // bit0: bins, bit1: clip side buffer
+    uint32_t nVisibleDraws;
+    uint32_t _pad[2];
+};
+
+// ---------------------------------------------------------------------------
+// FrustumCuller.IsSphereInFrustum (FrustumCuller.cs:153-224, Plane ctor :19-28)
+// ---------------------------------------------------------------------------
+template <bool FMA>
+__device__ bool sphere_in_frustum(const float* sphere, const float* M, const float* V, const float* P) {
+    float4 wc = transform4<FMA>(make_float4(sphere[0], sphere[1], sphere[2], 1.0f), M);
+    float s0 = __fsqrt_rn(add(add(mul(M[0], M[0]), mul(M[1], M[1])), mul(M[2], M[2])));
+    float s1 = __fsqrt_rn(add(add(mul(M[4], M[4]), mul(M[5], M[5])), mul(M[6], M[6])));
+    float s2 = __fsqrt_rn(add(add(mul(M[8], M[8]), mul(M[9], M[9])), mul(M[10], M[10])));
+    float r = mul(sphere[3], net_max(net_max(s0, s1), s2));
+    float VP[16];                                    // Matrix4x4.Multiply(view, projection)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float4 row = transform4<FMA>(make_float4(V[4 * i], V[4 * i + 1], V[4 * i + 2], V[4 * i + 3]), P);
+        VP[4 * i] = row.x; VP[4 * i + 1] = row.y; VP[4 * i + 2] = row.z; VP[4 * i + 3] = row.w;
+    }
+    bool ok = true;
+    // Left, Right, Top, Bottom, Near, Far (:211-216): column k with sign +/-.
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            float sg = s == 0 ? 1.0f : -1.0f;
+            float x = add(VP[3], mul(sg, VP[k])), y = add(VP[7], mul(sg, VP[4 + k]));
+            float z = add(VP[11], mul(sg, VP[8 + k])), d = add(VP[15], mul(sg, VP[12 + k]));
+            float mag = __fsqrt_rn(add(add(mul(x, x), mul(y, y)), mul(z, z)));     // NormalizePlane
+            float nx = fdiv(x, mag), ny = fdiv(y, mag), nz = fdiv(z, mag), dist = fdiv(d, mag);
+            float len = __fsqrt_rn(dot3(nx, ny, nz, nx, ny, nz));                  // Plane ctor :26
+            nx = fdiv(nx, len); ny = fdiv(ny, len); nz = fdiv(nz, len);
+            float sd = add(dot3(nx, ny, nz, wc.x, wc.y, wc.z), dist);
+            ok = ok && (sd > -r);
+        }
+    }
+    return ok;
+}
+
+__global__ void frustum_draws_kernel(DrawRec* draws, int nDraws, int fma, Counters* cnt) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nDraws) return;
+    DrawRec& d = draws[i];
+    int vis = 1;
+    if (d.flags & SRB_DRAW_FRUSTUM_CULL)
+        vis = fma ? sphere_in_frustum<true>(d.sphere, d.model, d.view, d.proj)
+                  : sphere_in_frustum<false>(d.sphere, d.model, d.view, d.proj);
+    d.visible = vis;
+    if (vis) atomicAdd(&cnt->nVisibleDraws, 1u);
+}
+
+__global__ void frustum_batch_kernel(const float* spheres, const float* models, const float* viewproj,
+                                     int n, int fma, int32_t* out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* V = viewproj;
+    const float* P = viewproj + 16;
+    out[i] = fma ? sphere_in_frustum<true>(spheres + 4 * i, models + 16 * i, V, P)
+                 : sphere_in_frustum<false>(spheres + 4 * i, models + 16 * i, V, P);
+}
+
+// Largest i with base[i] <= g  (base has n+1 entries, base[n] = total).
+__device__ __forceinline__ int find_owner(const int32_t* __restrict__ base, int n, int g) {
+    int lo = 0, hi = n;            // invariant: base[lo] <= g < base[hi]
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (__ldg(base + mid) <= g) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// ---------------------------------------------------------------------------
+// Vertex stage: Renderer.VertexShader (Renderer.cs:830-846) once per unique
+// vertex of every visible draw.  48-B vertex read as three float4.
+// ---------------------------------------------------------------------------
+template <bool FMA>
+__global__ void __launch_bounds__(256)
+vertex_kernel(const DrawRec* __restrict__ draws, const int32_t* __restrict__ vbase, FrameParams fp,
+              float4* __restrict__ clipOut, float4* __restrict__ wnOut) {
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= fp.totalV) return;
+    int di = find_owner(vbase, fp.nDraws, g);
+    const DrawRec& d = draws[di];
+    if (!d.visible) return;
+    int v = g - d.vbase;
+    float4 a = __ldg(d.vtx + 3 * v);          // pos.xyz, uv.x
+    float4 b = __ldg(d.vtx + 3 * v + 1);      // uv.y, normal.xyz
+    float4 world = transform4<FMA>(make_float4(a.x, a.y, a.z, 1.0f), d.model);
+    float4 view = transform4<FMA>(world, d.view);
+    float4 clip = transform4<FMA>(view, d.proj);
+    float nx = xform_normal_col<FMA>(b.y, b.z, b.w, d.model, 0);
+    float ny = xform_normal_col<FMA>(b.y, b.z, b.w, d.model, 1);
+    float nz = xform_normal_col<FMA>(b.y, b.z, b.w, d.model, 2);
+    float len = __fsqrt_rn(dot3(nx, ny, nz, nx, ny, nz));     // Vector3.Normalize = v / Length
+    clipOut[g] = clip;
+    wnOut[g] = make_float4(fdiv(nx, len), fdiv(ny, len), fdiv(nz, len), 0.0f);
+}
+
+// ---------------------------------------------------------------------------
+// Triangle setup
+// ---------------------------------------------------------------------------
+// DrawTriangle + head of RasterizeTriangle (Rasterizer.cs:365-398, 411-442) on
+// corners already in output order {v2,v1,v0}.  Returns false on rejection.
+__device__ __forceinline__ bool setup_tri(const float4 c[3], int W, int H, int cull, TriRec& r,
+                                          int& minX, int& maxX, int& minY, int& maxY) {
+    float sx[3], sy[3], dz[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float invW = fdiv(1.0f, c[i].w);
+        float nx = mul(c[i].x, invW), ny = mul(c[i].y, invW), nz = mul(c[i].z, invW);
+        if (isnan(nx) || isnan(ny) || isnan(nz) || isinf(nx) || isinf(ny) || isinf(nz)) return false;
+        sx[i] = mul(add(mul(nx, 0.5f), 0.5f), (float)W);
+        sy[i] = mul(sub(1.0f, add(mul(ny, 0.5f), 0.5f)), (float)H);
+        dz[i] = mul(add(nz, 1.0f), 0.5f);
+    }
+    if (c[0].w == 0.0f || c[1].w == 0.0f || c[2].w == 0.0f) return false;
+    float area = edge_fn(sx[0], sy[0], sx[1], sy[1], sx[2], sy[2]);
+    if (area == 0.0f) return false;
+    bool front = area < 0.0f;
+    if ((cull == SRB_CULL_BACK && !front) || (cull == SRB_CULL_FRONT && front)) return false;
+    r.s0x = sx[0]; r.s0y = sy[0]; r.s1x = sx[1]; r.s1y = sy[1]; r.s2x = sx[2]; r.s2y = sy[2];
+    r.d0 = dz[0]; r.d1 = dz[1]; r.d2 = dz[2];
+    r.cz0 = c[0].z; r.cz1 = c[1].z; r.cz2 = c[2].z;
+    r.cw0 = c[0].w; r.cw1 = c[1].w; r.cw2 = c[2].w;
+    tri_bbox(r, W, H, minX, maxX, minY, maxY);
+    return !(minX > maxX || minY > maxY);
+}
+
+// Full varyings of one corner, needed only inside the near clipper.
+struct ClipVtx {
+    float4 clip;
+    float uv[2];
+    float col[4];
+    float wn[3];
+};
+__device__ __forceinline__ ClipVtx clipvtx_lerp(const ClipVtx& a, const ClipVtx& b, float t, bool fma) {
+    ClipVtx o;                                       // Shaders.Lerp (Shaders.cs:49-95), interpolate=true
+    o.clip = make_float4(lerp1(a.clip.x, b.clip.x, t, fma), lerp1(a.clip.y, b.clip.y, t, fma),
+                         lerp1(a.clip.z, b.clip.z, t, fma), lerp1(a.clip.w, b.clip.w, t, fma));
+#pragma unroll
+    for (int k = 0; k < 2; ++k) o.uv[k] = lerp1(a.uv[k], b.uv[k], t, fma);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o.col[k] = lerp1(a.col[k], b.col[k], t, fma);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) o.wn[k] = lerp1(a.wn[k], b.wn[k], t, fma);
+    return o;
+}
+
+// Result of per-thread setup handed to the binning helpers.
+struct SetupOut {
+    int n;                 // accepted triangles of this thread (0..2)
+    uint32_t seq[2];
+    uint32_t tx[2], ty[2]; // packed tile ranges
+};
+
+// Near-clipped triangle (Rasterizer.cs:95-160, 217-224).  Rare and divergent.
+__device__ __noinline__ void setup_clipped(const DrawRec& d, int vbase, const int i3[3],
+                                           const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
+                                           const FrameParams& fp, const SrbUniforms& U, uint32_t gtri,
+                                           TriRec* recs, ClipAttr* clipAttrs, Counters* cnt, SetupOut& out) {
+    const bool fma = U.numerics_fma != 0;
+    ClipVtx v[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        int vi = i3[k];
+        float4 a = __ldg(d.vtx + 3 * vi), b = __ldg(d.vtx + 3 * vi + 1), c = __ldg(d.vtx + 3 * vi + 2);
+        float4 wn = clipIn == nullptr ? make_float4(0, 0, 0, 0) : wnIn[vbase + vi];
+        v[k].clip = clipIn[vbase + vi];
+        v[k].uv[0] = a.w; v[k].uv[1] = b.x;
+        v[k].col[0] = c.x; v[k].col[1] = c.y; v[k].col[2] = c.z; v[k].col[3] = c.w;
+        v[k].wn[0] = wn.x; v[k].wn[1] = wn.y; v[k].wn[2] = wn.z;
+    }
+    atomicAdd(&cnt->nClippedTris, 1u);
+    ClipVtx poly[4];
+    int n = 0;
+    const float nc = U.near_clip;
+    for (int i = 0; i < 3; ++i) {
+        const ClipVtx& cur = v[i];
+        const ClipVtx& nxt = v[(i + 1) % 3];
+        bool curIn = cur.clip.z >= mul(nc, cur.clip.w);
+        bool nxtIn = nxt.clip.z >= mul(nc, nxt.clip.w);
+        if (curIn && n < 4) poly[n++] = cur;
+        if (curIn != nxtIn) {
+            float z0 = cur.clip.z, w0 = cur.clip.w, z1 = nxt.clip.z, w1 = nxt.clip.w;
+            float denom = sub(sub(z1, z0), mul(nc, sub(w1, w0)));
+            float t;
+            if (fabsf(denom) < kEps) {
+                t = 0.5f;
+            } else {
+                t = fdiv(sub(z0, mul(nc, w0)), sub(mul(nc, sub(w1, w0)), sub(z1, z0)));
+                t = net_clamp(t, 0.0f, 1.0f);
+            }
+            if (n < 4) poly[n++] = clipvtx_lerp(cur, nxt, t, fma);
+        }
+    }
+    if (n < 3) return;
+    for (int f = 0; f + 2 < n; ++f) {                 // fan (0, f+1, f+2)
+        const ClipVtx* tri[3] = {&poly[0], &poly[f + 1], &poly[f + 2]};
+        const ClipVtx* o[3] = {tri[2], tri[1], tri[0]};            // :367 order {v2,v1,v0}
+        float4 c[3] = {o[0]->clip, o[1]->clip, o[2]->clip};
+        TriRec r;
+        int minX, maxX, minY, maxY;
+        if (!setup_tri(c, fp.W, fp.H, d.cull, r, minX, maxX, minY, maxY)) continue;
+        int ty0 = max(minY / kTile, fp.bandRow0), ty1 = min(maxY / kTile, fp.bandRow1 - 1);
+        if (ty0 > ty1) continue;
+        uint32_t slot = atomicAdd(&cnt->nClipped, 1u);
+        if (slot >= fp.clipCap) { atomicOr(&cnt->overflow, 2u); continue; }
+        ClipAttr ca;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            ca.uv[k][0] = o[k]->uv[0]; ca.uv[k][1] = o[k]->uv[1];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ca.col[k][j] = o[k]->col[j];
+#pragma unroll
+            for (int j = 0; j < 3; ++j) ca.wn[k][j] = o[k]->wn[j];
+        }
+        ca.draw = (int32_t)(&d - (const DrawRec*)nullptr);   // patched by caller (see below)
+        clipAttrs[slot] = ca;
+        r.meta = 0x80000000u | slot;
+        uint32_t seq = 2u * gtri + (uint32_t)f;
+        recs[seq] = r;
+        int k = out.n++;
+        out.seq[k] = seq;
+        out.tx[k] = (uint32_t)(minX / kTile) | ((uint32_t)(maxX / kTile) << 16);
+        out.ty[k] = (uint32_t)ty0 | ((uint32_t)ty1 << 16);
+    }
+}
+
+}  // namespace srb
