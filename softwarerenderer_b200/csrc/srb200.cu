@@ -1,0 +1,687 @@
+// srb200.cu -- C ABI (include/srb200.h) over the sm_100a kernels.
+//
+// One SrbContext = one GPU, one CUDA stream, one framebuffer (or band of it).
+// srb_draw* only records commands; srb_end_frame uploads the draw table and
+// launches the whole pipeline asynchronously:
+//   frustum -> vertex -> setup(+count) -> scan -> fill -> [sort ->] tile raster.
+// There is no CPU fallback: without a CUDA device srb_create fails.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "srb_raster.cuh"
+
+using namespace srb;
+
+namespace {
+
+thread_local std::string g_createError;
+
+struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
+struct TexRes { uchar4* px = nullptr; int w = 0, h = 0; bool opaque = true, alive = false; };
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = n + n / 4 + 64;
+        cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct QueuedDraw { SrbDrawCmd cmd; int64_t order; };
+
+}  // namespace
+
+struct SrbContext {
+    int device = 0;
+    int W = 0, H = 0, tilesX = 0, tilesY = 0;
+    int band0 = 0, band1 = 0;
+    bool bandSet = false;
+    int pipeline = SRB_PIPELINE_AUTO;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float4* color = nullptr;
+    float* depth = nullptr;
+    std::vector<MeshRes> meshes;      // handle = index + 1
+    std::vector<TexRes> textures;
+    std::mutex mu;
+    SrbUniforms uniforms;
+    // frame recording
+    bool inFrame = false, haveFrame = false, framePending = false;
+    float clear[4] = {0, 0, 0, 1};
+    uint32_t clearFlags = 0;
+    std::vector<QueuedDraw> queue;
+    int64_t callCounter = 0;
+    // resident frame
+    FrameParams fp;
+    bool useVis = false;
+    int visMode = 0;
+    DevBuf<DrawRec> dDraws;
+    DevBuf<int32_t> dVbase, dTbase;
+    DevBuf<float4> dClip, dWn;
+    DevBuf<TriRec> dRecs;
+    DevBuf<TriRef> dRefs;
+    DevBuf<ClipAttr> dClipAttrs;
+    DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dBins, dBinScratch;
+    Counters* dCnt = nullptr;
+    Counters* hCnt = nullptr;         // pinned
+    DrawRec* hDraws = nullptr;        // pinned staging
+    int32_t* hBases = nullptr;        // pinned staging: vbase then tbase
+    size_t hDrawsCap = 0;
+    SrbStats stats;
+    std::string err;
+};
+
+namespace {
+
+int fail(SrbContext* c, int code, const std::string& msg) {
+    if (c) c->err = msg; else g_createError = msg;
+    return code;
+}
+#define CK(c, call)                                                                           \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail((c), SRB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+void default_uniforms(SrbUniforms& u) {
+    std::memset(&u, 0, sizeof(u));
+    // Renderer.cs:39-44 defaults; EulerToDirection(-45,-45,0) is supplied by the caller normally.
+    u.light_dir[0] = 0.5f; u.light_dir[1] = -0.70710677f; u.light_dir[2] = -0.5f;
+    for (int i = 0; i < 4; ++i) u.light_color[i] = 1.0f;
+    u.fog_color[0] = 1.0f; u.fog_color[1] = 0.62f; u.fog_color[2] = 0.5f; u.fog_color[3] = 1.0f;
+    u.fog_start = 1.0f; u.fog_end = 25.0f;
+    u.near_clip = 0.1f;
+    u.numerics_fma = 1;
+}
+
+int alloc_framebuffer(SrbContext* c, int w, int h) {
+    if (c->color) cudaFree(c->color);
+    if (c->depth) cudaFree(c->depth);
+    c->color = nullptr; c->depth = nullptr;
+    CK(c, cudaMalloc((void**)&c->color, (size_t)w * h * sizeof(float4)));
+    CK(c, cudaMalloc((void**)&c->depth, (size_t)w * h * sizeof(float)));
+    CK(c, cudaMemsetAsync(c->color, 0, (size_t)w * h * sizeof(float4), c->stream));
+    CK(c, cudaMemsetAsync(c->depth, 0, (size_t)w * h * sizeof(float), c->stream));
+    c->W = w; c->H = h;
+    c->tilesX = (w + kTile - 1) / kTile;
+    c->tilesY = (h + kTile - 1) / kTile;
+    if (!c->bandSet) { c->band0 = 0; c->band1 = c->tilesY; }
+    c->band0 = std::min(c->band0, c->tilesY);
+    c->band1 = std::min(c->band1, c->tilesY);
+    c->haveFrame = false;
+    return SRB_OK;
+}
+
+// Launch the whole pipeline for the resident draw list.
+int launch_frame(SrbContext* c) {
+    FrameParams& fp = c->fp;
+    const SrbUniforms U = c->uniforms;
+    const int nTiles = fp.tilesX * fp.tilesY;
+    const int bandTiles = (fp.bandRow1 - fp.bandRow0) * fp.tilesX;
+    int launches = 0;
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, cudaMemsetAsync(c->dCnt, 0, sizeof(Counters), c->stream));
+    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), c->stream));
+    if (fp.nDraws > 0) {
+        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt);
+        ++launches;
+    }
+    if (fp.totalV > 0) {
+        int grid = (fp.totalV + 255) / 256;
+        if (U.numerics_fma)
+            vertex_kernel<true><<<grid, 256, 0, c->stream>>>(c->dDraws.p, c->dVbase.p, fp, c->dClip.p, c->dWn.p);
+        else
+            vertex_kernel<false><<<grid, 256, 0, c->stream>>>(c->dDraws.p, c->dVbase.p, fp, c->dClip.p, c->dWn.p);
+        ++launches;
+    }
+    if (fp.totalT > 0) {
+        setup_kernel<<<(fp.totalT + 255) / 256, 256, 0, c->stream>>>(
+            c->dDraws.p, c->dTbase.p, fp, U, c->dClip.p, c->dWn.p, c->dRecs.p, c->dClipAttrs.p, c->dRefs.p,
+            c->dTileCount.p, c->dCnt);
+        ++launches;
+    }
+    scan_tiles_kernel<<<1, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, nTiles, c->dCnt, fp.pairCap);
+    ++launches;
+    if (fp.totalT > 0) {
+        // worst case two accepted triangles per submitted one (near-clip fan)
+        size_t maxRefs = 2 * (size_t)fp.totalT;
+        fill_bins_kernel<<<(unsigned)((maxRefs + 255) / 256), 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
+        ++launches;
+    }
+    RasterArgs A;
+    A.draws = c->dDraws.p; A.tbase = c->dTbase.p; A.wn = c->dWn.p; A.recs = c->dRecs.p;
+    A.clipAttrs = c->dClipAttrs.p; A.tileStart = c->dTileStart.p; A.tileEnd = c->dTileCursor.p;
+    A.bins = c->dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = c->dCnt;
+    if (bandTiles > 0) {
+        if (c->useVis) {
+            switch (c->visMode) {
+                case 0: vis_tile_kernel<0><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 1: vis_tile_kernel<1><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 2: vis_tile_kernel<2><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                default: vis_tile_kernel<3><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+            }
+            ++launches;
+        } else {
+            sort_bins_kernel<<<bandTiles, 256, 0, c->stream>>>(c->dTileStart.p, c->dTileCursor.p, c->dBins.p,
+                                                              c->dBinScratch.p, fp.bandRow0 * fp.tilesX, c->dCnt);
+            ordered_tile_kernel<<<bandTiles, 256, 0, c->stream>>>(A, fp, U);
+            launches += 2;
+        }
+    }
+    CK(c, cudaGetLastError());
+    CK(c, cudaMemcpyAsync(c->hCnt, c->dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->stats.kernel_launches = launches;
+    c->stats.pipeline_used = c->useVis ? SRB_PIPELINE_VISIBILITY : SRB_PIPELINE_ORDERED;
+    c->framePending = true;
+    return SRB_OK;
+}
+
+// Wait for the pending frame; if a device-side capacity overflowed, grow and re-run.
+int complete_frame(SrbContext* c) {
+    CK(c, cudaStreamSynchronize(c->stream));
+    if (!c->framePending) return SRB_OK;
+    for (int attempt = 0; attempt < 8; ++attempt) {
+        const Counters& k = *c->hCnt;
+        if (!k.overflow) break;
+        if (c->fp.loadColor || c->fp.loadDepth)
+            return fail(c, SRB_ERR_STATE, "bin overflow on a frame that preserves the framebuffer; cannot re-run");
+        if (k.overflow & 1u) {
+            size_t want = (size_t)k.nPairs + k.nPairs / 8 + 1024;
+            CK(c, c->dBins.reserve(want));
+            CK(c, c->dBinScratch.reserve(c->dBins.cap));
+            c->fp.pairCap = (uint32_t)std::min<size_t>(c->dBins.cap, 0xffffffffu);
+        }
+        if (k.overflow & 2u) {
+            size_t want = std::max<size_t>(4 * (size_t)k.nClipped, 4096);
+            CK(c, c->dClipAttrs.reserve(want));
+            c->fp.clipCap = (uint32_t)c->dClipAttrs.cap;
+        }
+        int rc = launch_frame(c);
+        if (rc != SRB_OK) return rc;
+        CK(c, cudaStreamSynchronize(c->stream));
+    }
+    if (c->hCnt->overflow) return fail(c, SRB_ERR_CUDA, "bin capacity overflow persisted after regrow");
+    c->framePending = false;
+    const Counters& k = *c->hCnt;
+    c->stats.draws_visible = k.nVisibleDraws;
+    c->stats.triangles_setup = k.nRefs;
+    c->stats.tile_pairs = k.nPairs;
+    c->stats.clipped_triangles = k.nClippedTris;
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.gpu_ms = ms;
+    return SRB_OK;
+}
+
+}  // namespace
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" {
+
+int srb_version(void) { return 100; }
+
+const char* srb_last_error(SrbContext* ctx) { return ctx ? ctx->err.c_str() : g_createError.c_str(); }
+
+int srb_create(int device, int width, int height, SrbContext** out_ctx) {
+    if (!out_ctx) return fail(nullptr, SRB_ERR_ARG, "out_ctx is null");
+    *out_ctx = nullptr;
+    if (width <= 0 || height <= 0)      // Rasterizer.InitializeTileLocks throws ArgumentException (:71-74)
+        return fail(nullptr, SRB_ERR_ARG, "Width and height must be positive non-zero values.");
+    if (width > 65535 || height > 65535) return fail(nullptr, SRB_ERR_ARG, "render target larger than 65535");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0)
+        return fail(nullptr, SRB_ERR_CUDA, std::string("no CUDA device (srb200 has no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(nullptr, SRB_ERR_ARG, "bad device index");
+    SrbContext* c = new SrbContext();
+    c->device = device;
+    std::memset(&c->stats, 0, sizeof(c->stats));
+    std::memset(&c->fp, 0, sizeof(c->fp));
+    default_uniforms(c->uniforms);
+    auto bail = [&](const char* what, cudaError_t err) {
+        g_createError = std::string(what) + ": " + cudaGetErrorString(err);
+        delete c;
+        return SRB_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaMalloc((void**)&c->dCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMallocHost((void**)&c->hCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMallocHost", e);
+    std::memset(c->hCnt, 0, sizeof(Counters));
+    int rc = alloc_framebuffer(c, width, height);
+    if (rc != SRB_OK) { g_createError = c->err; delete c; return rc; }
+    *out_ctx = c;
+    return SRB_OK;
+}
+
+int srb_destroy(SrbContext* c) {
+    if (!c) return SRB_ERR_ARG;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); }
+    for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
+    c->dDraws.release(); c->dVbase.release(); c->dTbase.release(); c->dClip.release(); c->dWn.release();
+    c->dRecs.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dTileCount.release();
+    c->dTileStart.release(); c->dTileCursor.release(); c->dBins.release(); c->dBinScratch.release();
+    if (c->color) cudaFree(c->color);
+    if (c->depth) cudaFree(c->depth);
+    if (c->dCnt) cudaFree(c->dCnt);
+    if (c->hCnt) cudaFreeHost(c->hCnt);
+    if (c->hDraws) cudaFreeHost(c->hDraws);
+    if (c->hBases) cudaFreeHost(c->hBases);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return SRB_OK;
+}
+
+int srb_resize(SrbContext* c, int width, int height) {
+    if (!c) return SRB_ERR_ARG;
+    if (width <= 0 || height <= 0) return fail(c, SRB_ERR_ARG, "Width and height must be positive non-zero values.");
+    if (width > 65535 || height > 65535) return fail(c, SRB_ERR_ARG, "render target larger than 65535");
+    if (c->inFrame) return fail(c, SRB_ERR_STATE, "resize inside a frame");
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    c->bandSet = false;
+    return alloc_framebuffer(c, width, height);
+}
+
+int srb_get_size(SrbContext* c, int* w, int* h) {
+    if (!c) return SRB_ERR_ARG;
+    if (w) *w = c->W;
+    if (h) *h = c->H;
+    return SRB_OK;
+}
+
+int srb_set_band(SrbContext* c, int r0, int r1) {
+    if (!c) return SRB_ERR_ARG;
+    if (r0 < 0 || r1 < r0 || r1 > c->tilesY) return fail(c, SRB_ERR_ARG, "band rows out of range");
+    c->band0 = r0; c->band1 = r1; c->bandSet = true;
+    return SRB_OK;
+}
+
+int srb_set_pipeline(SrbContext* c, int p) {
+    if (!c) return SRB_ERR_ARG;
+    if (p < 0 || p > 2) return fail(c, SRB_ERR_ARG, "bad pipeline");
+    c->pipeline = p;
+    return SRB_OK;
+}
+
+int srb_texture_create(SrbContext* c, const uint8_t* rgba8, int w, int h, SrbTexture* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    if (!rgba8 || w <= 0 || h <= 0) return fail(c, SRB_ERR_ARG, "bad texture");
+    CK(c, cudaSetDevice(c->device));
+    TexRes t;
+    t.w = w; t.h = h;
+    size_t n = (size_t)w * h;
+    t.opaque = true;
+    for (size_t i = 0; i < n; ++i) if (rgba8[4 * i + 3] != 255) { t.opaque = false; break; }
+    CK(c, cudaMalloc((void**)&t.px, n * 4));
+    CK(c, cudaMemcpy(t.px, rgba8, n * 4, cudaMemcpyHostToDevice));
+    t.alive = true;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->textures.push_back(t);
+    *out = (SrbTexture)c->textures.size();
+    return SRB_OK;
+}
+
+int srb_texture_destroy(SrbContext* c, SrbTexture tex) {
+    if (!c) return SRB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (tex <= 0 || (size_t)tex > c->textures.size() || !c->textures[tex - 1].alive)
+        return fail(c, SRB_ERR_HANDLE, "unknown texture handle");
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(c->textures[tex - 1].px);
+    c->textures[tex - 1] = TexRes();
+    c->haveFrame = false;
+    return SRB_OK;
+}
+
+int srb_mesh_create(SrbContext* c, const float* vertices, int nV, const uint16_t* indices, int nI, SrbMesh* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    if (!vertices || !indices || nV <= 0 || nI < 0) return fail(c, SRB_ERR_ARG, "bad mesh arrays");
+    if (nV > 65536) return fail(c, SRB_ERR_ARG, "mesh exceeds ushort index range (ModelLoader.cs:47)");
+    for (int i = 0; i < nI; ++i)
+        if (indices[i] >= nV) return fail(c, SRB_ERR_ARG, "index out of range (IndexOutOfRangeException in the reference)");
+    CK(c, cudaSetDevice(c->device));
+    MeshRes m;
+    m.nV = nV; m.nI = nI;
+    m.opaque = true;
+    for (int i = 0; i < nV; ++i) if (vertices[12 * i + 11] != 1.0f) { m.opaque = false; break; }
+    CK(c, cudaMalloc((void**)&m.vtx, (size_t)nV * 48));
+    CK(c, cudaMalloc((void**)&m.idx, std::max<size_t>((size_t)nI * 2, 16)));
+    CK(c, cudaMemcpy(m.vtx, vertices, (size_t)nV * 48, cudaMemcpyHostToDevice));
+    if (nI > 0) CK(c, cudaMemcpy(m.idx, indices, (size_t)nI * 2, cudaMemcpyHostToDevice));
+    m.alive = true;
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->meshes.push_back(m);
+    *out = (SrbMesh)c->meshes.size();
+    return SRB_OK;
+}
+
+int srb_mesh_destroy(SrbContext* c, SrbMesh mesh) {
+    if (!c) return SRB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (mesh <= 0 || (size_t)mesh > c->meshes.size() || !c->meshes[mesh - 1].alive)
+        return fail(c, SRB_ERR_HANDLE, "unknown mesh handle");
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(c->meshes[mesh - 1].vtx);
+    cudaFree(c->meshes[mesh - 1].idx);
+    c->meshes[mesh - 1] = MeshRes();
+    c->haveFrame = false;
+    return SRB_OK;
+}
+
+int srb_set_uniforms(SrbContext* c, const SrbUniforms* u) {
+    if (!c || !u) return SRB_ERR_ARG;
+    if (u->n_extra_lights < 0 || u->n_extra_lights > 4) return fail(c, SRB_ERR_ARG, "n_extra_lights must be 0..4");
+    if (u->tex_filter < 0 || u->tex_filter > 1) return fail(c, SRB_ERR_ARG, "tex_filter must be 0 or 1");
+    c->uniforms = *u;
+    return SRB_OK;
+}
+
+int srb_begin_frame(SrbContext* c, const float clear_rgba[4], uint32_t clear_flags) {
+    if (!c) return SRB_ERR_ARG;
+    if (c->inFrame) return fail(c, SRB_ERR_STATE, "begin_frame inside a frame");
+    if ((clear_flags & SRB_CLEAR_COLOR) && !clear_rgba) return fail(c, SRB_ERR_ARG, "clear colour missing");
+    if (clear_rgba) std::memcpy(c->clear, clear_rgba, sizeof(c->clear));
+    c->clearFlags = clear_flags;
+    c->queue.clear();
+    c->callCounter = 0;
+    c->inFrame = true;
+    return SRB_OK;
+}
+
+static int queue_draw(SrbContext* c, const SrbDrawCmd& cmd) {
+    if (cmd.mesh <= 0 || (size_t)cmd.mesh > c->meshes.size() || !c->meshes[cmd.mesh - 1].alive)
+        return fail(c, SRB_ERR_HANDLE, "unknown mesh handle");
+    if (cmd.texture < 0 || (size_t)cmd.texture > c->textures.size() ||
+        (cmd.texture > 0 && !c->textures[cmd.texture - 1].alive))
+        return fail(c, SRB_ERR_HANDLE, "unknown texture handle");
+    if (cmd.cull < 0 || cmd.cull > 2 || cmd.depth_test < 0 || cmd.depth_test > 7 || cmd.blend < 0 || cmd.blend > 3)
+        return fail(c, SRB_ERR_ARG, "bad cull/depth/blend enum");
+    QueuedDraw q;
+    q.cmd = cmd;
+    q.order = cmd.submission_index >= 0 ? (int64_t)cmd.submission_index : (int64_t)0x40000000 + c->callCounter;
+    ++c->callCounter;
+    c->queue.push_back(q);
+    return SRB_OK;
+}
+
+int srb_draw(SrbContext* c, SrbMesh mesh, const float model[16], const float view[16], const float proj[16],
+             SrbTexture tex, int cull, int depth_test, int blend, int submission_index) {
+    if (!c || !model || !view || !proj) return SRB_ERR_ARG;
+    SrbDrawCmd cmd;
+    std::memset(&cmd, 0, sizeof(cmd));
+    cmd.mesh = mesh; cmd.texture = tex;
+    std::memcpy(cmd.model, model, 64); std::memcpy(cmd.view, view, 64); std::memcpy(cmd.proj, proj, 64);
+    cmd.cull = cull; cmd.depth_test = depth_test; cmd.blend = blend;
+    cmd.submission_index = submission_index;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->inFrame) return fail(c, SRB_ERR_STATE, "draw outside begin/end frame");
+    return queue_draw(c, cmd);
+}
+
+int srb_submit_draws(SrbContext* c, const SrbDrawCmd* cmds, int n) {
+    if (!c || (!cmds && n > 0) || n < 0) return SRB_ERR_ARG;
+    std::lock_guard<std::mutex> lk(c->mu);
+    if (!c->inFrame) return fail(c, SRB_ERR_STATE, "draw outside begin/end frame");
+    c->queue.reserve(c->queue.size() + n);
+    for (int i = 0; i < n; ++i) {
+        int rc = queue_draw(c, cmds[i]);
+        if (rc != SRB_OK) return rc;
+    }
+    return SRB_OK;
+}
+
+int srb_end_frame(SrbContext* c) {
+    if (!c) return SRB_ERR_ARG;
+    if (!c->inFrame) return fail(c, SRB_ERR_STATE, "end_frame without begin_frame");
+    c->inFrame = false;
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);          // previous frame's staging buffers are reused below
+    if (rc != SRB_OK) return rc;
+    std::stable_sort(c->queue.begin(), c->queue.end(),
+                     [](const QueuedDraw& a, const QueuedDraw& b) { return a.order < b.order; });
+    const int nDraws = (int)c->queue.size();
+    if ((size_t)nDraws + 1 > c->hDrawsCap) {
+        if (c->hDraws) cudaFreeHost(c->hDraws);
+        if (c->hBases) cudaFreeHost(c->hBases);
+        c->hDraws = nullptr; c->hBases = nullptr;
+        size_t cap = (size_t)nDraws + nDraws / 2 + 64;
+        CK(c, cudaMallocHost((void**)&c->hDraws, cap * sizeof(DrawRec)));
+        CK(c, cudaMallocHost((void**)&c->hBases, 2 * (cap + 1) * sizeof(int32_t)));
+        c->hDrawsCap = cap;
+    }
+    int32_t* hV = c->hBases;
+    int32_t* hT = c->hBases + (nDraws + 1);
+    int64_t totalV = 0, totalT = 0;
+    bool eligible = (c->clearFlags & SRB_CLEAR_COLOR) && (c->clearFlags & SRB_CLEAR_DEPTH);
+    int commonDepth = -1;
+    for (int i = 0; i < nDraws; ++i) {
+        const SrbDrawCmd& q = c->queue[i].cmd;
+        const MeshRes& m = c->meshes[q.mesh - 1];
+        DrawRec& d = c->hDraws[i];
+        std::memcpy(d.model, q.model, 64); std::memcpy(d.view, q.view, 64); std::memcpy(d.proj, q.proj, 64);
+        std::memcpy(d.sphere, q.sphere, 16);
+        d.vtx = m.vtx; d.idx = m.idx;
+        d.tex = nullptr; d.tex_w = d.tex_h = 0;
+        bool texOpaque = true;
+        if (q.texture > 0) {
+            const TexRes& t = c->textures[q.texture - 1];
+            d.tex = t.px; d.tex_w = t.w; d.tex_h = t.h;
+            texOpaque = t.opaque;
+        }
+        d.n_vertices = m.nV; d.n_triangles = m.nI / 3;
+        d.vbase = (int32_t)totalV; d.tbase = (int32_t)totalT;
+        d.cull = q.cull; d.depth_test = q.depth_test; d.blend = q.blend;
+        d.flags = q.flags; d.visible = 1; d._pad = 0;
+        hV[i] = (int32_t)totalV; hT[i] = (int32_t)totalT;
+        totalV += m.nV; totalT += m.nI / 3;
+        // Visibility path eligibility: extreme-depth winner with
+        // alpha provably 1, one depth function for the whole frame.
+        if (q.depth_test < SRB_DEPTH_LESS || q.depth_test > SRB_DEPTH_GREATER_EQUAL) eligible = false;
+        if (commonDepth < 0) commonDepth = q.depth_test; else if (commonDepth != q.depth_test) eligible = false;
+        if (q.blend != SRB_BLEND_ALPHA && q.blend != SRB_BLEND_NONE) eligible = false;
+        if (!m.opaque || !texOpaque) eligible = false;
+    }
+    hV[nDraws] = (int32_t)totalV; hT[nDraws] = (int32_t)totalT;
+    if (totalV > 0x3fffffff || totalT > 0x3fffffff) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
+    if (c->pipeline == SRB_PIPELINE_ORDERED) eligible = false;
+    if (c->pipeline == SRB_PIPELINE_VISIBILITY && !eligible && nDraws > 0)
+        return fail(c, SRB_ERR_STATE, "frame is not eligible for the visibility pipeline");
+    c->useVis = eligible || nDraws == 0;
+    if (!((c->clearFlags & SRB_CLEAR_COLOR) && (c->clearFlags & SRB_CLEAR_DEPTH))) c->useVis = false;
+    switch (commonDepth) {
+        case SRB_DEPTH_LESS: c->visMode = 1; break;
+        case SRB_DEPTH_GREATER_EQUAL: c->visMode = 2; break;
+        case SRB_DEPTH_GREATER: c->visMode = 3; break;
+        default: c->visMode = 0; break;
+    }
+    const int nTiles = c->tilesX * c->tilesY;
+    CK(c, c->dDraws.reserve((size_t)nDraws + 1));
+    CK(c, c->dVbase.reserve((size_t)nDraws + 1));
+    CK(c, c->dTbase.reserve((size_t)nDraws + 1));
+    CK(c, c->dClip.reserve((size_t)totalV + 1));
+    CK(c, c->dWn.reserve((size_t)totalV + 1));
+    CK(c, c->dRecs.reserve(2 * (size_t)totalT + 2));
+    CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
+    CK(c, c->dClipAttrs.reserve(4096));
+    CK(c, c->dTileCount.reserve(nTiles));
+    CK(c, c->dTileStart.reserve(nTiles));
+    CK(c, c->dTileCursor.reserve(nTiles));
+    CK(c, c->dBins.reserve(std::max<size_t>(1u << 20, 3 * (size_t)totalT)));
+    CK(c, c->dBinScratch.reserve(c->dBins.cap));
+    if (nDraws > 0) {
+        CK(c, cudaMemcpyAsync(c->dDraws.p, c->hDraws, (size_t)nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, c->stream));
+    }
+    CK(c, cudaMemcpyAsync(c->dVbase.p, hV, ((size_t)nDraws + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(c, cudaMemcpyAsync(c->dTbase.p, hT, ((size_t)nDraws + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    FrameParams& fp = c->fp;
+    fp.W = c->W; fp.H = c->H; fp.tilesX = c->tilesX; fp.tilesY = c->tilesY;
+    fp.bandRow0 = c->band0; fp.bandRow1 = c->band1;
+    fp.nDraws = nDraws; fp.totalV = (int)totalV; fp.totalT = (int)totalT;
+    fp.pairCap = (uint32_t)std::min<size_t>(c->dBins.cap, 0xffffffffu);
+    fp.clipCap = (uint32_t)c->dClipAttrs.cap;
+    std::memcpy(fp.clearColor, c->clear, 16);
+    fp.loadColor = (c->clearFlags & SRB_CLEAR_COLOR) ? 0 : 1;
+    fp.loadDepth = (c->clearFlags & SRB_CLEAR_DEPTH) ? 0 : 1;
+    fp.depthMode = commonDepth;
+    c->stats.draws_submitted = nDraws;
+    c->stats.triangles_submitted = totalT;
+    c->haveFrame = true;
+    return launch_frame(c);
+}
+
+int srb_replay_frame(SrbContext* c) {
+    if (!c) return SRB_ERR_ARG;
+    if (!c->haveFrame || c->inFrame) return fail(c, SRB_ERR_STATE, "no resident frame to replay");
+    if (c->fp.loadColor || c->fp.loadDepth) return fail(c, SRB_ERR_STATE, "cannot replay a frame that preserves the framebuffer");
+    CK(c, cudaSetDevice(c->device));
+    if (c->framePending && c->hCnt->overflow) {       // conservative: settle capacities first
+        int rc = complete_frame(c);
+        if (rc != SRB_OK) return rc;
+    }
+    return launch_frame(c);
+}
+
+int srb_sync(SrbContext* c) {
+    if (!c) return SRB_ERR_ARG;
+    CK(c, cudaSetDevice(c->device));
+    return complete_frame(c);
+}
+
+int srb_read_color_rows(SrbContext* c, float* out, int y0, int y1) {
+    if (!c || !out) return SRB_ERR_ARG;
+    if (y0 < 0 || y1 < y0 || y1 > c->H) return fail(c, SRB_ERR_ARG, "row range out of bounds");
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    size_t off = (size_t)y0 * c->W, n = (size_t)(y1 - y0) * c->W;
+    CK(c, cudaMemcpyAsync(out, c->color + off, n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return SRB_OK;
+}
+
+int srb_read_color(SrbContext* c, float* out) { return c ? srb_read_color_rows(c, out, 0, c->H) : SRB_ERR_ARG; }
+
+int srb_read_depth(SrbContext* c, float* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpyAsync(out, c->depth, (size_t)c->W * c->H * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return SRB_OK;
+}
+
+static int pixel_index(SrbContext* c, int x, int y, size_t* idx) {
+    if (x < 0 || x >= c->W || y < 0 || y >= c->H) return 0;     // accessors ignore out-of-range (MainWindow.cs:384,392)
+    *idx = (size_t)y * c->W + x;
+    return 1;
+}
+int srb_get_pixel(SrbContext* c, int x, int y, float out[4]) {
+    if (!c || !out) return SRB_ERR_ARG;
+    size_t i;
+    if (!pixel_index(c, x, y, &i)) { out[0] = out[1] = out[2] = out[3] = 0.0f; return SRB_OK; }   // Vector4.Zero (:397)
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpy(out, c->color + i, 16, cudaMemcpyDeviceToHost));
+    return SRB_OK;
+}
+int srb_set_pixel(SrbContext* c, int x, int y, const float rgba[4]) {
+    if (!c || !rgba) return SRB_ERR_ARG;
+    size_t i;
+    if (!pixel_index(c, x, y, &i)) return SRB_OK;
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpy(c->color + i, rgba, 16, cudaMemcpyHostToDevice));
+    return SRB_OK;
+}
+int srb_get_depth(SrbContext* c, int x, int y, float* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    size_t i;
+    if (!pixel_index(c, x, y, &i)) { *out = kClearDepth; return SRB_OK; }     // float.MinValue (:426)
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpy(out, c->depth + i, 4, cudaMemcpyDeviceToHost));
+    return SRB_OK;
+}
+int srb_set_depth(SrbContext* c, int x, int y, float depth) {
+    if (!c) return SRB_ERR_ARG;
+    size_t i;
+    if (!pixel_index(c, x, y, &i)) return SRB_OK;
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpy(c->depth + i, &depth, 4, cudaMemcpyHostToDevice));
+    return SRB_OK;
+}
+
+int srb_read_color_rgba8(SrbContext* c, uint8_t* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    size_t n = (size_t)c->W * c->H;
+    CK(c, c->dBinScratch.reserve(n));            // reuse scratch: 4 B per pixel
+    pack_rgba8_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->color, (uchar4*)c->dBinScratch.p, n);
+    CK(c, cudaGetLastError());
+    CK(c, cudaMemcpyAsync(out, c->dBinScratch.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return SRB_OK;
+}
+
+int srb_frustum_test(SrbContext* c, const float* spheres, const float* models, const float view[16],
+                     const float proj[16], int n, int32_t* out_visible) {
+    if (!c || !spheres || !models || !view || !proj || !out_visible || n < 0) return SRB_ERR_ARG;
+    if (n == 0) return SRB_OK;
+    CK(c, cudaSetDevice(c->device));
+    float* d = nullptr;
+    size_t fl = (size_t)n * 20 + 32;
+    CK(c, cudaMalloc((void**)&d, fl * sizeof(float) + (size_t)n * sizeof(int32_t)));
+    float* dS = d; float* dM = d + (size_t)n * 4; float* dVP = dM + (size_t)n * 16;
+    int32_t* dOut = (int32_t*)(dVP + 32);
+    cudaError_t e = cudaMemcpyAsync(dS, spheres, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dM, models, (size_t)n * 64, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dVP, view, 64, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dVP + 16, proj, 64, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        frustum_batch_kernel<<<(n + 127) / 128, 128, 0, c->stream>>>(dS, dM, dVP, n, c->uniforms.numerics_fma, dOut);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_visible, dOut, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(c, SRB_ERR_CUDA, std::string("srb_frustum_test: ") + cudaGetErrorString(e));
+    return SRB_OK;
+}
+
+void* srb_device_color_ptr(SrbContext* c) { return c ? (void*)c->color : nullptr; }
+void* srb_device_depth_ptr(SrbContext* c) { return c ? (void*)c->depth : nullptr; }
+void* srb_stream(SrbContext* c) { return c ? (void*)c->stream : nullptr; }
+
+int srb_get_stats(SrbContext* c, SrbStats* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    *out = c->stats;
+    return SRB_OK;
+}
+
+}  // extern "C"

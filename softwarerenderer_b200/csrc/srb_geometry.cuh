@@ -183,7 +183,7 @@ struct SetupOut {
 };
 
 // Near-clipped triangle (Rasterizer.cs:95-160, 217-224).  Rare and divergent.
-__device__ __noinline__ void setup_clipped(const DrawRec& d, int vbase, const int i3[3],
+__device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int vbase, const int i3[3],
                                            const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
                                            const FrameParams& fp, const SrbUniforms& U, uint32_t gtri,
                                            TriRec* recs, ClipAttr* clipAttrs, Counters* cnt, SetupOut& out) {
@@ -193,7 +193,7 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int vbase, const in
     for (int k = 0; k < 3; ++k) {
         int vi = i3[k];
         float4 a = __ldg(d.vtx + 3 * vi), b = __ldg(d.vtx + 3 * vi + 1), c = __ldg(d.vtx + 3 * vi + 2);
-        float4 wn = clipIn == nullptr ? make_float4(0, 0, 0, 0) : wnIn[vbase + vi];
+        float4 wn = wnIn[vbase + vi];
         v[k].clip = clipIn[vbase + vi];
         v[k].uv[0] = a.w; v[k].uv[1] = b.x;
         v[k].col[0] = c.x; v[k].col[1] = c.y; v[k].col[2] = c.z; v[k].col[3] = c.w;
@@ -243,7 +243,7 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int vbase, const in
 #pragma unroll
             for (int j = 0; j < 3; ++j) ca.wn[k][j] = o[k]->wn[j];
         }
-        ca.draw = (int32_t)(&d - (const DrawRec*)nullptr);   // patched by caller (see below)
+        ca.draw = drawIndex;
         clipAttrs[slot] = ca;
         r.meta = 0x80000000u | slot;
         uint32_t seq = 2u * gtri + (uint32_t)f;

@@ -1,0 +1,308 @@
+// srb_raster.cuh -- the two tile rasterizers.
+//
+//  * ordered_tile_kernel: exact submission-order semantics for ANY state
+//    (all depth tests, all blend modes, alpha <= 0 discards, BlendMode.None
+//    row break).  One CTA per 16x16 tile, one thread per pixel, bin sorted by
+//    submission sequence, colour+depth of the pixel live in registers.
+//  * vis_tile_kernel: the fast path for frames whose result is provably
+//    order-independent: per-pixel winner = extreme depth, ties
+//    by submission order, kept as a 64-bit key in shared memory; coverage is
+//    walked by (triangle,row) work items; the winner is shaded once and the
+//    tile is written with 128-bit stores.  The clear is fused into tile init.
+#pragma once
+#include "srb_shade.cuh"
+
+namespace srb {
+
+__device__ __forceinline__ TriRec load_rec(const TriRec* p) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    TriRec r;
+    r.s0x = a.x; r.s0y = a.y; r.s1x = a.z; r.s1y = a.w;
+    r.s2x = b.x; r.s2y = b.y; r.d0 = b.z; r.d1 = b.w;
+    r.d2 = c.x; r.cz0 = c.y; r.cz1 = c.z; r.cz2 = c.w;
+    r.cw0 = d.x; r.cw1 = d.y; r.cw2 = d.z; r.meta = __float_as_uint(d.w);
+    return r;
+}
+
+// Edge values at pixel (x,y) of the tile whose clipped bbox starts at
+// (startX,startY): direct formula at the start pixel, then dy rounded adds of
+// b and dx rounded adds of a -- the reference's accumulation order
+// (Rasterizer.cs:481-483, 527-534).
+__device__ __forceinline__ void edge_chain(const TriRec& r, const TriEq& e, int startX, int startY, int x, int y,
+                                           float& w0, float& w1, float& w2) {
+    row_base(r, e, startX, startY, w0, w1, w2);
+    for (int i = startY; i < y; ++i) { w0 = add(w0, e.b12); w1 = add(w1, e.b20); w2 = add(w2, e.b01); }
+    for (int i = startX; i < x; ++i) { w0 = add(w0, e.a12); w1 = add(w1, e.a20); w2 = add(w2, e.a01); }
+}
+
+// ---------------------------------------------------------------------------
+// Bin sort by submission sequence (ordered path only).
+// ---------------------------------------------------------------------------
+constexpr int kSortSmem = 4096;
+__global__ void __launch_bounds__(256)
+sort_bins_kernel(const uint32_t* __restrict__ tileStart, const uint32_t* __restrict__ tileEnd,
+                 uint32_t* __restrict__ bins, uint32_t* __restrict__ scratch, int tileBase,
+                 const Counters* __restrict__ cnt) {
+    __shared__ uint32_t sm[kSortSmem];
+    if (cnt->overflow) return;
+    int tile = tileBase + blockIdx.x;
+    uint32_t s = tileStart[tile], e = tileEnd[tile];
+    int n = (int)(e - s);
+    if (n <= 1) return;
+    uint32_t* b = bins + s;
+    if (n <= kSortSmem) {
+        int P = 1;
+        while (P < n) P <<= 1;
+        for (int i = threadIdx.x; i < P; i += blockDim.x) sm[i] = i < n ? b[i] : 0xffffffffu;
+        __syncthreads();
+        for (int k = 2; k <= P; k <<= 1) {
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = threadIdx.x; i < P; i += blockDim.x) {
+                    int ixj = i ^ j;
+                    if (ixj > i) {
+                        uint32_t a = sm[i], c = sm[ixj];
+                        bool up = (i & k) == 0;
+                        if ((a > c) == up) { sm[i] = c; sm[ixj] = a; }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        for (int i = threadIdx.x; i < n; i += blockDim.x) b[i] = sm[i];
+    } else {
+        // Rank sort through a scratch copy (sequence ids are unique).
+        uint32_t* t = scratch + s;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) t[i] = b[i];
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            uint32_t v = t[i];
+            int rank = 0;
+            for (int j = 0; j < n; ++j) rank += t[j] < v;
+            b[rank] = v;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Ordered tile rasterizer: pixel loops of RasterizeTriangle (Rasterizer.cs:
+// 466-536) replayed per pixel in submission order.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
+    const unsigned full = 0xffffffffu;
+    if (A.cnt->overflow) return;
+    const int tile = fp.bandRow0 * fp.tilesX + blockIdx.x;
+    const int tX = tile % fp.tilesX, tY = tile / fp.tilesX;
+    const int tx0 = tX * kTile, ty0 = tY * kTile;
+    const int px = threadIdx.x & 15, py = threadIdx.x >> 4;
+    const int x = tx0 + px, y = ty0 + py;
+    const bool inb = x < fp.W && y < fp.H;
+    const size_t pidx = (size_t)y * fp.W + x;
+    float4 col = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
+    float dep = kClearDepth;
+    if (inb && fp.loadColor) col = A.color[pidx];
+    if (inb && fp.loadDepth) dep = A.depth[pidx];
+    const int tileEndX = min(tx0 + kTile - 1, fp.W - 1), tileEndY = min(ty0 + kTile - 1, fp.H - 1);
+    const uint32_t bs = A.tileStart[tile], be = A.tileEnd[tile];
+    for (uint32_t ei = bs; ei < be; ++ei) {
+        const uint32_t seq = __ldg(A.bins + ei);
+        const TriRec r = load_rec(A.recs + seq);
+        const TriEq e = tri_eq(r, fp.W, fp.H);
+        const int startX = max(e.minX, tx0), endX = min(e.maxX, tileEndX);
+        const int startY = max(e.minY, ty0), endY = min(e.maxY, tileEndY);
+        if (startX > endX || startY > endY) continue;            // uniform over the CTA
+        const int di = (r.meta & 0x80000000u) ? A.clipAttrs[r.meta & 0x7fffffffu].draw : (int)r.meta;
+        const int depthTest = A.draws[di].depth_test, blendMode = A.draws[di].blend;
+        bool pass = false, writeOk = false;
+        float depth = 0.0f;
+        float4 c = make_float4(0, 0, 0, 0);
+        if (inb && x >= startX && x <= endX && y >= startY && y <= endY) {
+            float w0, w1, w2;
+            edge_chain(r, e, startX, startY, x, y, w0, w1, w2);
+            if (inside3(w0, w1, w2)) {
+                float w0f, w1f, w2f;
+                depth = frag_depth(r.d0, r.d1, r.d2, e.invArea, w0, w1, w2, w0f, w1f, w2f);
+                if (depth_pass(depthTest, depth, dep)) {
+                    pass = true;
+                    int dtmp;
+                    c = shade_fragment(A, fp, U, r, seq, w0f, w1f, w2f, dtmp);
+                    writeOk = c.w > 0.0f;                                      // :511
+                }
+            }
+        }
+        // BlendMode.None: the first depth-passing fragment of a tile row with
+        // alpha <= 0 (or NaN) ends that row for this triangle (:520-523).
+        bool skipped = false;
+        if (blendMode == SRB_BLEND_NONE) {
+            unsigned brk = __ballot_sync(full, pass && !writeOk);
+            unsigned rowBits = (brk >> (16 * ((threadIdx.x & 31) >> 4))) & 0xffffu;
+            if (rowBits) skipped = px > (__ffs(rowBits) - 1);
+        }
+        if (pass && writeOk && !skipped) {
+            col = blend_px(c, col, blendMode);
+            if (depthTest != SRB_DEPTH_DISABLED) dep = depth;
+        }
+    }
+    if (inb) {
+        A.color[pidx] = col;
+        A.depth[pidx] = dep;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Visibility tile rasterizer.
+// MODE: 0 LessEqual (max depth, later wins ties), 1 Less (max, earlier wins),
+//       2 GreaterEqual (min, later wins), 3 Greater (min, earlier wins).
+// ---------------------------------------------------------------------------
+template <int MODE>
+__device__ __forceinline__ unsigned long long make_key(float depth, uint32_t seq) {
+    uint32_t hi = f2ord(depth);
+    if (MODE >= 2) hi = ~hi;
+    uint32_t lo = (MODE & 1) ? (0xfffffffeu - seq) : (seq + 1u);
+    return ((unsigned long long)hi << 32) | lo;
+}
+template <int MODE>
+__device__ __forceinline__ unsigned long long clear_key() {
+    uint32_t hi = f2ord(kClearDepth);
+    if (MODE >= 2) hi = ~hi;
+    uint32_t lo = (MODE & 1) ? 0xffffffffu : 0u;
+    return ((unsigned long long)hi << 32) | lo;
+}
+
+constexpr int kVisThreads = 128;
+constexpr int kVisWarps = kVisThreads / 32;
+constexpr int kVisFields = 15;
+
+template <int MODE>
+__global__ void __launch_bounds__(kVisThreads)
+vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
+    __shared__ unsigned long long keys[kTile * kTile];
+    __shared__ float soa[kVisWarps][kVisFields][32];
+    const unsigned full = 0xffffffffu;
+    if (A.cnt->overflow) return;
+    const int tile = fp.bandRow0 * fp.tilesX + blockIdx.x;
+    const int tX = tile % fp.tilesX, tY = tile / fp.tilesX;
+    const int tx0 = tX * kTile, ty0 = tY * kTile;
+    const int tileEndX = min(tx0 + kTile - 1, fp.W - 1), tileEndY = min(ty0 + kTile - 1, fp.H - 1);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned long long ckey = clear_key<MODE>();
+    for (int i = threadIdx.x; i < kTile * kTile; i += kVisThreads) keys[i] = ckey;
+    __syncthreads();
+
+    const uint32_t bs = A.tileStart[tile], be = A.tileEnd[tile];
+    float (*S)[32] = soa[wid];
+    for (uint32_t cb = bs + 32u * wid; cb < be; cb += 32u * kVisWarps) {
+        // ---- one triangle per lane: derive its raster constants for this tile ----
+        const bool valid = cb + lane < be;
+        int nrows = 0;
+        if (valid) {
+            const uint32_t seq = __ldg(A.bins + cb + lane);
+            const TriRec r = load_rec(A.recs + seq);
+            const TriEq e = tri_eq(r, fp.W, fp.H);
+            const int startX = max(e.minX, tx0), endX = min(e.maxX, tileEndX);
+            const int startY = max(e.minY, ty0), endY = min(e.maxY, tileEndY);
+            if (startX <= endX && startY <= endY) {
+                nrows = endY - startY + 1;
+                float w0, w1, w2;
+                row_base(r, e, startX, startY, w0, w1, w2);
+                S[0][lane] = w0; S[1][lane] = w1; S[2][lane] = w2;
+                S[3][lane] = e.a12; S[4][lane] = e.a20; S[5][lane] = e.a01;
+                S[6][lane] = e.b12; S[7][lane] = e.b20; S[8][lane] = e.b01;
+                S[9][lane] = e.invArea;
+                S[10][lane] = r.d0; S[11][lane] = r.d1; S[12][lane] = r.d2;
+                S[13][lane] = __uint_as_float((uint32_t)(startX - tx0) | ((uint32_t)(endX - tx0) << 8) |
+                                              ((uint32_t)(startY - ty0) << 16));
+                S[14][lane] = __uint_as_float(seq);
+            }
+        }
+        int incl = nrows;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(full, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const int excl = incl - nrows;
+        const int total = __shfl_sync(full, incl, 31);
+        __syncwarp();
+        // ---- (triangle,row) work items, 32 at a time ----
+        for (int ib = 0; ib < total; ib += 32) {
+            const int i = ib + lane;
+            int j = 0, ej = 0;
+#pragma unroll
+            for (int s = 16; s > 0; s >>= 1) {
+                int cand = j + s;
+                int v = __shfl_sync(full, excl, cand & 31);
+                if (cand < 32 && v <= i) { j = cand; ej = v; }
+            }
+            if (i < total) {
+                const int dy = i - ej;
+                float w0 = S[0][j], w1 = S[1][j], w2 = S[2][j];
+                const float a12 = S[3][j], a20 = S[4][j], a01 = S[5][j];
+                const float b12 = S[6][j], b20 = S[7][j], b01 = S[8][j];
+                const float invArea = S[9][j], d0 = S[10][j], d1 = S[11][j], d2 = S[12][j];
+                const uint32_t pk = __float_as_uint(S[13][j]);
+                const uint32_t seq = __float_as_uint(S[14][j]);
+                const int sx = pk & 0xff, ex = (pk >> 8) & 0xff, row = (int)(pk >> 16) + dy;
+                for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
+                unsigned long long* krow = keys + row * kTile;
+                for (int xx = sx; xx <= ex; ++xx) {
+                    if (inside3(w0, w1, w2)) {
+                        float w0f, w1f, w2f;
+                        float depth = frag_depth(d0, d1, d2, invArea, w0, w1, w2, w0f, w1f, w2f);
+                        if (depth == depth) {                       // NaN never passes a depth test
+                            unsigned long long key = make_key<MODE>(depth, seq);
+                            if (key > krow[xx]) atomicMax(krow + xx, key);
+                        }
+                    }
+                    w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
+                }
+            }
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- resolve: shade each pixel's winner once, write colour + depth ----
+    const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
+    for (int p = threadIdx.x; p < kTile * kTile; p += kVisThreads) {
+        const int px = p & 15, py = p >> 4;
+        const int x = tx0 + px, y = ty0 + py;
+        if (x >= fp.W || y >= fp.H) continue;
+        const unsigned long long key = keys[p];
+        float4 outc = clearCol;
+        float outd = kClearDepth;
+        if (key != ckey) {
+            uint32_t lo = (uint32_t)key, hi = (uint32_t)(key >> 32);
+            const uint32_t seq = (MODE & 1) ? (0xfffffffeu - lo) : (lo - 1u);
+            if (MODE >= 2) hi = ~hi;
+            const TriRec r = load_rec(A.recs + seq);
+            const TriEq e = tri_eq(r, fp.W, fp.H);
+            const int startX = max(e.minX, tx0), startY = max(e.minY, ty0);
+            float w0, w1, w2, w0f, w1f, w2f;
+            edge_chain(r, e, startX, startY, x, y, w0, w1, w2);
+            frag_depth(r.d0, r.d1, r.d2, e.invArea, w0, w1, w2, w0f, w1f, w2f);
+            int di;
+            float4 c = shade_fragment(A, fp, U, r, seq, w0f, w1f, w2f, di);
+            // Eligibility guarantees alpha > 0 and alpha == 1 up to rounding, so
+            // the blend destination is immaterial at 8 bits; use the clear colour.
+            outc = blend_px(c, clearCol, A.draws[di].blend);
+            outd = ord2f(hi);
+        }
+        const size_t pidx = (size_t)y * fp.W + x;
+        A.color[pidx] = outc;
+        A.depth[pidx] = outd;
+    }
+}
+
+// Present-format step (MainWindow.cs:234-250 converts the float buffer for the
+// GL upload): float4 -> RGBA8, clamp to [0,1], round to nearest.
+__global__ void pack_rgba8_kernel(const float4* __restrict__ color, uchar4* __restrict__ out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 c = color[i];
+    auto q = [](float v) { v = fminf(fmaxf(v, 0.0f), 1.0f); return (unsigned char)__float2int_rn(v * 255.0f); };
+    out[i] = make_uchar4(q(c.x), q(c.y), q(c.z), q(c.w));
+}
+
+}  // namespace srb

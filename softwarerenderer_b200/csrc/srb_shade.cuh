@@ -1,0 +1,138 @@
+// srb_shade.cuh -- per-fragment work: attribute fetch, Rasterizer.Interpolate /
+// InterpolateData, Renderer.FragmentShader, Texture.Sample.
+#pragma once
+#include "srb_binning.cuh"
+
+namespace srb {
+
+// Everything the tile kernels need to reach per-frame data.
+struct RasterArgs {
+    const DrawRec* draws;
+    const int32_t* tbase;
+    const float4* wn;             // world normals from vertex_kernel
+    const TriRec* recs;
+    const ClipAttr* clipAttrs;
+    const uint32_t* tileStart;
+    const uint32_t* tileEnd;      // == tileCursor after the fill pass
+    uint32_t* bins;
+    float4* color;
+    float* depth;
+    const Counters* cnt;          // kernels bail out when a capacity overflowed (frame is re-run)
+};
+
+// Texture.Sample (Texture.cs:42-63): nearest, repeat.
+__device__ __forceinline__ float4 tex_nearest(const uchar4* tex, int tw, int th, float uu, float vv) {
+    float u = sub(uu, (float)sat_int(uu));
+    float v = sub(vv, (float)sat_int(vv));
+    u = add(u, (u < 0.0f) ? 1.0f : 0.0f);
+    v = add(v, (v < 0.0f) ? 1.0f : 0.0f);
+    int x = sat_int(mul(u, (float)tw)) % tw;
+    int y = sat_int(mul(v, (float)th)) % th;
+    if (x < 0) x += tw;
+    if (y < 0) y += th;
+    uchar4 p = __ldg(tex + (size_t)y * tw + x);
+    const float inv255 = 1.0f / 255.0f;
+    return make_float4(mul((float)p.x, inv255), mul((float)p.y, inv255), mul((float)p.z, inv255), mul((float)p.w, inv255));
+}
+
+// EXTENSION (not in the reference): bilinear + repeat, texel centres at +0.5.
+__device__ __forceinline__ float4 tex_bilinear(const uchar4* tex, int tw, int th, float uu, float vv) {
+    float u = sub(uu, floorf(uu)), v = sub(vv, floorf(vv));
+    float fx = sub(mul(u, (float)tw), 0.5f), fy = sub(mul(v, (float)th), 0.5f);
+    float x0f = floorf(fx), y0f = floorf(fy);
+    float ax = sub(fx, x0f), ay = sub(fy, y0f);
+    int x0 = sat_int(x0f) % tw; if (x0 < 0) x0 += tw;
+    int y0 = sat_int(y0f) % th; if (y0 < 0) y0 += th;
+    int x1 = (x0 + 1) % tw, y1 = (y0 + 1) % th;
+    uchar4 p00 = __ldg(tex + (size_t)y0 * tw + x0), p10 = __ldg(tex + (size_t)y0 * tw + x1);
+    uchar4 p01 = __ldg(tex + (size_t)y1 * tw + x0), p11 = __ldg(tex + (size_t)y1 * tw + x1);
+    const float inv255 = 1.0f / 255.0f;
+    auto ch = [&](unsigned char a, unsigned char b, unsigned char c, unsigned char d) {
+        float t00 = mul((float)a, inv255), t10 = mul((float)b, inv255);
+        float t01 = mul((float)c, inv255), t11 = mul((float)d, inv255);
+        float top = add(t00, mul(sub(t10, t00), ax));
+        float bot = add(t01, mul(sub(t11, t01), ax));
+        return add(top, mul(sub(bot, top), ay));
+    };
+    return make_float4(ch(p00.x, p10.x, p01.x, p11.x), ch(p00.y, p10.y, p01.y, p11.y),
+                       ch(p00.z, p10.z, p01.z, p11.z), ch(p00.w, p10.w, p01.w, p11.w));
+}
+
+// Shade one fragment of triangle `seq` at normalised edge weights (w0f,w1f,w2f):
+// Rasterizer.Interpolate (:566-640) + InterpolateData (:643-707, WorldNormal key)
+// + Renderer.FragmentShader (Renderer.cs:848-860).  Returns the fragment colour;
+// `drawOut` receives the draw index (for blend/depth state).
+__device__ __forceinline__ float4 shade_fragment(const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U,
+                                                 const TriRec& r, uint32_t seq, float w0f, float w1f, float w2f,
+                                                 int& drawOut) {
+    float uv[3][2], col[3][4], wn[3][3];
+    int di;
+    if (r.meta & 0x80000000u) {
+        const ClipAttr& ca = A.clipAttrs[r.meta & 0x7fffffffu];
+        di = ca.draw;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            uv[k][0] = ca.uv[k][0]; uv[k][1] = ca.uv[k][1];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) col[k][j] = ca.col[k][j];
+#pragma unroll
+            for (int j = 0; j < 3; ++j) wn[k][j] = ca.wn[k][j];
+        }
+    } else {
+        di = (int)r.meta;
+        const DrawRec& d = A.draws[di];
+        int t = (int)(seq >> 1) - d.tbase;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            int vi = (int)__ldg(d.idx + 3 * t + (2 - k));     // outputs {v2,v1,v0} (:367)
+            float4 a = __ldg(d.vtx + 3 * vi), b = __ldg(d.vtx + 3 * vi + 1), c = __ldg(d.vtx + 3 * vi + 2);
+            float4 n = __ldg(A.wn + d.vbase + vi);
+            uv[k][0] = a.w; uv[k][1] = b.x;
+            col[k][0] = c.x; col[k][1] = c.y; col[k][2] = c.z; col[k][3] = c.w;
+            wn[k][0] = n.x; wn[k][1] = n.y; wn[k][2] = n.z;
+        }
+    }
+    drawOut = di;
+    const DrawRec& d = A.draws[di];
+    // Interpolate (:576-585)
+    float ra = fdiv(w0f, r.cw0), rb = fdiv(w1f, r.cw1), rc = fdiv(w2f, r.cw2);
+    float sum = add(add(ra, rb), rc);
+    float w = fdiv(1.0f, sum);
+    float wa = mul(ra, w), wb = mul(rb, w), wc = mul(rc, w);
+    auto persp = [&](float a, float b, float c) { return mul(add(add(mul(a, ra), mul(b, rb)), mul(c, rc)), w); };
+    float clipZ = persp(r.cz0, r.cz1, r.cz2);
+    float tu = persp(uv[0][0], uv[1][0], uv[2][0]), tv = persp(uv[0][1], uv[1][1], uv[2][1]);
+    float cr = persp(col[0][0], col[1][0], col[2][0]), cg = persp(col[0][1], col[1][1], col[2][1]);
+    float cb = persp(col[0][2], col[1][2], col[2][2]), cA = persp(col[0][3], col[1][3], col[2][3]);
+    // InterpolateData Vector3 branch (:680-688)
+    float nx = add(add(mul(wn[0][0], wa), mul(wn[1][0], wb)), mul(wn[2][0], wc));
+    float ny = add(add(mul(wn[0][1], wa), mul(wn[1][1], wb)), mul(wn[2][1], wc));
+    float nz = add(add(mul(wn[0][2], wa), mul(wn[1][2], wb)), mul(wn[2][2], wc));
+    float l2 = dot3(nx, ny, nz, nx, ny, nz);
+    if (l2 > 1e-6f) {
+        float inv = fdiv(1.0f, __fsqrt_rn(l2));
+        nx = mul(nx, inv); ny = mul(ny, inv); nz = mul(nz, inv);
+    }
+    // FragmentShader (Renderer.cs:848-860)
+    const bool fma = U.numerics_fma != 0;
+    float diffuse = net_max(0.25f, dot3(nx, ny, nz, -U.light_dir[0], -U.light_dir[1], -U.light_dir[2]));
+    float4 tex = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    if (d.tex != nullptr)
+        tex = U.tex_filter == 1 ? tex_bilinear(d.tex, d.tex_w, d.tex_h, tu, tv) : tex_nearest(d.tex, d.tex_w, d.tex_h, tu, tv);
+    float bx = mul(cr, tex.x), by = mul(cg, tex.y), bz = mul(cb, tex.z), bw = mul(cA, tex.w);
+    float fog = net_clamp(fdiv(sub(U.fog_end, clipZ), sub(U.fog_end, U.fog_start)), 0.0f, 1.0f);
+    fog = mul(mul(fog, fog), sub(3.0f, mul(2.0f, fog)));
+    float k = add(0.1f, mul(0.9f, diffuse));
+    float lx = mul(mul(bx, k), U.light_color[0]), ly = mul(mul(by, k), U.light_color[1]);
+    float lz = mul(mul(bz, k), U.light_color[2]);
+    for (int i = 0; i < U.n_extra_lights && i < 4; ++i) {      // EXTENSION: extra directional lights
+        float di2 = net_max(0.0f, dot3(nx, ny, nz, -U.extra_dir[i][0], -U.extra_dir[i][1], -U.extra_dir[i][2]));
+        lx = add(lx, mul(mul(bx, di2), U.extra_color[i][0]));
+        ly = add(ly, mul(mul(by, di2), U.extra_color[i][1]));
+        lz = add(lz, mul(mul(bz, di2), U.extra_color[i][2]));
+    }
+    return make_float4(lerp1(U.fog_color[0], lx, fog, fma), lerp1(U.fog_color[1], ly, fog, fma),
+                       lerp1(U.fog_color[2], lz, fog, fma), bw);
+}
+
+}  // namespace srb
