@@ -117,6 +117,9 @@ int srb_set_pipeline(SrbContext* ctx, int pipeline);
 /* ---- resources: Texture (Texture.cs:31-63), Mesh arrays (ModelLoader.cs:42-57) ---- */
 int srb_texture_create(SrbContext* ctx, const uint8_t* rgba8, int width, int height, SrbTexture* out);
 int srb_texture_destroy(SrbContext* ctx, SrbTexture tex);
+/* Texture.Sample (Texture.cs:42-63) for n uv pairs, evaluated on the device; filter as SrbUniforms.tex_filter. */
+int srb_texture_sample(SrbContext* ctx, SrbTexture tex, const float* uv /* n*2 */, int n, int filter,
+                       float* rgba_out /* n*4 */);
 int srb_mesh_create(SrbContext* ctx, const float* vertices, int n_vertices,
                     const uint16_t* indices, int n_indices, SrbMesh* out);
 int srb_mesh_destroy(SrbContext* ctx, SrbMesh mesh);

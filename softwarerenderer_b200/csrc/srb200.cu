@@ -357,6 +357,33 @@ int srb_texture_destroy(SrbContext* c, SrbTexture tex) {
     return SRB_OK;
 }
 
+int srb_texture_sample(SrbContext* c, SrbTexture tex, const float* uv, int n, int filter, float* out) {
+    if (!c || !uv || !out || n < 0) return SRB_ERR_ARG;
+    if (n == 0) return SRB_OK;
+    TexRes t;
+    {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (tex <= 0 || (size_t)tex > c->textures.size() || !c->textures[tex - 1].alive)
+            return fail(c, SRB_ERR_HANDLE, "unknown texture handle");
+        t = c->textures[tex - 1];
+    }
+    CK(c, cudaSetDevice(c->device));
+    float* d = nullptr;
+    CK(c, cudaMalloc((void**)&d, (size_t)n * 24));
+    float4* dOut = (float4*)d;
+    float2* dUv = (float2*)(d + (size_t)n * 4);
+    cudaError_t e = cudaMemcpyAsync(dUv, uv, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        texture_sample_kernel<<<(n + 127) / 128, 128, 0, c->stream>>>(t.px, t.w, t.h, dUv, n, filter, dOut);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dOut, (size_t)n * 16, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(c, SRB_ERR_CUDA, std::string("srb_texture_sample: ") + cudaGetErrorString(e));
+    return SRB_OK;
+}
+
 int srb_mesh_create(SrbContext* c, const float* vertices, int nV, const uint16_t* indices, int nI, SrbMesh* out) {
     if (!c || !out) return SRB_ERR_ARG;
     if (!vertices || !indices || nV <= 0 || nI < 0) return fail(c, SRB_ERR_ARG, "bad mesh arrays");

@@ -295,6 +295,14 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     }
 }
 
+__global__ void texture_sample_kernel(const uchar4* __restrict__ tex, int tw, int th, const float2* __restrict__ uv,
+                                      int n, int filter, float4* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float2 t = uv[i];
+    out[i] = filter == 1 ? tex_bilinear(tex, tw, th, t.x, t.y) : tex_nearest(tex, tw, th, t.x, t.y);
+}
+
 // Present-format step (MainWindow.cs:234-250 converts the float buffer for the
 // GL upload): float4 -> RGBA8, clamp to [0,1], round to nearest.
 __global__ void pack_rgba8_kernel(const float4* __restrict__ color, uchar4* __restrict__ out, size_t n) {

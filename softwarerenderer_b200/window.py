@@ -1,0 +1,188 @@
+"""MainWindow -- headless owner of the device framebuffer (MainWindow.cs:17-437).
+
+The reference's window/GL present is replaced by a device buffer; the public
+buffer surface (RenderWidth/Height, ColorBuffer, DepthBuffer, clears, pixel
+accessors, RenderFrame) is kept.  Draws recorded by Rasterizer.RenderMesh are
+deferred: RenderFrame() submits them and launches the CUDA pipeline.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import zlib
+from typing import Optional
+
+import numpy as np
+
+from . import _native as N
+from .numerics import euler_to_direction
+
+
+class Uniforms:
+    """Captured state of the stock shaders (Renderer.cs:39-44) + Rasterizer.NearClip."""
+
+    def __init__(self):
+        self.LightDirection = euler_to_direction((-45.0, -45.0, 0.0))
+        self.LightColor = np.ones(4, dtype=np.float32)
+        self.FogColor = np.array([1.0, 0.62, 0.5, 1.0], dtype=np.float32)
+        self.FogStart = 1.0
+        self.FogEnd = 25.0
+        self.NumericsFma = 1
+        self.TexFilter = 0            # 0 nearest (reference), 1 bilinear (extension)
+        self.ExtraLights = []         # extension: list of (direction3, color3)
+
+    def to_struct(self, near_clip: float) -> N.SrbUniforms:
+        u = N.SrbUniforms()
+        for i in range(3):
+            u.light_dir[i] = float(self.LightDirection[i])
+        for i in range(4):
+            u.light_color[i] = float(self.LightColor[i])
+            u.fog_color[i] = float(self.FogColor[i])
+        u.fog_start, u.fog_end, u.near_clip = float(self.FogStart), float(self.FogEnd), float(near_clip)
+        u.numerics_fma, u.tex_filter = int(self.NumericsFma), int(self.TexFilter)
+        u.n_extra_lights = len(self.ExtraLights)
+        for k, (d, col) in enumerate(self.ExtraLights[:4]):
+            for i in range(3):
+                u.extra_dir[k][i] = float(d[i])
+                u.extra_color[k][i] = float(col[i])
+        return u
+
+
+class MainWindow:
+    def __init__(self, width: int, height: int, device: int = 0, render_scale: float = 1.0):
+        if width <= 0 or height <= 0:
+            raise ValueError("Width and height must be positive non-zero values.")   # Rasterizer.cs:71-74
+        self.RenderScale = render_scale
+        w, h = max(1, int(width * render_scale)), max(1, int(height * render_scale))
+        ctx = C.c_void_p()
+        rc = N.lib().srb_create(device, w, h, C.byref(ctx))
+        if rc != N.SRB_OK:
+            N.check(None, rc)
+        self._ctx = ctx
+        self.RenderWidth, self.RenderHeight = w, h
+        self.Uniforms = Uniforms()
+        self._clear_flags = 0
+        self._clear_color = np.zeros(4, dtype=np.float32)
+        self._draws = []               # recorded SrbDrawCmd rows
+        self._mesh_cache = {}
+        self._keepalive = []
+
+    # -- lifetime -----------------------------------------------------------
+    def Close(self) -> None:
+        if self._ctx:
+            N.lib().srb_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.Close()
+        except Exception:
+            pass
+
+    def Resize(self, width: int, height: int) -> None:
+        """MainWindow.HandleResize (MainWindow.cs:298-361)."""
+        w, h = max(1, int(width * self.RenderScale)), max(1, int(height * self.RenderScale))
+        N.check(self._ctx, N.lib().srb_resize(self._ctx, w, h))
+        self.RenderWidth, self.RenderHeight = w, h
+
+    def SetBand(self, tile_row0: int, tile_row1: int) -> None:
+        N.check(self._ctx, N.lib().srb_set_band(self._ctx, tile_row0, tile_row1))
+
+    def SetPipeline(self, pipeline: int) -> None:
+        N.check(self._ctx, N.lib().srb_set_pipeline(self._ctx, pipeline))
+
+    # -- clears (MainWindow.cs:400-407, 429-436) ------------------------------
+    def ClearColorBuffer(self, clear_color) -> None:
+        if self._draws:
+            self.RenderFrame()
+        self._clear_color = np.asarray(clear_color, dtype=np.float32).reshape(4).copy()
+        self._clear_flags |= N.SRB_CLEAR_COLOR
+
+    def ClearDepthBuffer(self) -> None:
+        if self._draws:
+            self.RenderFrame()
+        self._clear_flags |= N.SRB_CLEAR_DEPTH
+
+    # -- mesh upload cache (the reference re-passes ToArray() copies every call) --
+    def mesh_handle(self, vertices: np.ndarray, indices: np.ndarray) -> int:
+        v = np.ascontiguousarray(vertices)
+        i = np.ascontiguousarray(indices, dtype=np.uint16)
+        key = (v.nbytes, i.nbytes, zlib.crc32(v.view(np.uint8).reshape(-1)), zlib.crc32(i.view(np.uint8).reshape(-1)))
+        h = self._mesh_cache.get(key)
+        if h is None:
+            flat = v.view(np.float32).reshape(-1)
+            if flat.size % 12:
+                raise ValueError("vertices must be VertexInput[] (12 floats each)")
+            out = C.c_int32(0)
+            N.check(self._ctx, N.lib().srb_mesh_create(self._ctx, N.ptr(flat), flat.size // 12, N.ptr(i), i.size,
+                                                       C.byref(out)))
+            h = out.value
+            self._mesh_cache[key] = h
+        return h
+
+    def record_draw(self, row: np.ndarray) -> None:
+        self._draws.append(row)
+
+    # -- frame ----------------------------------------------------------------
+    def RenderFrame(self, near_clip: Optional[float] = None) -> None:
+        """MainWindow.RenderFrame (MainWindow.cs:209-212): submit the recorded draws, run the pipeline."""
+        from .rasterizer import Rasterizer
+
+        L = N.lib()
+        u = self.Uniforms.to_struct(Rasterizer.NearClip if near_clip is None else near_clip)
+        N.check(self._ctx, L.srb_set_uniforms(self._ctx, C.byref(u)))
+        cc = (C.c_float * 4)(*[float(x) for x in self._clear_color])
+        N.check(self._ctx, L.srb_begin_frame(self._ctx, cc, self._clear_flags))
+        if self._draws:
+            cmds = np.concatenate(self._draws)
+            N.check(self._ctx, L.srb_submit_draws(self._ctx, N.ptr(cmds), cmds.shape[0]))
+        N.check(self._ctx, L.srb_end_frame(self._ctx))
+        self._draws = []
+        self._clear_flags = 0
+
+    def ReplayFrame(self) -> None:
+        N.check(self._ctx, N.lib().srb_replay_frame(self._ctx))
+
+    def Sync(self) -> None:
+        N.check(self._ctx, N.lib().srb_sync(self._ctx))
+
+    # -- buffers (MainWindow.cs:30-31) -----------------------------------------
+    @property
+    def ColorBuffer(self) -> np.ndarray:
+        out = np.empty((self.RenderHeight, self.RenderWidth, 4), dtype=np.float32)
+        N.check(self._ctx, N.lib().srb_read_color(self._ctx, N.ptr(out)))
+        return out
+
+    @property
+    def DepthBuffer(self) -> np.ndarray:
+        out = np.empty((self.RenderHeight, self.RenderWidth), dtype=np.float32)
+        N.check(self._ctx, N.lib().srb_read_depth(self._ctx, N.ptr(out)))
+        return out
+
+    def ColorBufferRgba8(self) -> np.ndarray:
+        out = np.empty((self.RenderHeight, self.RenderWidth, 4), dtype=np.uint8)
+        N.check(self._ctx, N.lib().srb_read_color_rgba8(self._ctx, N.ptr(out)))
+        return out
+
+    # -- accessors (MainWindow.cs:378-427) ----------------------------------------
+    def GetPixel(self, x: int, y: int) -> np.ndarray:
+        out = (C.c_float * 4)()
+        N.check(self._ctx, N.lib().srb_get_pixel(self._ctx, x, y, out))
+        return np.array(list(out), dtype=np.float32)
+
+    def SetPixel(self, x: int, y: int, color) -> None:
+        c = (C.c_float * 4)(*[float(v) for v in color])
+        N.check(self._ctx, N.lib().srb_set_pixel(self._ctx, x, y, c))
+
+    def GetDepth(self, x: int, y: int) -> float:
+        out = C.c_float()
+        N.check(self._ctx, N.lib().srb_get_depth(self._ctx, x, y, C.byref(out)))
+        return out.value
+
+    def SetDepth(self, x: int, y: int, depth: float) -> None:
+        N.check(self._ctx, N.lib().srb_set_depth(self._ctx, x, y, float(depth)))
+
+    def Stats(self) -> N.SrbStats:
+        self.Sync()
+        s = N.SrbStats()
+        N.check(self._ctx, N.lib().srb_get_stats(self._ctx, C.byref(s)))
+        return s
