@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""bench.py -- frames/s and Mpixels/s of the rasterization hot path on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload city4k|gun1080|stress8k]
+  python bench.py --impl reference ...      # the CPU path (oracle port) on the host cores
+
+A step = one frame of the workload.  `value` = frames/s with the draw list and
+all meshes/textures resident in HBM (srb_replay_frame); `e2e` = the same frame
+through the public API with host buffers: begin_frame + submit_draws (host
+matrices -> pinned -> H2D) + end_frame + read_color (D2H, float4) every step.
+N>1: sort-first bands on 16-row tile boundaries, one rank per GPU, NCCL
+send/recv gather of the bands into rank 0's framebuffer inside the timed region.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # BASELINE.json configs[2] / [3]: the 4K roofline config (and its band-partitioned form)
+    "city4k": dict(kind="city", width=3840, height=2160, desc="74x{dust2,Gun,gordon}=1,007,140 tris, 1332 draws, FrustumCuller active, 3840x2160"),
+    # configs[1]
+    "gun1080": dict(kind="gun", width=1920, height=1080, desc="bundled Gun (3,910 tris, 2048^2 texture), 1920x1080"),
+    # configs[4]
+    "stress8k": dict(kind="stress", width=7680, height=4320, desc="155 grid meshes x 64,800 = 10,044,000 small tris, 1024^2 texture, 7680x4320"),
+    # small variants for quick checks
+    "city720": dict(kind="city", width=1280, height=720, desc="city scene at 1280x720"),
+}
+
+
+def build_scene(name):
+    from softwarerenderer_b200 import scene as S
+    w = WORKLOADS[name]
+    if w["kind"] == "city":
+        return S.scene_city(w["width"], w["height"])
+    if w["kind"] == "gun":
+        return S.scene_model("Gun", w["width"], w["height"])
+    return S.scene_stress(w["width"], w["height"])
+
+
+def band_rows(tiles_y, n, r):
+    """Tile-row band of rank r of n (balanced by tile rows)."""
+    base, rem = divmod(tiles_y, n)
+    r0 = r * base + min(r, rem)
+    return r0, r0 + base + (1 if r < rem else 0)
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 8 for i in range(4) if r[4 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def algorithmic_bytes(scene, visible, p_cov):
+    """compulsory bytes per frame."""
+    geo, texs = 0, {}
+    for d, vis in zip(scene.draws, visible):
+        if not vis:
+            continue
+        geo += 48 * d.mesh.Vertices.shape[0] + 2 * d.mesh.Indices.size + 192
+        if d.mesh.Texture is not None:
+            texs[id(d.mesh.Texture)] = 4 * d.mesh.Texture.Width * d.mesh.Texture.Height
+    tex = min(sum(texs.values()), 4 * p_cov)
+    fb = 20 * scene.width * scene.height
+    return dict(geometry=geo, texels=tex, framebuffer=fb, total=geo + tex + fb)
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path.  The C# itself cannot run here (no .NET), so this
+    is the C++ restatement (oracle 'port'), tile-row-parallel on all host threads."""
+    from oracle import pyoracle as O
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    O.build()
+    scene = build_scene(args.workload)
+    cores = os.cpu_count() or 1
+    L = O.lib()
+    u = O.make_uniforms(scene)
+    arr, n, keep = O.make_draws(scene, O.frustum_flags(scene))
+    win = L.orc_create(scene.width, scene.height)
+    cc = (C.c_float * 4)(*[float(x) for x in scene.clear_color])
+
+    def frame():
+        L.orc_clear_depth(win)
+        L.orc_clear_color(win, cc)
+        L.orc_render_frame_mt(win, arr, n, C.byref(u), cores, 0, 1 << 30)
+
+    budget = float(os.environ.get("SRB_REF_BUDGET_S", "150"))
+    t_start = time.perf_counter()
+    for _ in range(min(args.warmup, 1)):
+        frame()
+    t0 = time.perf_counter()
+    one = t0 - t_start if args.warmup else None
+    steps = 0
+    while steps < args.steps:
+        frame()
+        steps += 1
+        if time.perf_counter() - t_start > budget:
+            break
+    dt = time.perf_counter() - t0
+    fps = steps / dt
+    W, H = scene.width, scene.height
+    line = {
+        "impl": "reference", "metric": "frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": 1000.0 * dt / steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "mpixels_per_sec": W * H * fps / 1e6,
+        "config": {"workload": args.workload, "scene": WORKLOADS[args.workload]["desc"], "width": W, "height": H,
+                   "triangles": scene.triangle_count, "draws": len(scene.draws)},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} full frame(s) of the workload (requested {args.steps}; bounded to ~{budget:.0f}s); "
+                                   "C++ restatement of the C# path, tile-row-parallel; the C# reference cannot run here (no .NET)"},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+class _DevArray:
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+STAGES = ["frustum", "vertex", "setup_count", "scan", "fill", "sort", "tile_raster"]
+DRAW_REC_BYTES = 280
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import _native as N
+    from softwarerenderer_b200 import scene as S
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback; use --impl reference for the CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = N.lib()
+    scene = build_scene(args.workload)
+    W, H = scene.width, scene.height
+    tiles_y = (H + 15) // 16
+    win = srb.MainWindow(W, H, device=local)
+    ctx = win._ctx
+    r0, r1 = band_rows(tiles_y, world, rank)
+    if world > 1:
+        win.SetBand(r0, r1)
+    y0, y1 = r0 * 16, min(r1 * 16, H)
+    if args.pipeline:
+        win.SetPipeline(args.pipeline)
+
+    # ---- first frame through the mirror API: uploads meshes/textures, settles capacities ----
+    S.submit_scene(win, scene)
+    st = win.Stats()
+    # host-side command array for the e2e loop (what the C# shim would pin and pass)
+    rows = []
+    from softwarerenderer_b200.rasterizer import Rasterizer
+    from softwarerenderer_b200.shaders import Shaders
+    S.submit_scene.__doc__  # noqa: B018
+    win.ClearDepthBuffer(); win.ClearColorBuffer(scene.clear_color)
+    for i, d in enumerate(scene.draws):
+        Rasterizer.RenderMesh(win, d.mesh.Vertices, d.mesh.Indices, d.model, d.view, d.proj, Shaders.StockVertexShader,
+                              Shaders.StockFragmentShader(d.mesh.Texture), d.cull, d.depth, d.blend, submissionIndex=i,
+                              sphereBounds=d.mesh.SphereBounds if d.frustum_cull else None)
+    cmds = np.concatenate(win._draws)
+    win._draws = []
+    win._clear_flags = 0
+    clear = (C.c_float * 4)(*[float(x) for x in scene.clear_color])
+
+    ext = torch.cuda.ExternalStream(L.srb_stream(ctx), device=dev)
+    fb = torch.as_tensor(_DevArray(L.srb_device_color_ptr(ctx), (H, W, 4)), device=dev)
+    bands = [band_rows(tiles_y, world, r) for r in range(world)]
+
+    def gather():
+        if world == 1:
+            return
+        ops = []
+        if rank == 0:
+            for r in range(1, world):
+                a, b = bands[r][0] * 16, min(bands[r][1] * 16, H)
+                if b > a:
+                    ops.append(dist.P2POp(dist.irecv, fb[a:b], r))
+        elif y1 > y0:
+            ops.append(dist.P2POp(dist.isend, fb[y0:y1], 0))
+        if ops:
+            for w_ in dist.batch_isend_irecv(ops):
+                w_.wait()
+
+    def step_resident():
+        N.check(ctx, L.srb_replay_frame(ctx))
+        gather()
+
+    host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+
+    def step_e2e():
+        N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
+        N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
+        N.check(ctx, L.srb_end_frame(ctx))
+        gather()
+        if rank == 0:
+            N.check(ctx, L.srb_read_color(ctx, C.c_void_p(host.data_ptr())))
+
+    def timed(step, K, Wm, sampler=None):
+        with torch.cuda.stream(ext):
+            for _ in range(Wm):
+                step()
+            torch.cuda.synchronize(dev)
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+            if sampler:
+                sampler.start()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record(ext)
+            for _ in range(K):
+                step()
+            e1.record(ext)
+            torch.cuda.synchronize(dev)
+            wall = time.perf_counter() - t0
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+            clocks = sampler.stop() if sampler else None
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms, wall * 1000.0], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1]) / 1000.0
+        return ms, wall, clocks
+
+    K, Wm = args.steps, max(args.warmup, 3)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, wall, clocks = timed(step_resident, K, Wm, sampler)
+    fps = K / (ms / 1000.0)
+    # e2e: host buffers in, host frame out, every step (wall clock: it includes host work by design)
+    Ke = max(5, min(K, args.e2e_steps))
+    ms_e, wall_e, _ = timed(step_e2e, Ke, 3)
+    fps_e = Ke / max(wall_e, ms_e / 1000.0)
+
+    # ---- per-stage device times (CUDA events on the pipeline stream), one synced frame at a time ----
+    N.check(ctx, L.srb_set_profiling(ctx, 1))
+    Kp = min(K, 50)
+    acc = np.zeros(len(STAGES))
+    buf = (C.c_float * len(STAGES))()
+    for i in range(Kp + 3):
+        N.check(ctx, L.srb_replay_frame(ctx))
+        N.check(ctx, L.srb_get_stage_ms(ctx, buf, len(STAGES)))
+        if i >= 3:
+            acc += np.array(list(buf))
+    N.check(ctx, L.srb_set_profiling(ctx, 0))
+    stage_ms = {n_: float(a / Kp) for n_, a in zip(STAGES, acc)}
+
+    # ---- roofline bookkeeping ----
+    depth = win.DepthBuffer
+    p_cov = int((depth[y0:y1] != np.float32(-3.4028235e38)).sum())
+    from softwarerenderer_b200.rasterizer import FrustumCuller
+    cullable = [d for d in scene.draws if d.frustum_cull]
+    visible = [True] * len(scene.draws)
+    if cullable:
+        flags = FrustumCuller.TestSpheres(win, [d.mesh.SphereBounds for d in cullable], [d.model for d in cullable],
+                                          scene.draws[0].view, scene.draws[0].proj)
+        it = iter(flags)
+        visible = [bool(next(it)) if d.frustum_cull else True for d in scene.draws]
+    balg = algorithmic_bytes(scene, visible, p_cov)
+    balg["framebuffer"] = 20 * W * (y1 - y0)
+    balg["total"] = balg["geometry"] + balg["texels"] + balg["framebuffer"]
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    dom = max(stage_ms, key=stage_ms.get)
+    dom_bytes = balg["framebuffer"] + balg["texels"] if dom == "tile_raster" else balg["geometry"]
+    achieved = dom_bytes / (stage_ms[dom] / 1000.0) / 1e9 if stage_ms[dom] > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(args.workload, {}).get(dom)
+    frame_ms = ms / K
+    st = win.Stats()
+
+    line = None
+    if rank == 0:
+        line = {
+            "metric": "frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "mpixels_per_sec": W * H * fps / 1e6,
+            "config": {"workload": args.workload, "scene": WORKLOADS[args.workload]["desc"], "width": W, "height": H,
+                       "triangles": scene.triangle_count, "draws": len(scene.draws),
+                       "draws_visible": int(sum(visible)), "triangles_setup": int(st.triangles_setup),
+                       "tile_pairs": int(st.tile_pairs), "pipeline": "visibility" if st.pipeline_used == 2 else "ordered",
+                       "parallelism": f"bands{world}" if world > 1 else "single",
+                       "l2": "no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
+                             if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush"},
+            "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES + 8 * (cmds.shape[0] + 1)),
+                    "d2h_bytes_per_step": int(W * H * 16), "steps": Ke, "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke,
+                    "mpixels_per_sec": W * H * fps_e / 1e6},
+            "gpu_launches": int(st.kernel_launches) * K,
+            "clocks": clocks,
+            "stage_ms": stage_ms,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes": dom_bytes, "peak_source": peak_src},
+            "roofline_frame": {"algorithmic_bytes": balg, "achieved": balg["total"] / (frame_ms / 1000.0) / 1e9,
+                               "frac": balg["total"] / (frame_ms / 1000.0) / 1e9 / peak, "unit": "GB/s"},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(scene)
+    win.Close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line))
+
+
+def cpu_baseline(scene, budget_s=25.0):
+    """Oracle port timed on the box's host cores on a bounded sample (whole frames)."""
+    from oracle import pyoracle as O
+    O.build()
+    L = O.lib()
+    cores = os.cpu_count() or 1
+    u = O.make_uniforms(scene)
+    arr, n, keep = O.make_draws(scene, O.frustum_flags(scene))
+    win = L.orc_create(scene.width, scene.height)
+    cc = (C.c_float * 4)(*[float(x) for x in scene.clear_color])
+    times = []
+    t_all = time.perf_counter()
+    for i in range(6):
+        t0 = time.perf_counter()
+        L.orc_clear_depth(win)
+        L.orc_clear_color(win, cc)
+        L.orc_render_frame_mt(win, arr, n, C.byref(u), cores, 0, 1 << 30)
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() - t_all > budget_s and len(times) >= 2:
+            break
+    L.orc_destroy(win)
+    meas = times[1:] if len(times) > 1 else times
+    med = float(np.median(meas))
+    return {"value": 1.0 / med, "unit": "frames/s", "cores": cores, "kind": "port",
+            "sample": f"{len(meas)} full frame(s) after 1 warm-up, median; C++ restatement of the C# path "
+                      "(tile-row-parallel, bit-identical to the literal oracle); the C# reference cannot run here"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="srb200", choices=["srb200", "reference"])
+    ap.add_argument("--workload", default="city4k", choices=sorted(WORKLOADS))
+    ap.add_argument("--pipeline", type=int, default=0, help="0 auto, 1 ordered, 2 visibility")
+    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -156,6 +156,12 @@ int srb_frustum_test(SrbContext* ctx, const float* spheres /* n*4 */, const floa
                      const float view[16], const float proj[16], int n, int32_t* out_visible);
 
 int srb_get_stats(SrbContext* ctx, SrbStats* out);
+/* Per-stage device times of the last completed frame (CUDA events on the pipeline stream).
+ * Enable with srb_set_profiling(ctx, 1); stages: 0 frustum, 1 vertex, 2 setup+count, 3 scan,
+ * 4 fill, 5 sort (ordered path only), 6 tile raster.  Returns ms per stage in out[0..n). */
+#define SRB_N_STAGES 7
+int srb_set_profiling(SrbContext* ctx, int enabled);
+int srb_get_stage_ms(SrbContext* ctx, float* out, int n);
 int srb_version(void);
 
 #ifdef __cplusplus

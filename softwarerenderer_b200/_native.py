@@ -53,7 +53,7 @@ class SrbStats(C.Structure):
     ]
 
 
-# numpy mirror of SrbDrawCmd (272 bytes) for batched submission.
+# numpy mirror of SrbDrawCmd (248 bytes) for batched submission.
 DRAW_CMD_DTYPE = np.dtype(
     [
         ("mesh", "<i4"),
@@ -81,7 +81,7 @@ EXPORTS = [
     "srb_submit_draws", "srb_end_frame", "srb_replay_frame", "srb_sync", "srb_read_color",
     "srb_read_depth", "srb_read_color_rgba8", "srb_read_color_rows", "srb_get_pixel", "srb_set_pixel",
     "srb_get_depth", "srb_set_depth", "srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream",
-    "srb_frustum_test", "srb_get_stats", "srb_version",
+    "srb_frustum_test", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
 ]
 
 _lib = None
@@ -139,6 +139,8 @@ def lib() -> C.CDLL:
     L.srb_frustum_test.argtypes = [vp, vp, vp, vp, vp, i32, vp]
     L.srb_get_stats.argtypes = [vp, C.POINTER(SrbStats)]
     L.srb_version.argtypes = []
+    L.srb_set_profiling.argtypes = [vp, i32]
+    L.srb_get_stage_ms.argtypes = [vp, f32p, i32]
     _lib = L
     return L
 

@@ -80,6 +80,10 @@ struct SrbContext {
     int32_t* hBases = nullptr;        // pinned staging: vbase then tbase
     size_t hDrawsCap = 0;
     SrbStats stats;
+    bool profiling = false;
+    cudaEvent_t stageEv[SRB_N_STAGES + 1] = {};
+    bool stageRan[SRB_N_STAGES] = {};
+    float stageMs[SRB_N_STAGES] = {};
     std::string err;
 };
 
@@ -132,13 +136,20 @@ int launch_frame(SrbContext* c) {
     const int nTiles = fp.tilesX * fp.tilesY;
     const int bandTiles = (fp.bandRow1 - fp.bandRow0) * fp.tilesX;
     int launches = 0;
+    int stage = 0;
+    auto mark = [&](int next) {       // close stages [stage, next) at this point of the stream
+        if (!c->profiling) return;
+        for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], c->stream);
+    };
     CK(c, cudaEventRecord(c->ev0, c->stream));
     CK(c, cudaMemsetAsync(c->dCnt, 0, sizeof(Counters), c->stream));
     CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), c->stream));
+    if (c->profiling) cudaEventRecord(c->stageEv[0], c->stream);
     if (fp.nDraws > 0) {
         frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt);
         ++launches;
     }
+    mark(1);
     if (fp.totalV > 0) {
         int grid = (fp.totalV + 255) / 256;
         if (U.numerics_fma)
@@ -147,20 +158,24 @@ int launch_frame(SrbContext* c) {
             vertex_kernel<false><<<grid, 256, 0, c->stream>>>(c->dDraws.p, c->dVbase.p, fp, c->dClip.p, c->dWn.p);
         ++launches;
     }
+    mark(2);
     if (fp.totalT > 0) {
         setup_kernel<<<(fp.totalT + 255) / 256, 256, 0, c->stream>>>(
             c->dDraws.p, c->dTbase.p, fp, U, c->dClip.p, c->dWn.p, c->dRecs.p, c->dClipAttrs.p, c->dRefs.p,
             c->dTileCount.p, c->dCnt);
         ++launches;
     }
+    mark(3);
     scan_tiles_kernel<<<1, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, nTiles, c->dCnt, fp.pairCap);
     ++launches;
+    mark(4);
     if (fp.totalT > 0) {
         // worst case two accepted triangles per submitted one (near-clip fan)
         size_t maxRefs = 2 * (size_t)fp.totalT;
         fill_bins_kernel<<<(unsigned)((maxRefs + 255) / 256), 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
         ++launches;
     }
+    mark(5);
     RasterArgs A;
     A.draws = c->dDraws.p; A.tbase = c->dTbase.p; A.wn = c->dWn.p; A.recs = c->dRecs.p;
     A.clipAttrs = c->dClipAttrs.p; A.tileStart = c->dTileStart.p; A.tileEnd = c->dTileCursor.p;
@@ -177,10 +192,12 @@ int launch_frame(SrbContext* c) {
         } else {
             sort_bins_kernel<<<bandTiles, 256, 0, c->stream>>>(c->dTileStart.p, c->dTileCursor.p, c->dBins.p,
                                                               c->dBinScratch.p, fp.bandRow0 * fp.tilesX, c->dCnt);
+            mark(6);
             ordered_tile_kernel<<<bandTiles, 256, 0, c->stream>>>(A, fp, U);
             launches += 2;
         }
     }
+    mark(7);
     CK(c, cudaGetLastError());
     CK(c, cudaMemcpyAsync(c->hCnt, c->dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaEventRecord(c->ev1, c->stream));
@@ -223,6 +240,11 @@ int complete_frame(SrbContext* c) {
     c->stats.clipped_triangles = k.nClippedTris;
     float ms = 0.0f;
     if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.gpu_ms = ms;
+    if (c->profiling)
+        for (int i = 0; i < SRB_N_STAGES; ++i) {
+            float t = 0.0f;
+            c->stageMs[i] = cudaEventElapsedTime(&t, c->stageEv[i], c->stageEv[i + 1]) == cudaSuccess ? t : 0.0f;
+        }
     return SRB_OK;
 }
 
@@ -288,6 +310,7 @@ int srb_destroy(SrbContext* c) {
     if (c->hBases) cudaFreeHost(c->hBases);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    for (auto& e : c->stageEv) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
     return SRB_OK;
@@ -704,6 +727,26 @@ int srb_frustum_test(SrbContext* c, const float* spheres, const float* models, c
 void* srb_device_color_ptr(SrbContext* c) { return c ? (void*)c->color : nullptr; }
 void* srb_device_depth_ptr(SrbContext* c) { return c ? (void*)c->depth : nullptr; }
 void* srb_stream(SrbContext* c) { return c ? (void*)c->stream : nullptr; }
+
+int srb_set_profiling(SrbContext* c, int enabled) {
+    if (!c) return SRB_ERR_ARG;
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    if (enabled && !c->stageEv[0])
+        for (int i = 0; i <= SRB_N_STAGES; ++i) CK(c, cudaEventCreate(&c->stageEv[i]));
+    c->profiling = enabled != 0;
+    return SRB_OK;
+}
+
+int srb_get_stage_ms(SrbContext* c, float* out, int n) {
+    if (!c || !out || n < 0) return SRB_ERR_ARG;
+    if (!c->profiling) return fail(c, SRB_ERR_STATE, "profiling is off");
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    for (int i = 0; i < n && i < SRB_N_STAGES; ++i) out[i] = c->stageMs[i];
+    return SRB_OK;
+}
 
 int srb_get_stats(SrbContext* c, SrbStats* out) {
     if (!c || !out) return SRB_ERR_ARG;

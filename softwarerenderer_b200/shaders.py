@@ -108,7 +108,7 @@ class Texture:
             return None
 
     def handle(self, window) -> int:
-        key = id(window)
+        key = window._uid
         h = self._handles.get(key)
         if h is None:
             import ctypes as C

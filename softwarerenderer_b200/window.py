@@ -48,6 +48,8 @@ class Uniforms:
 
 
 class MainWindow:
+    _next_uid = 0
+
     def __init__(self, width: int, height: int, device: int = 0, render_scale: float = 1.0):
         if width <= 0 or height <= 0:
             raise ValueError("Width and height must be positive non-zero values.")   # Rasterizer.cs:71-74
@@ -58,6 +60,8 @@ class MainWindow:
         if rc != N.SRB_OK:
             N.check(None, rc)
         self._ctx = ctx
+        MainWindow._next_uid += 1
+        self._uid = MainWindow._next_uid     # key for per-context resource handles
         self.RenderWidth, self.RenderHeight = w, h
         self.Uniforms = Uniforms()
         self._clear_flags = 0
