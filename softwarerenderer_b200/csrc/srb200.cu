@@ -182,6 +182,7 @@ int launch_frame(SrbContext* c) {
     A.bins = c->dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = c->dCnt;
     if (bandTiles > 0) {
         if (c->useVis) {
+            mark(6);                       // no sort stage on the visibility path
             switch (c->visMode) {
                 case 0: vis_tile_kernel<0><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
                 case 1: vis_tile_kernel<1><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
