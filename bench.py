@@ -48,11 +48,7 @@ def build_scene(name):
     return S.scene_stress(w["width"], w["height"])
 
 
-def band_rows(tiles_y, n, r):
-    """Tile-row band of rank r of n (balanced by tile rows)."""
-    base, rem = divmod(tiles_y, n)
-    r0 = r * base + min(r, rem)
-    return r0, r0 + base + (1 if r < rem else 0)
+from softwarerenderer_b200.bands import band_rows, gather_bands  # noqa: E402
 
 
 class ClockSampler:
@@ -214,22 +210,9 @@ def run_gpu(args):
 
     ext = torch.cuda.ExternalStream(L.srb_stream(ctx), device=dev)
     fb = torch.as_tensor(_DevArray(L.srb_device_color_ptr(ctx), (H, W, 4)), device=dev)
-    bands = [band_rows(tiles_y, world, r) for r in range(world)]
 
     def gather():
-        if world == 1:
-            return
-        ops = []
-        if rank == 0:
-            for r in range(1, world):
-                a, b = bands[r][0] * 16, min(bands[r][1] * 16, H)
-                if b > a:
-                    ops.append(dist.P2POp(dist.irecv, fb[a:b], r))
-        elif y1 > y0:
-            ops.append(dist.P2POp(dist.isend, fb[y0:y1], 0))
-        if ops:
-            for w_ in dist.batch_isend_irecv(ops):
-                w_.wait()
+        gather_bands(fb, H, rank, world, dist)
 
     def step_resident():
         N.check(ctx, L.srb_replay_frame(ctx))

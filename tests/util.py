@@ -58,4 +58,5 @@ def screen_tri_scene(W, H, tris, colors=None, uvs=None, ndc_z=0.5, cull=0, depth
         v = Shaders.make_vertices(np.asarray(pos)[sel], uv=np.asarray(uv)[sel], color=np.asarray(col)[sel])
         idx = np.arange(len(sel), dtype=np.uint16)
         draws.append(DrawItem(Mesh(v, idx, Material(), None, texture), I, I, I, cull=cull, depth=depth, blend=blend))
-    return Scene(W, H, draws, clear_color=(0.0, 0.0, 0.0, 0.0), fog_start=-2.0, fog_end=-1.0)
+    # fog_start > every clip z used here -> fog factor clamps to 1 -> no fog unless a test sets it
+    return Scene(W, H, draws, clear_color=(0.0, 0.0, 0.0, 0.0), fog_start=10.0, fog_end=20.0)
