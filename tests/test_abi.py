@@ -91,3 +91,10 @@ def test_product_does_not_link_or_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dp, f)).read()
                 assert "pyoracle" not in text and "liboracle" not in text and "import oracle" not in text, f
+
+
+def test_csharp_binding_covers_the_header():
+    """csharp/Native.cs (the P/Invoke stub a maintainer adds) binds every declared symbol."""
+    text = open(os.path.join(ROOT, "csharp", "Native.cs")).read()
+    bound = set(re.findall(r"extern\s+\w+\s+(srb_[a-z0-9_]+)\s*\(", text))
+    assert bound == set(_declared())
