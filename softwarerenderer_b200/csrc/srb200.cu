@@ -44,7 +44,7 @@ struct QueuedDraw { SrbDrawCmd cmd; int64_t order; };
 }  // namespace
 
 struct SrbContext {
-    int device = 0;
+    int device = 0, smCount = 148;
     int W = 0, H = 0, tilesX = 0, tilesY = 0;
     int band0 = 0, band1 = 0;
     bool bandSet = false;
@@ -68,17 +68,18 @@ struct SrbContext {
     bool useVis = false;
     int visMode = 0;
     DevBuf<DrawRec> dDraws;
-    DevBuf<int32_t> dVbase, dTbase;
+    DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels
+    int nVBlocks = 0, nTBlocks = 0;
     DevBuf<float4> dClip, dWn;
-    DevBuf<TriRec> dRecs;
+    DevBuf<float4> dRecsR, dRecsS;    // split setup records (RecStore)
     DevBuf<TriRef> dRefs;
     DevBuf<ClipAttr> dClipAttrs;
-    DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dBins, dBinScratch;
+    DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dOrder, dBins, dBinScratch;
     Counters* dCnt = nullptr;
     Counters* hCnt = nullptr;         // pinned
     DrawRec* hDraws = nullptr;        // pinned staging
-    int32_t* hBases = nullptr;        // pinned staging: vbase then tbase
-    size_t hDrawsCap = 0;
+    int2* hBlocks = nullptr;          // pinned staging: vertex blocks then triangle blocks
+    size_t hDrawsCap = 0, hBlocksCap = 0;
     SrbStats stats;
     bool profiling = false;
     cudaEvent_t stageEv[SRB_N_STAGES + 1] = {};
@@ -150,34 +151,37 @@ int launch_frame(SrbContext* c) {
         ++launches;
     }
     mark(1);
-    if (fp.totalV > 0) {
-        int grid = (fp.totalV + 255) / 256;
+    if (c->nVBlocks > 0) {
         if (U.numerics_fma)
-            vertex_kernel<true><<<grid, 256, 0, c->stream>>>(c->dDraws.p, c->dVbase.p, fp, c->dClip.p, c->dWn.p);
+            vertex_kernel<true><<<c->nVBlocks, kGeomBlock, 0, c->stream>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, c->dWn.p);
         else
-            vertex_kernel<false><<<grid, 256, 0, c->stream>>>(c->dDraws.p, c->dVbase.p, fp, c->dClip.p, c->dWn.p);
+            vertex_kernel<false><<<c->nVBlocks, kGeomBlock, 0, c->stream>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, c->dWn.p);
         ++launches;
     }
     mark(2);
-    if (fp.totalT > 0) {
-        setup_kernel<<<(fp.totalT + 255) / 256, 256, 0, c->stream>>>(
-            c->dDraws.p, c->dTbase.p, fp, U, c->dClip.p, c->dWn.p, c->dRecs.p, c->dClipAttrs.p, c->dRefs.p,
+    if (c->nTBlocks > 0) {
+        setup_kernel<<<c->nTBlocks, kGeomBlock, 0, c->stream>>>(
+            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, c->dWn.p, RecStore{c->dRecsR.p, c->dRecsS.p}, c->dClipAttrs.p, c->dRefs.p,
             c->dTileCount.p, c->dCnt);
         ++launches;
     }
     mark(3);
-    scan_tiles_kernel<<<1, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, nTiles, c->dCnt, fp.pairCap);
-    ++launches;
+    if (bandTiles > 0) {
+        scan_tiles_kernel<<<1, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, c->dOrder.p,
+                                                     fp.bandRow0 * fp.tilesX, bandTiles, c->dCnt, fp.pairCap);
+        ++launches;
+    }
     mark(4);
-    if (fp.totalT > 0) {
-        // worst case two accepted triangles per submitted one (near-clip fan)
+    if (fp.totalT > 0 && bandTiles > 0) {
+        // grid-stride over the accepted-triangle list (its length is only known on the device)
         size_t maxRefs = 2 * (size_t)fp.totalT;
-        fill_bins_kernel<<<(unsigned)((maxRefs + 255) / 256), 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
+        unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
+        fill_bins_kernel<<<grid, 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
         ++launches;
     }
     mark(5);
     RasterArgs A;
-    A.draws = c->dDraws.p; A.tbase = c->dTbase.p; A.wn = c->dWn.p; A.recs = c->dRecs.p;
+    A.draws = c->dDraws.p; A.order = c->dOrder.p; A.wn = c->dWn.p; A.recs.R = c->dRecsR.p; A.recs.S = c->dRecsS.p;
     A.clipAttrs = c->dClipAttrs.p; A.tileStart = c->dTileStart.p; A.tileEnd = c->dTileCursor.p;
     A.bins = c->dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = c->dCnt;
     if (bandTiles > 0) {
@@ -282,6 +286,8 @@ int srb_create(int device, int width, int height, SrbContext** out_ctx) {
         return SRB_ERR_CUDA;
     };
     if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    cudaDeviceGetAttribute(&c->smCount, cudaDevAttrMultiProcessorCount, device);
+    if (c->smCount <= 0) c->smCount = 148;
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail("cudaEventCreate", e);
@@ -300,15 +306,15 @@ int srb_destroy(SrbContext* c) {
     cudaStreamSynchronize(c->stream);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
-    c->dDraws.release(); c->dVbase.release(); c->dTbase.release(); c->dClip.release(); c->dWn.release();
-    c->dRecs.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dTileCount.release();
+    c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dOrder.release(); c->dClip.release(); c->dWn.release();
+    c->dRecsR.release(); c->dRecsS.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dTileCount.release();
     c->dTileStart.release(); c->dTileCursor.release(); c->dBins.release(); c->dBinScratch.release();
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
     if (c->dCnt) cudaFree(c->dCnt);
     if (c->hCnt) cudaFreeHost(c->hCnt);
     if (c->hDraws) cudaFreeHost(c->hDraws);
-    if (c->hBases) cudaFreeHost(c->hBases);
+    if (c->hBlocks) cudaFreeHost(c->hBlocks);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     for (auto& e : c->stageEv) if (e) cudaEventDestroy(e);
@@ -518,15 +524,27 @@ int srb_end_frame(SrbContext* c) {
     const int nDraws = (int)c->queue.size();
     if ((size_t)nDraws + 1 > c->hDrawsCap) {
         if (c->hDraws) cudaFreeHost(c->hDraws);
-        if (c->hBases) cudaFreeHost(c->hBases);
-        c->hDraws = nullptr; c->hBases = nullptr;
+        c->hDraws = nullptr;
         size_t cap = (size_t)nDraws + nDraws / 2 + 64;
         CK(c, cudaMallocHost((void**)&c->hDraws, cap * sizeof(DrawRec)));
-        CK(c, cudaMallocHost((void**)&c->hBases, 2 * (cap + 1) * sizeof(int32_t)));
         c->hDrawsCap = cap;
     }
-    int32_t* hV = c->hBases;
-    int32_t* hT = c->hBases + (nDraws + 1);
+    size_t nVB = 0, nTB = 0;
+    for (int i = 0; i < nDraws; ++i) {
+        const MeshRes& m = c->meshes[c->queue[i].cmd.mesh - 1];
+        nVB += ((size_t)m.nV + kGeomBlock - 1) / kGeomBlock;
+        nTB += ((size_t)(m.nI / 3) + kGeomBlock - 1) / kGeomBlock;
+    }
+    if (nVB + nTB + 1 > c->hBlocksCap) {
+        if (c->hBlocks) cudaFreeHost(c->hBlocks);
+        c->hBlocks = nullptr;
+        size_t cap = (nVB + nTB) + (nVB + nTB) / 2 + 64;
+        CK(c, cudaMallocHost((void**)&c->hBlocks, cap * sizeof(int2)));
+        c->hBlocksCap = cap;
+    }
+    int2* hV = c->hBlocks;
+    int2* hT = c->hBlocks + nVB;
+    size_t iv = 0, it = 0;
     int64_t totalV = 0, totalT = 0;
     bool eligible = (c->clearFlags & SRB_CLEAR_COLOR) && (c->clearFlags & SRB_CLEAR_DEPTH);
     int commonDepth = -1;
@@ -548,7 +566,8 @@ int srb_end_frame(SrbContext* c) {
         d.vbase = (int32_t)totalV; d.tbase = (int32_t)totalT;
         d.cull = q.cull; d.depth_test = q.depth_test; d.blend = q.blend;
         d.flags = q.flags; d.visible = 1; d._pad = 0;
-        hV[i] = (int32_t)totalV; hT[i] = (int32_t)totalT;
+        for (int f = 0; f < m.nV; f += kGeomBlock) hV[iv++] = make_int2(i, f);
+        for (int f = 0; f < m.nI / 3; f += kGeomBlock) hT[it++] = make_int2(i, f);
         totalV += m.nV; totalT += m.nI / 3;
         // Visibility path eligibility: extreme-depth winner with
         // alpha provably 1, one depth function for the whole frame.
@@ -557,7 +576,6 @@ int srb_end_frame(SrbContext* c) {
         if (q.blend != SRB_BLEND_ALPHA && q.blend != SRB_BLEND_NONE) eligible = false;
         if (!m.opaque || !texOpaque) eligible = false;
     }
-    hV[nDraws] = (int32_t)totalV; hT[nDraws] = (int32_t)totalT;
     if (totalV > 0x3fffffff || totalT > 0x3fffffff) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
     if (c->pipeline == SRB_PIPELINE_ORDERED) eligible = false;
     if (c->pipeline == SRB_PIPELINE_VISIBILITY && !eligible && nDraws > 0)
@@ -572,11 +590,13 @@ int srb_end_frame(SrbContext* c) {
     }
     const int nTiles = c->tilesX * c->tilesY;
     CK(c, c->dDraws.reserve((size_t)nDraws + 1));
-    CK(c, c->dVbase.reserve((size_t)nDraws + 1));
-    CK(c, c->dTbase.reserve((size_t)nDraws + 1));
+    CK(c, c->dVBlocks.reserve(nVB + 1));
+    CK(c, c->dTBlocks.reserve(nTB + 1));
+    CK(c, c->dOrder.reserve(nTiles));
     CK(c, c->dClip.reserve((size_t)totalV + 1));
     CK(c, c->dWn.reserve((size_t)totalV + 1));
-    CK(c, c->dRecs.reserve(2 * (size_t)totalT + 2));
+    CK(c, c->dRecsR.reserve(3 * (2 * (size_t)totalT + 2)));
+    CK(c, c->dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
     CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
     CK(c, c->dClipAttrs.reserve(4096));
     CK(c, c->dTileCount.reserve(nTiles));
@@ -587,8 +607,9 @@ int srb_end_frame(SrbContext* c) {
     if (nDraws > 0) {
         CK(c, cudaMemcpyAsync(c->dDraws.p, c->hDraws, (size_t)nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, c->stream));
     }
-    CK(c, cudaMemcpyAsync(c->dVbase.p, hV, ((size_t)nDraws + 1) * 4, cudaMemcpyHostToDevice, c->stream));
-    CK(c, cudaMemcpyAsync(c->dTbase.p, hT, ((size_t)nDraws + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    if (nVB) CK(c, cudaMemcpyAsync(c->dVBlocks.p, hV, nVB * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
+    if (nTB) CK(c, cudaMemcpyAsync(c->dTBlocks.p, hT, nTB * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
+    c->nVBlocks = (int)nVB; c->nTBlocks = (int)nTB;
     FrameParams& fp = c->fp;
     fp.W = c->W; fp.H = c->H; fp.tilesX = c->tilesX; fp.tilesY = c->tilesY;
     fp.bandRow0 = c->band0; fp.bandRow1 = c->band1;

@@ -37,17 +37,52 @@ struct DrawRec {
     int32_t _pad;
 };
 
-// ---- triangle setup record, 64 B, slot = 2*global_triangle + fan ----
+// ---- triangle setup record, slot = 2*global_triangle + fan ----
 // s = screen coords of outputs {v2,v1,v0} (Rasterizer.cs:367,383-386),
-// d = depths (:388), cz/cw = clip z/w of the same three corners.
-struct __align__(16) TriRec {
+// d = depths (:388), cz/cw = clip z/w of the same three corners, invArea = 1f/area (:427),
+// bbox = the clamped integer bounding box (:432-442).
+// In memory the record is split: 48 B the coverage pass reads (RecStore::R: s, d, invArea,
+// bbox) and 32 B only shading reads (RecStore::S: cz, cw, meta).
+struct TriRec {
     float s0x, s0y, s1x, s1y;
     float s2x, s2y, d0, d1;
-    float d2, cz0, cz1, cz2;
-    float cw0, cw1, cw2;
+    float d2, invArea;
+    uint32_t bx, by;          // minX | maxX << 16,  minY | maxY << 16
+    float cz0, cz1, cz2, cw0;
+    float cw1, cw2;
     uint32_t meta;            // bit31: clipped (low bits = side-buffer index); else draw id
 };
-static_assert(sizeof(TriRec) == 64, "TriRec must be 64 B");
+struct RecStore {
+    float4* R;                // 3 float4 per slot
+    float4* S;                // 2 float4 per slot
+};
+__device__ __forceinline__ void store_rec(const RecStore& st, uint32_t seq, const TriRec& r) {
+    float4* q = st.R + 3 * (size_t)seq;
+    q[0] = make_float4(r.s0x, r.s0y, r.s1x, r.s1y);
+    q[1] = make_float4(r.s2x, r.s2y, r.d0, r.d1);
+    q[2] = make_float4(r.d2, r.invArea, __uint_as_float(r.bx), __uint_as_float(r.by));
+    float4* t = st.S + 2 * (size_t)seq;
+    t[0] = make_float4(r.cz0, r.cz1, r.cz2, r.cw0);
+    t[1] = make_float4(r.cw1, r.cw2, __uint_as_float(r.meta), 0.0f);
+}
+// Coverage part only (cz/cw/meta left unset).
+__device__ __forceinline__ TriRec load_rec_raster(const RecStore& st, uint32_t seq) {
+    const float4* q = st.R + 3 * (size_t)seq;
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+    TriRec r;
+    r.s0x = a.x; r.s0y = a.y; r.s1x = a.z; r.s1y = a.w;
+    r.s2x = b.x; r.s2y = b.y; r.d0 = b.z; r.d1 = b.w;
+    r.d2 = c.x; r.invArea = c.y; r.bx = __float_as_uint(c.z); r.by = __float_as_uint(c.w);
+    return r;
+}
+__device__ __forceinline__ TriRec load_rec(const RecStore& st, uint32_t seq) {
+    TriRec r = load_rec_raster(st, seq);
+    const float4* t = st.S + 2 * (size_t)seq;
+    float4 a = __ldg(t), b = __ldg(t + 1);
+    r.cz0 = a.x; r.cz1 = a.y; r.cz2 = a.z; r.cw0 = a.w;
+    r.cw1 = b.x; r.cw2 = b.y; r.meta = __float_as_uint(b.z);
+    return r;
+}
 
 // Varyings of a near-clipped triangle (Shaders.Lerp outputs), 3 corners in output order.
 struct __align__(16) ClipAttr {
@@ -194,14 +229,14 @@ __device__ __forceinline__ void tri_bbox(const TriRec& r, int W, int H, int& min
     minY = max(sat_int(floorf(minYf)), 0);
     maxY = min(sat_int(ceilf(maxYf)), H - 1);
 }
-__device__ __forceinline__ TriEq tri_eq(const TriRec& r, int W, int H) {
+__device__ __forceinline__ TriEq tri_eq(const TriRec& r) {
     TriEq e;
-    float area = edge_fn(r.s0x, r.s0y, r.s1x, r.s1y, r.s2x, r.s2y);
-    e.invArea = fdiv(1.0f, area);
+    e.invArea = r.invArea;
     e.a01 = sub(r.s0y, r.s1y); e.b01 = sub(r.s1x, r.s0x);   // :445-447
     e.a12 = sub(r.s1y, r.s2y); e.b12 = sub(r.s2x, r.s1x);
     e.a20 = sub(r.s2y, r.s0y); e.b20 = sub(r.s0x, r.s2x);
-    tri_bbox(r, W, H, e.minX, e.maxX, e.minY, e.maxY);
+    e.minX = (int)(r.bx & 0xffffu); e.maxX = (int)(r.bx >> 16);
+    e.minY = (int)(r.by & 0xffffu); e.maxY = (int)(r.by >> 16);
     return e;
 }
 // Row bases at (startX, startY) by the direct formula (Rasterizer.cs:481-483).

@@ -88,30 +88,26 @@ __global__ void frustum_batch_kernel(const float* spheres, const float* models, 
                  : sphere_in_frustum<false>(spheres + 4 * i, models + 16 * i, V, P);
 }
 
-// Largest i with base[i] <= g  (base has n+1 entries, base[n] = total).
-__device__ __forceinline__ int find_owner(const int32_t* __restrict__ base, int n, int g) {
-    int lo = 0, hi = n;            // invariant: base[lo] <= g < base[hi]
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (__ldg(base + mid) <= g) lo = mid; else hi = mid;
-    }
-    return lo;
-}
+// Geometry kernels run one CTA per block-table entry: a run of <= kGeomBlock
+// vertices (or triangles) of ONE draw, built on the host when the draw list is
+// uploaded.  The draw lookup is a single load and a frustum-culled draw retires
+// whole CTAs at once.  int2 = {draw index, first element within the draw}.
+constexpr int kGeomBlock = 128;
 
 // ---------------------------------------------------------------------------
 // Vertex stage: Renderer.VertexShader (Renderer.cs:830-846) once per unique
 // vertex of every visible draw.  48-B vertex read as three float4.
 // ---------------------------------------------------------------------------
 template <bool FMA>
-__global__ void __launch_bounds__(256)
-vertex_kernel(const DrawRec* __restrict__ draws, const int32_t* __restrict__ vbase, FrameParams fp,
+__global__ void __launch_bounds__(kGeomBlock)
+vertex_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ vblocks,
               float4* __restrict__ clipOut, float4* __restrict__ wnOut) {
-    int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= fp.totalV) return;
-    int di = find_owner(vbase, fp.nDraws, g);
-    const DrawRec& d = draws[di];
+    const int2 blk = __ldg(vblocks + blockIdx.x);
+    const DrawRec& d = draws[blk.x];
     if (!d.visible) return;
-    int v = g - d.vbase;
+    const int v = blk.y + threadIdx.x;
+    if (v >= d.n_vertices) return;
+    const int g = d.vbase + v;
     float4 a = __ldg(d.vtx + 3 * v);          // pos.xyz, uv.x
     float4 b = __ldg(d.vtx + 3 * v + 1);      // uv.y, normal.xyz
     float4 world = transform4<FMA>(make_float4(a.x, a.y, a.z, 1.0f), d.model);
@@ -151,8 +147,12 @@ __device__ __forceinline__ bool setup_tri(const float4 c[3], int W, int H, int c
     r.d0 = dz[0]; r.d1 = dz[1]; r.d2 = dz[2];
     r.cz0 = c[0].z; r.cz1 = c[1].z; r.cz2 = c[2].z;
     r.cw0 = c[0].w; r.cw1 = c[1].w; r.cw2 = c[2].w;
+    r.invArea = fdiv(1.0f, area);                                 // :427
     tri_bbox(r, W, H, minX, maxX, minY, maxY);
-    return !(minX > maxX || minY > maxY);
+    if (minX > maxX || minY > maxY) return false;                 // :442
+    r.bx = (uint32_t)minX | ((uint32_t)maxX << 16);
+    r.by = (uint32_t)minY | ((uint32_t)maxY << 16);
+    return true;
 }
 
 // Full varyings of one corner, needed only inside the near clipper.
@@ -186,7 +186,7 @@ struct SetupOut {
 __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int vbase, const int i3[3],
                                            const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
                                            const FrameParams& fp, const SrbUniforms& U, uint32_t gtri,
-                                           TriRec* recs, ClipAttr* clipAttrs, Counters* cnt, SetupOut& out) {
+                                           const RecStore& recs, ClipAttr* clipAttrs, Counters* cnt, SetupOut& out) {
     const bool fma = U.numerics_fma != 0;
     ClipVtx v[3];
 #pragma unroll
@@ -247,7 +247,7 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int 
         clipAttrs[slot] = ca;
         r.meta = 0x80000000u | slot;
         uint32_t seq = 2u * gtri + (uint32_t)f;
-        recs[seq] = r;
+        store_rec(recs, seq, r);
         int k = out.n++;
         out.seq[k] = seq;
         out.tx[k] = (uint32_t)(minX / kTile) | ((uint32_t)(maxX / kTile) << 16);

@@ -14,17 +14,6 @@
 
 namespace srb {
 
-__device__ __forceinline__ TriRec load_rec(const TriRec* p) {
-    const float4* q = reinterpret_cast<const float4*>(p);
-    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
-    TriRec r;
-    r.s0x = a.x; r.s0y = a.y; r.s1x = a.z; r.s1y = a.w;
-    r.s2x = b.x; r.s2y = b.y; r.d0 = b.z; r.d1 = b.w;
-    r.d2 = c.x; r.cz0 = c.y; r.cz1 = c.z; r.cz2 = c.w;
-    r.cw0 = d.x; r.cw1 = d.y; r.cw2 = d.z; r.meta = __float_as_uint(d.w);
-    return r;
-}
-
 // Edge values at pixel (x,y) of the tile whose clipped bbox starts at
 // (startX,startY): direct formula at the start pixel, then dy rounded adds of
 // b and dx rounded adds of a -- the reference's accumulation order
@@ -107,8 +96,8 @@ ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     const uint32_t bs = A.tileStart[tile], be = A.tileEnd[tile];
     for (uint32_t ei = bs; ei < be; ++ei) {
         const uint32_t seq = __ldg(A.bins + ei);
-        const TriRec r = load_rec(A.recs + seq);
-        const TriEq e = tri_eq(r, fp.W, fp.H);
+        const TriRec r = load_rec(A.recs, seq);
+        const TriEq e = tri_eq(r);
         const int startX = max(e.minX, tx0), endX = min(e.maxX, tileEndX);
         const int startY = max(e.minY, ty0), endY = min(e.maxY, tileEndY);
         if (startX > endX || startY > endY) continue;            // uniform over the CTA
@@ -174,98 +163,120 @@ constexpr int kVisThreads = 128;
 constexpr int kVisWarps = kVisThreads / 32;
 constexpr int kVisFields = 15;
 
+struct VisSmem {
+    unsigned long long keys[kTile * kTile];
+    float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
+    int prefix[kVisThreads];               // exclusive prefix of rows per triangle
+    int warpRows[kVisWarps];
+};
+
+// One 16x16 tile, whole CTA.  Ends with every thread past its last shared-memory access
+// only after the caller's __syncthreads() (heavy-list CTAs loop over several tiles).
 template <int MODE>
-__global__ void __launch_bounds__(kVisThreads)
-vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
-    __shared__ unsigned long long keys[kTile * kTile];
-    __shared__ float soa[kVisWarps][kVisFields][32];
+__device__ __forceinline__ void vis_process_tile(const int tile, const RasterArgs& A, const FrameParams& fp,
+                                                 const SrbUniforms& U, VisSmem& sm) {
+    unsigned long long* keys = sm.keys;
+    float (*S)[kVisThreads] = sm.S;
+    int* prefix = sm.prefix;
+    int* warpRows = sm.warpRows;
     const unsigned full = 0xffffffffu;
-    if (A.cnt->overflow) return;
-    const int tile = fp.bandRow0 * fp.tilesX + blockIdx.x;
     const int tX = tile % fp.tilesX, tY = tile / fp.tilesX;
     const int tx0 = tX * kTile, ty0 = tY * kTile;
     const int tileEndX = min(tx0 + kTile - 1, fp.W - 1), tileEndY = min(ty0 + kTile - 1, fp.H - 1);
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const unsigned long long ckey = clear_key<MODE>();
-    for (int i = threadIdx.x; i < kTile * kTile; i += kVisThreads) keys[i] = ckey;
-    __syncthreads();
-
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t bs = A.tileStart[tile], be = A.tileEnd[tile];
-    float (*S)[32] = soa[wid];
-    for (uint32_t cb = bs + 32u * wid; cb < be; cb += 32u * kVisWarps) {
-        // ---- one triangle per lane: derive its raster constants for this tile ----
-        const bool valid = cb + lane < be;
+    const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
+
+    if (bs == be) {
+        // Empty bin: the fused clear is all there is (pure store bandwidth).
+        for (int p = tid; p < kTile * kTile; p += kVisThreads) {
+            const int x = tx0 + (p & 15), y = ty0 + (p >> 4);
+            if (x < fp.W && y < fp.H) {
+                const size_t pidx = (size_t)y * fp.W + x;
+                __stcs(A.color + pidx, clearCol);
+                __stcs(A.depth + pidx, kClearDepth);
+            }
+        }
+        return;
+    }
+
+    const unsigned long long ckey = clear_key<MODE>();
+    for (int i = tid; i < kTile * kTile; i += kVisThreads) keys[i] = ckey;
+
+    for (uint32_t cb = bs; cb < be; cb += kVisThreads) {
+        // ---- one triangle per thread: derive its raster constants for this tile ----
         int nrows = 0;
-        if (valid) {
-            const uint32_t seq = __ldg(A.bins + cb + lane);
-            const TriRec r = load_rec(A.recs + seq);
-            const TriEq e = tri_eq(r, fp.W, fp.H);
+        if (cb + tid < be) {
+            const uint32_t seq = __ldg(A.bins + cb + tid);
+            const TriRec r = load_rec_raster(A.recs, seq);
+            const TriEq e = tri_eq(r);
             const int startX = max(e.minX, tx0), endX = min(e.maxX, tileEndX);
             const int startY = max(e.minY, ty0), endY = min(e.maxY, tileEndY);
             if (startX <= endX && startY <= endY) {
                 nrows = endY - startY + 1;
                 float w0, w1, w2;
                 row_base(r, e, startX, startY, w0, w1, w2);
-                S[0][lane] = w0; S[1][lane] = w1; S[2][lane] = w2;
-                S[3][lane] = e.a12; S[4][lane] = e.a20; S[5][lane] = e.a01;
-                S[6][lane] = e.b12; S[7][lane] = e.b20; S[8][lane] = e.b01;
-                S[9][lane] = e.invArea;
-                S[10][lane] = r.d0; S[11][lane] = r.d1; S[12][lane] = r.d2;
-                S[13][lane] = __uint_as_float((uint32_t)(startX - tx0) | ((uint32_t)(endX - tx0) << 8) |
-                                              ((uint32_t)(startY - ty0) << 16));
-                S[14][lane] = __uint_as_float(seq);
+                S[0][tid] = w0; S[1][tid] = w1; S[2][tid] = w2;
+                S[3][tid] = e.a12; S[4][tid] = e.a20; S[5][tid] = e.a01;
+                S[6][tid] = e.b12; S[7][tid] = e.b20; S[8][tid] = e.b01;
+                S[9][tid] = e.invArea;
+                S[10][tid] = r.d0; S[11][tid] = r.d1; S[12][tid] = r.d2;
+                S[13][tid] = __uint_as_float((uint32_t)(startX - tx0) | ((uint32_t)(endX - tx0) << 8) |
+                                             ((uint32_t)(startY - ty0) << 16));
+                S[14][tid] = __uint_as_float(seq);
             }
         }
+        // ---- CTA-wide exclusive scan of the row counts ----
         int incl = nrows;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             int v = __shfl_up_sync(full, incl, o);
             if (lane >= o) incl += v;
         }
-        const int excl = incl - nrows;
-        const int total = __shfl_sync(full, incl, 31);
-        __syncwarp();
-        // ---- (triangle,row) work items, 32 at a time ----
-        for (int ib = 0; ib < total; ib += 32) {
-            const int i = ib + lane;
-            int j = 0, ej = 0;
+        if (lane == 31) warpRows[wid] = incl;
+        __syncthreads();
+        int woff = 0, total = 0;
 #pragma unroll
-            for (int s = 16; s > 0; s >>= 1) {
-                int cand = j + s;
-                int v = __shfl_sync(full, excl, cand & 31);
-                if (cand < 32 && v <= i) { j = cand; ej = v; }
-            }
-            if (i < total) {
-                const int dy = i - ej;
-                float w0 = S[0][j], w1 = S[1][j], w2 = S[2][j];
-                const float a12 = S[3][j], a20 = S[4][j], a01 = S[5][j];
-                const float b12 = S[6][j], b20 = S[7][j], b01 = S[8][j];
-                const float invArea = S[9][j], d0 = S[10][j], d1 = S[11][j], d2 = S[12][j];
-                const uint32_t pk = __float_as_uint(S[13][j]);
-                const uint32_t seq = __float_as_uint(S[14][j]);
-                const int sx = pk & 0xff, ex = (pk >> 8) & 0xff, row = (int)(pk >> 16) + dy;
-                for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
-                unsigned long long* krow = keys + row * kTile;
-                for (int xx = sx; xx <= ex; ++xx) {
-                    if (inside3(w0, w1, w2)) {
-                        float w0f, w1f, w2f;
-                        float depth = frag_depth(d0, d1, d2, invArea, w0, w1, w2, w0f, w1f, w2f);
-                        if (depth == depth) {                       // NaN never passes a depth test
-                            unsigned long long key = make_key<MODE>(depth, seq);
-                            if (key > krow[xx]) atomicMax(krow + xx, key);
-                        }
+        for (int w = 0; w < kVisWarps; ++w) {
+            const int v = warpRows[w];
+            if (w < wid) woff += v;
+            total += v;
+        }
+        prefix[tid] = woff + incl - nrows;
+        __syncthreads();
+        // ---- (triangle,row) work items spread over the whole CTA ----
+        for (int i = tid; i < total; i += kVisThreads) {
+            int j = 0;
+#pragma unroll
+            for (int s = kVisThreads / 2; s > 0; s >>= 1)
+                if (prefix[j + s] <= i) j += s;               // largest j with prefix[j] <= i (always has rows)
+            const int dy = i - prefix[j];
+            float w0 = S[0][j], w1 = S[1][j], w2 = S[2][j];
+            const float a12 = S[3][j], a20 = S[4][j], a01 = S[5][j];
+            const float b12 = S[6][j], b20 = S[7][j], b01 = S[8][j];
+            const float invArea = S[9][j], d0 = S[10][j], d1 = S[11][j], d2 = S[12][j];
+            const uint32_t pk = __float_as_uint(S[13][j]);
+            const uint32_t seq = __float_as_uint(S[14][j]);
+            const int sx = pk & 0xff, ex = (pk >> 8) & 0xff, row = (int)(pk >> 16) + dy;
+            for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
+            unsigned long long* krow = keys + row * kTile;
+            for (int xx = sx; xx <= ex; ++xx) {
+                if (inside3(w0, w1, w2)) {
+                    float w0f, w1f, w2f;
+                    float depth = frag_depth(d0, d1, d2, invArea, w0, w1, w2, w0f, w1f, w2f);
+                    if (depth == depth) {                       // NaN never passes a depth test
+                        unsigned long long key = make_key<MODE>(depth, seq);
+                        if (key > krow[xx]) atomicMax(krow + xx, key);
                     }
-                    w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
                 }
+                w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
             }
         }
-        __syncwarp();
+        __syncthreads();
     }
-    __syncthreads();
 
     // ---- resolve: shade each pixel's winner once, write colour + depth ----
-    const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
-    for (int p = threadIdx.x; p < kTile * kTile; p += kVisThreads) {
+    for (int p = tid; p < kTile * kTile; p += kVisThreads) {
         const int px = p & 15, py = p >> 4;
         const int x = tx0 + px, y = ty0 + py;
         if (x >= fp.W || y >= fp.H) continue;
@@ -276,8 +287,8 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
             uint32_t lo = (uint32_t)key, hi = (uint32_t)(key >> 32);
             const uint32_t seq = (MODE & 1) ? (0xfffffffeu - lo) : (lo - 1u);
             if (MODE >= 2) hi = ~hi;
-            const TriRec r = load_rec(A.recs + seq);
-            const TriEq e = tri_eq(r, fp.W, fp.H);
+            const TriRec r = load_rec(A.recs, seq);
+            const TriEq e = tri_eq(r);
             const int startX = max(e.minX, tx0), startY = max(e.minY, ty0);
             float w0, w1, w2, w0f, w1f, w2f;
             edge_chain(r, e, startX, startY, x, y, w0, w1, w2);
@@ -290,9 +301,17 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
             outd = ord2f(hi);
         }
         const size_t pidx = (size_t)y * fp.W + x;
-        A.color[pidx] = outc;
-        A.depth[pidx] = outd;
+        __stcs(A.color + pidx, outc);
+        __stcs(A.depth + pidx, outd);
     }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kVisThreads)
+vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
+    __shared__ VisSmem sm;
+    if (A.cnt->overflow) return;
+    vis_process_tile<MODE>((int)__ldg(A.order + blockIdx.x), A, fp, U, sm);
 }
 
 __global__ void texture_sample_kernel(const uchar4* __restrict__ tex, int tw, int th, const float2* __restrict__ uv,

@@ -8,13 +8,13 @@ namespace srb {
 // Everything the tile kernels need to reach per-frame data.
 struct RasterArgs {
     const DrawRec* draws;
-    const int32_t* tbase;
     const float4* wn;             // world normals from vertex_kernel
-    const TriRec* recs;
+    RecStore recs;
     const ClipAttr* clipAttrs;
     const uint32_t* tileStart;
     const uint32_t* tileEnd;      // == tileCursor after the fill pass
     uint32_t* bins;
+    const uint32_t* order;        // launch order of the band's tiles (scan kernel): heavy bins first
     float4* color;
     float* depth;
     const Counters* cnt;          // kernels bail out when a capacity overflowed (frame is re-run)

@@ -38,19 +38,21 @@ def main():
             ins = int(r[hdr.index("Instructions Executed")])
         except ValueError:
             continue
-        lines.append((smp, ins, fname, r[0], r[1].strip()))
+        stalls = sorted(((int(r[k]) if r[k].isdigit() else 0, hdr[k].replace("stall_", "")) for k in range(len(hdr))
+                         if hdr[k].startswith("stall_") and "Not Issued" not in hdr[k]), reverse=True)[:3]
+        lines.append((smp, ins, fname, r[0], r[1].strip(), " ".join(f"{n}:{v}" for v, n in stalls if v)))
     tot_s = sum(x[0] for x in lines) or 1
     tot_i = sum(x[1] for x in lines) or 1
     print(f"total samples {tot_s}, total warp instructions {tot_i}")
     byfile = {}
-    for s, i, f, _, _ in lines:
+    for s, i, f, *_ in lines:
         a = byfile.setdefault(f, [0, 0])
         a[0] += s
         a[1] += i
     for f, (s, i) in byfile.items():
         print(f"  {f:22s} samples {s / tot_s:6.1%}  instr {i / tot_i:6.1%}")
-    for s, i, f, ln, src in sorted(lines, reverse=True)[:top]:
-        print(f"{s:7d} {s / tot_s:6.1%} {i:10d} {i / tot_i:6.1%}  {f}:{ln:>4s}  {src[:110]}")
+    for s, i, f, ln, src, st in sorted(lines, reverse=True)[:top]:
+        print(f"{s:7d} {s / tot_s:6.1%} {i:10d} {i / tot_i:6.1%}  {f}:{ln:>4s}  {src[:90]}   [{st}]")
 
 
 if __name__ == "__main__":
