@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsrb200.so")
+# SRB200_LIB selects an alternative build of the same library (kernel A/B experiments); never a fallback.
+LIB_PATH = os.environ.get("SRB200_LIB") or os.path.join(_HERE, "libsrb200.so")
 
 SRB_OK = 0
 SRB_ERR_ARG, SRB_ERR_CUDA, SRB_ERR_HANDLE, SRB_ERR_STATE, SRB_ERR_UNSUPPORTED = -1, -2, -3, -4, -5

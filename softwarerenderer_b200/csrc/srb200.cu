@@ -74,6 +74,7 @@ struct SrbContext {
     DevBuf<float4> dRecsR, dRecsS;    // split setup records (RecStore)
     DevBuf<TriRef> dRefs;
     DevBuf<ClipAttr> dClipAttrs;
+    DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
     DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dOrder, dBins, dBinScratch;
     Counters* dCnt = nullptr;
     Counters* hCnt = nullptr;         // pinned
@@ -161,13 +162,14 @@ int launch_frame(SrbContext* c) {
     mark(2);
     if (c->nTBlocks > 0) {
         setup_kernel<<<c->nTBlocks, kGeomBlock, 0, c->stream>>>(
-            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, c->dWn.p, RecStore{c->dRecsR.p, c->dRecsS.p}, c->dClipAttrs.p, c->dRefs.p,
+            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, c->dWn.p, RecStore{c->dRecsR.p, c->dRecsS.p}, c->dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
             c->dTileCount.p, c->dCnt);
-        ++launches;
+        bin_big_kernel<0><<<c->smCount * 4, 256, 0, c->stream>>>(c->dBigQ.p, c->dCnt, fp, c->dTileCount.p, nullptr);
+        launches += 2;
     }
     mark(3);
     if (bandTiles > 0) {
-        scan_tiles_kernel<<<1, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, c->dOrder.p,
+        scan_tiles_kernel<<<kScanCtas, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, c->dOrder.p,
                                                      fp.bandRow0 * fp.tilesX, bandTiles, c->dCnt, fp.pairCap);
         ++launches;
     }
@@ -177,7 +179,8 @@ int launch_frame(SrbContext* c) {
         size_t maxRefs = 2 * (size_t)fp.totalT;
         unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
         fill_bins_kernel<<<grid, 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
-        ++launches;
+        bin_big_kernel<1><<<c->smCount * 4, 256, 0, c->stream>>>(c->dBigQ.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
+        launches += 2;
     }
     mark(5);
     RasterArgs A;
@@ -231,6 +234,10 @@ int complete_frame(SrbContext* c) {
             size_t want = std::max<size_t>(4 * (size_t)k.nClipped, 4096);
             CK(c, c->dClipAttrs.reserve(want));
             c->fp.clipCap = (uint32_t)c->dClipAttrs.cap;
+        }
+        if (k.overflow & 4u) {
+            CK(c, c->dBigQ.reserve((size_t)k.nBig + k.nBig / 4 + 1024));
+            c->fp.bigCap = (uint32_t)c->dBigQ.cap;
         }
         int rc = launch_frame(c);
         if (rc != SRB_OK) return rc;
@@ -307,7 +314,7 @@ int srb_destroy(SrbContext* c) {
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
     c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dOrder.release(); c->dClip.release(); c->dWn.release();
-    c->dRecsR.release(); c->dRecsS.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dTileCount.release();
+    c->dRecsR.release(); c->dRecsS.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dBigQ.release(); c->dTileCount.release();
     c->dTileStart.release(); c->dTileCursor.release(); c->dBins.release(); c->dBinScratch.release();
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
@@ -599,6 +606,7 @@ int srb_end_frame(SrbContext* c) {
     CK(c, c->dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
     CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
     CK(c, c->dClipAttrs.reserve(4096));
+    CK(c, c->dBigQ.reserve(1u << 16));
     CK(c, c->dTileCount.reserve(nTiles));
     CK(c, c->dTileStart.reserve(nTiles));
     CK(c, c->dTileCursor.reserve(nTiles));
@@ -616,6 +624,7 @@ int srb_end_frame(SrbContext* c) {
     fp.nDraws = nDraws; fp.totalV = (int)totalV; fp.totalT = (int)totalT;
     fp.pairCap = (uint32_t)std::min<size_t>(c->dBins.cap, 0xffffffffu);
     fp.clipCap = (uint32_t)c->dClipAttrs.cap;
+    fp.bigCap = (uint32_t)c->dBigQ.cap;
     std::memcpy(fp.clearColor, c->clear, 16);
     fp.loadColor = (c->clearFlags & SRB_CLEAR_COLOR) ? 0 : 1;
     fp.loadDepth = (c->clearFlags & SRB_CLEAR_DEPTH) ? 0 : 1;

@@ -9,7 +9,10 @@ namespace srb {
 // scans, fill scatters.  Distant instances put thousands of consecutive
 // triangles into the same tile, so per-tile atomics are warp-aggregated with
 // match.any: one atomic per distinct tile per warp instead of one per lane.
-constexpr int kSmallTiles = 4;     // triangles touching <= this many tiles are walked by their own lane
+
+__device__ __forceinline__ int tile_range_count(uint32_t tx, uint32_t ty) {
+    return ((int)(tx >> 16) - (int)(tx & 0xffff) + 1) * ((int)(ty >> 16) - (int)(ty & 0xffff) + 1);
+}
 
 // k-th tile of a packed range (row-major), or -1.
 __device__ __forceinline__ int small_tile(uint32_t tx, uint32_t ty, int n, int k, int tilesX) {
@@ -19,55 +22,78 @@ __device__ __forceinline__ int small_tile(uint32_t tx, uint32_t ty, int n, int k
     return (y0 + yy) * tilesX + x0 + xx;
 }
 
-// Visit every tile of the accepted triangles held by the lanes of one warp.
-// MODE 0 = count (tileCount += 1), MODE 1 = fill (bins[cursor++] = seq).
-// All 32 lanes must call this.
+// Small triangles (<= kSmallTiles tiles) go through a CTA-wide aggregation table in shared
+// memory: (tile -> number of pairs from this CTA), open addressing keyed by the tile id.  Distant
+// instances put thousands of consecutive triangles into the same few tiles, and atomics on one
+// L2 address retire serially (tens of ns each): aggregated per CTA, a hot tile receives one
+// global atomic per CTA instead of one per triangle.
+constexpr int kAggSlots = 1024;            // >= the small pairs one CTA pass can produce (256 threads x 4)
+struct TileAgg {
+    uint32_t key[kAggSlots];               // tile + 1, 0 = empty
+    uint32_t val[kAggSlots];               // pairs counted; in fill mode replaced by the bin offset of the run
+};
+__device__ __forceinline__ void agg_clear(TileAgg& a) {
+    for (int i = threadIdx.x; i < kAggSlots; i += blockDim.x) { a.key[i] = 0u; a.val[i] = 0u; }
+}
+// Returns slot | rank << 16 (rank = position of this pair within the CTA's run for that tile).
+__device__ __forceinline__ uint32_t agg_insert(TileAgg& a, int tile) {
+    uint32_t h = (uint32_t)tile & (kAggSlots - 1);
+    const uint32_t want = (uint32_t)tile + 1u;
+    while (true) {
+        const uint32_t k = atomicCAS(&a.key[h], 0u, want);
+        if (k == 0u || k == want) break;
+        h = (h + 1u) & (kAggSlots - 1);
+    }
+    return h | (atomicAdd(&a.val[h], 1u) << 16);
+}
+// One global atomic per distinct tile.  Count mode adds to tileCount; fill mode reserves the run
+// in the bin and leaves its offset in val[].
 template <int MODE>
-__device__ __forceinline__ void warp_bin_tiles(bool valid, uint32_t seq, uint32_t tx, uint32_t ty, int tilesX,
-                                               uint32_t* __restrict__ tileCounter, uint32_t* __restrict__ bins,
-                                               uint32_t cap) {
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const int x0 = tx & 0xffff, x1 = tx >> 16, y0 = ty & 0xffff, y1 = ty >> 16;
-    const int nx = x1 - x0 + 1, n = valid ? nx * (y1 - y0 + 1) : 0;
-    const int nSmall = n <= kSmallTiles ? n : 0;
-    int maxSmall = nSmall;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) maxSmall = max(maxSmall, __shfl_xor_sync(full, maxSmall, o));
-    for (int k = 0; k < maxSmall; ++k) {
-        const int tile = small_tile(tx, ty, nSmall, k, tilesX);
-        const unsigned grp = __match_any_sync(full, tile);
-        if (tile >= 0) {
-            const int leader = __ffs(grp) - 1;
-            const int cnt = __popc(grp);
-            if (MODE == 0) {
-                if (lane == leader) atomicAdd(tileCounter + tile, (uint32_t)cnt);
-            } else {
-                uint32_t base = 0;
-                if (lane == leader) base = atomicAdd(tileCounter + tile, (uint32_t)cnt);
-                base = __shfl_sync(grp, base, leader);
-                const uint32_t slot = base + (uint32_t)__popc(grp & ((1u << lane) - 1u));
-                if (slot < cap) bins[slot] = seq;
-            }
+__device__ __forceinline__ void agg_flush(TileAgg& a, uint32_t* __restrict__ tileCounter) {
+    for (int i = threadIdx.x; i < kAggSlots; i += blockDim.x) {
+        const uint32_t k = a.key[i];
+        if (k) {
+            const uint32_t base = atomicAdd(tileCounter + (k - 1u), a.val[i]);
+            if (MODE == 1) a.val[i] = base;
         }
     }
-    // Larger triangles: the whole warp walks one triangle's tiles (distinct
-    // addresses per lane), four atomics in flight per lane.
-    unsigned big = __ballot_sync(full, n > kSmallTiles);
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const int bx0 = __shfl_sync(full, x0, src), by0 = __shfl_sync(full, y0, src);
-        const int bnx = __shfl_sync(full, nx, src), bn = __shfl_sync(full, n, src);
-        const uint32_t bseq = __shfl_sync(full, seq, src);
-        for (int i0 = lane; i0 < bn; i0 += 128) {
+}
+
+// Large triangles (more than kSmallTiles tiles) are appended to a global queue by the setup
+// kernel and binned by their own kernel, one warp per triangle and one lane per tile of its
+// bounding box, four atomics in flight per lane.  Nearby meshes are runs of hundreds of large
+// triangles: handled inside the CTA that owns them they made a 40 us tail; as a queue they
+// spread over every SM.  Each (triangle, tile) pair passes the conservative tile test first
+// (about a quarter of the bbox tiles of large triangles drop out).
+// MODE 0 = count (tileCount += 1), MODE 1 = fill (bins[cursor++] = seq).
+template <int MODE>
+__global__ void __launch_bounds__(256)
+bin_big_kernel(const BigEntry* __restrict__ q, const Counters* __restrict__ cnt, FrameParams fp,
+               uint32_t* __restrict__ tileCounter, uint32_t* __restrict__ bins) {
+    if (cnt->overflow) return;
+    const uint32_t nq = min(cnt->nBig, fp.bigCap);
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nWarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t e = warp; e < nq; e += nWarps) {
+        const float4* p = reinterpret_cast<const float4*>(q + e);
+        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+        const uint32_t bx = __float_as_uint(b.z), by = __float_as_uint(b.w);
+        const uint32_t seq = __float_as_uint(c.x), tx = __float_as_uint(c.y), ty = __float_as_uint(c.z);
+        const int x0 = tx & 0xffff, nx = (int)(tx >> 16) - x0 + 1, y0 = ty & 0xffff;
+        const int n = nx * ((int)(ty >> 16) - y0 + 1);
+        const int minX = bx & 0xffffu, maxX = bx >> 16, minY = by & 0xffffu, maxY = by >> 16;
+        for (int i0 = lane; i0 < n; i0 += 128) {
             int tile[4];
             uint32_t slot[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int i = i0 + 32 * u;
-                const int yy = i / bnx, xx = i - yy * bnx;
-                tile[u] = i < bn ? (by0 + yy) * tilesX + bx0 + xx : -1;
+                const int yy = i / nx, xx = i - yy * nx;
+                const int tX = x0 + xx, tY = y0 + yy;
+                const bool keep = i < n && tile_may_cover(a.x, a.y, a.z, a.w, b.x, b.y,
+                                                          max(minX, tX * kTile), min(maxX, tX * kTile + kTile - 1),
+                                                          max(minY, tY * kTile), min(maxY, tY * kTile + kTile - 1));
+                tile[u] = keep ? tY * fp.tilesX + tX : -1;
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -78,7 +104,7 @@ __device__ __forceinline__ void warp_bin_tiles(bool valid, uint32_t seq, uint32_
             if (MODE == 1) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
-                    if (tile[u] >= 0 && slot[u] < cap) bins[slot[u]] = bseq;
+                    if (tile[u] >= 0 && slot[u] < fp.pairCap) bins[slot[u]] = seq;
             }
         }
     }
@@ -92,16 +118,20 @@ __device__ __forceinline__ void warp_bin_tiles(bool valid, uint32_t seq, uint32_
 // shader hoisted into vertex_kernel: behind tests, optional near clip,
 // DrawTriangle, cull, bbox; then per-tile counting for the bins.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(kGeomBlock)
+__global__ void __launch_bounds__(kGeomBlock, 8)
 setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks, FrameParams fp,
              SrbUniforms U, const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
-             RecStore recs, ClipAttr* __restrict__ clipAttrs, TriRef* __restrict__ refs,
+             RecStore recs, ClipAttr* __restrict__ clipAttrs, TriRef* __restrict__ refs, BigEntry* __restrict__ bigQ,
              uint32_t* __restrict__ tileCount, Counters* cnt) {
     const unsigned full = 0xffffffffu;
+    __shared__ TileAgg agg;
     const int2 blk = __ldg(tblocks + blockIdx.x);
     const int di = blk.x;
     const DrawRec& d = draws[di];
     if (!d.visible) return;                                   // uniform over the CTA
+    agg_clear(agg);
+    __syncthreads();
+    const BigQueue bq{bigQ, cnt, fp.bigCap};
     const int t = blk.y + threadIdx.x;
     SetupOut out;
     out.n = 0;
@@ -114,26 +144,18 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         if (b0 && b1 && b2) {
             // all behind: dropped (:212-215)
         } else if (b0 || b1 || b2) {
-            setup_clipped(d, di, d.vbase, i3, clipIn, wnIn, fp, U, (uint32_t)g, recs, clipAttrs, cnt, out);
+            setup_clipped(d, di, d.vbase, i3, clipIn, wnIn, fp, U, (uint32_t)g, recs, clipAttrs, cnt, bq, out);
         } else {
             float4 c[3] = {c2, c1, c0};                                    // :367
             TriRec r;
             int minX, maxX, minY, maxY;
             if (setup_tri(c, fp.W, fp.H, d.cull, r, minX, maxX, minY, maxY)) {
-                int ty0 = max(minY / kTile, fp.bandRow0), ty1 = min(maxY / kTile, fp.bandRow1 - 1);
-                if (ty0 <= ty1) {
-                    r.meta = (uint32_t)di;
-                    uint32_t seq = 2u * (uint32_t)g;
-                    store_rec(recs, seq, r);
-                    out.n = 1;
-                    out.seq[0] = seq;
-                    out.tx[0] = (uint32_t)(minX / kTile) | ((uint32_t)(maxX / kTile) << 16);
-                    out.ty[0] = (uint32_t)ty0 | ((uint32_t)ty1 << 16);
-                }
+                r.meta = (uint32_t)di;
+                accept_tri(r, 2u * (uint32_t)g, minX, maxX, minY, maxY, fp, recs, bq, out);
             }
         }
     }
-    // Warp-aggregated append to the compact accepted-triangle list.
+    // Warp-aggregated append to the compact accepted-triangle list (the fill pass walks it).
     const int lane = threadIdx.x & 31;
     int n = out.n;
     int incl = n;
@@ -143,19 +165,24 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         if (lane >= o) incl += v;
     }
     int total = __shfl_sync(full, incl, 31);
-    if (total == 0) return;                                   // uniform over the warp
-    uint32_t base = 0;
-    if (lane == 31) base = atomicAdd(&cnt->nRefs, (uint32_t)total);
-    base = __shfl_sync(full, base, 31);
-    for (int k = 0; k < n; ++k) {
-        TriRef rf;
-        rf.seq = out.seq[k]; rf.tx = out.tx[k]; rf.ty = out.ty[k]; rf._pad = 0;
-        refs[base + (uint32_t)(incl - n + k)] = rf;
+    if (total > 0) {                                          // uniform over the warp
+        uint32_t base = 0;
+        if (lane == 31) base = atomicAdd(&cnt->nRefs, (uint32_t)total);
+        base = __shfl_sync(full, base, 31);
+        for (int k = 0; k < n; ++k) {
+            TriRef rf;
+            rf.seq = out.seq[k]; rf.tx = out.tx[k]; rf.ty = out.ty[k]; rf._pad = 0;
+            refs[base + (uint32_t)(incl - n + k)] = rf;
+        }
     }
-    // Count pass.
-    warp_bin_tiles<0>(out.n > 0, out.seq[0], out.tx[0], out.ty[0], fp.tilesX, tileCount, nullptr, 0u);
-    if (__ballot_sync(full, out.n > 1))
-        warp_bin_tiles<0>(out.n > 1, out.seq[1], out.tx[1], out.ty[1], fp.tilesX, tileCount, nullptr, 0u);
+    // Count pass: small triangles through the aggregation table (large ones: bin_big_kernel<0>).
+    for (int k = 0; k < out.n; ++k) {
+        const int nt = tile_range_count(out.tx[k], out.ty[k]);
+        if (nt <= kSmallTiles)
+            for (int j = 0; j < nt; ++j) agg_insert(agg, small_tile(out.tx[k], out.ty[k], nt, j, fp.tilesX));
+    }
+    __syncthreads();
+    agg_flush<0>(agg, tileCount);
 }
 
 // ---------------------------------------------------------------------------
@@ -177,43 +204,64 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
     return v;
 }
 
-// All accesses are lane-contiguous: a single SM retires about one memory request per cycle,
-// so a per-thread strided layout (32 sectors per instruction) would bound this kernel.
-__global__ void __launch_bounds__(1024)
+// One thread-block cluster of kScanCtas CTAs (one launch, one cluster barrier): CTA r owns a
+// contiguous range of tiles, totals are exchanged through distributed shared memory.  All
+// accesses are lane-contiguous: an SM retires about one memory request per cycle, so a
+// per-thread strided layout (32 sectors per instruction) would bound this kernel.
+constexpr int kScanCtas = 8;
+
+__global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
 scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
                   uint32_t* __restrict__ tileCursor, uint32_t* __restrict__ order, int tile0, int nTiles,
                   Counters* cnt, uint32_t pairCap) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
     __shared__ uint32_t wsum[3][32];
-    __shared__ uint32_t tot[2];
+    __shared__ uint32_t ctaTot[3];                      // this CTA's range totals: pairs, heavy, medium (read remotely)
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int tileEnd = tile0 + nTiles;
-    // pass 1: how many heavy / medium tiles the band has (fixes the three regions of order[])
-    uint32_t nh = 0, nm = 0;
-    for (int i = tile0 + (int)threadIdx.x; i < tileEnd; i += 1024) {
-        const uint32_t c = __ldg(tileCount + i);
-        nh += c >= kHeavyBin;
-        nm += (c >= kMediumBin && c < kHeavyBin);
+    const int rank = (int)cluster.block_rank();
+    const int per = (((nTiles + kScanCtas - 1) / kScanCtas) + 31) & ~31;
+    const int r0 = min(tile0 + rank * per, tile0 + nTiles), r1 = min(r0 + per, tile0 + nTiles);
+    // phase 1: totals of this CTA's range
+    uint32_t ns = 0, nh = 0, nm = 0;
+    for (int i0 = r0 + (int)threadIdx.x; i0 < r1; i0 += 4 * 1024) {
+        uint32_t c[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) c[u] = i0 + u * 1024 < r1 ? __ldg(tileCount + i0 + u * 1024) : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            ns += c[u];
+            nh += c[u] >= kHeavyBin;
+            nm += (c[u] >= kMediumBin && c[u] < kHeavyBin);
+        }
     }
-    nh = warp_sum(nh); nm = warp_sum(nm);
-    if (lane == 0) { wsum[0][wid] = nh; wsum[1][wid] = nm; }
+    ns = warp_sum(ns); nh = warp_sum(nh); nm = warp_sum(nm);
+    if (lane == 0) { wsum[0][wid] = ns; wsum[1][wid] = nh; wsum[2][wid] = nm; }
     __syncthreads();
     if (wid == 0) {
-        uint32_t a = warp_sum(wsum[0][lane]), b = warp_sum(wsum[1][lane]);
-        if (lane == 0) { tot[0] = a; tot[1] = b; }
+        uint32_t a = warp_sum(wsum[0][lane]), b = warp_sum(wsum[1][lane]), d = warp_sum(wsum[2][lane]);
+        if (lane == 0) { ctaTot[0] = a; ctaTot[1] = b; ctaTot[2] = d; }
     }
-    __syncthreads();
-    const uint32_t th = tot[0], tm = tot[1];
-    // pass 2: offsets and order, chunk by chunk; warp w owns kScanIters*32 consecutive tiles of the chunk
-    uint32_t carry = 0, carryH = 0, carryM = 0;
-    for (int chunk = tile0; chunk < tileEnd; chunk += 1024 * kScanIters) {
+    cluster.sync();
+    uint32_t carry = 0, carryH = 0, carryM = 0, tp = 0, th = 0, tm = 0;
+#pragma unroll
+    for (int r = 0; r < kScanCtas; ++r) {
+        const uint32_t* t = cluster.map_shared_rank(ctaTot, r);
+        const uint32_t a = t[0], b = t[1], d = t[2];
+        if (r < rank) { carry += a; carryH += b; carryM += d; }
+        tp += a; th += b; tm += d;
+    }
+    cluster.sync();                                     // nobody leaves (or reuses wsum) while its totals are being read
+    // phase 2: offsets and order; warp w owns kScanIters*32 consecutive tiles of each chunk
+    for (int chunk = r0; chunk < r1; chunk += 1024 * kScanIters) {
         const int wb = chunk + wid * (32 * kScanIters);
         uint32_t c[kScanIters];
         uint32_t sum = 0, sh = 0, smd = 0;
 #pragma unroll
         for (int k = 0; k < kScanIters; ++k) {
             const int i = wb + k * 32 + lane;
-            c[k] = i < tileEnd ? __ldg(tileCount + i) : 0u;
+            c[k] = i < r1 ? __ldg(tileCount + i) : 0u;
             sum += c[k];
             sh += c[k] >= kHeavyBin;
             smd += (c[k] >= kMediumBin && c[k] < kHeavyBin);
@@ -229,7 +277,8 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
             run += warp_sum(a & below); oh += warp_sum(b & below); om += warp_sum(d & below);
             carry += warp_sum(a); carryH += warp_sum(b); carryM += warp_sum(d);
         }
-        uint32_t orest = (uint32_t)(min(wb, tileEnd) - tile0) - oh - om;      // earlier tiles that are neither
+        uint32_t orest = (uint32_t)(min(wb, r1) - tile0) - oh - om;      // earlier tiles that are neither
+        if (wb >= r1) continue;                            // (uniform per warp; no barrier below)
 #pragma unroll
         for (int k = 0; k < kScanIters; ++k) {
             const int i = wb + k * 32 + lane;
@@ -239,7 +288,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
                 uint32_t t = __shfl_up_sync(full, incl, o);
                 if (lane >= o) incl += t;
             }
-            const bool valid = i < tileEnd;
+            const bool valid = i < r1;
             const bool hv = valid && c[k] >= kHeavyBin, md = valid && c[k] >= kMediumBin && !hv;
             const unsigned mh = __ballot_sync(full, hv), mm = __ballot_sync(full, md), mv = __ballot_sync(full, valid);
             const unsigned lt = (1u << lane) - 1u;
@@ -257,9 +306,9 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
             oh += __popc(mh); om += __popc(mm); orest += __popc(mv & ~mh & ~mm);
         }
     }
-    if (threadIdx.x == 0) {
-        cnt->nPairs = carry;
-        if (carry > pairCap) atomicOr(&cnt->overflow, 1u);
+    if (rank == 0 && threadIdx.x == 0) {
+        cnt->nPairs = tp;
+        if (tp > pairCap) atomicOr(&cnt->overflow, 1u);
     }
 }
 
@@ -271,14 +320,32 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
 __global__ void __launch_bounds__(256)
 fill_bins_kernel(const TriRef* __restrict__ refs, const Counters* __restrict__ cnt, FrameParams fp,
                  uint32_t* __restrict__ tileCursor, uint32_t* __restrict__ bins) {
+    __shared__ TileAgg agg;
     const uint32_t nRefs = cnt->nRefs;
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; (i & ~31u) < nRefs; i += stride) {
-        const bool valid = i < nRefs;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < nRefs; base += stride) {     // uniform over the CTA
+        agg_clear(agg);
+        __syncthreads();
+        const uint32_t i = base + threadIdx.x;
         TriRef rf;
         rf.seq = 0; rf.tx = 0; rf.ty = 0; rf._pad = 0;
-        if (valid) rf = refs[i];
-        warp_bin_tiles<1>(valid, rf.seq, rf.tx, rf.ty, fp.tilesX, tileCursor, bins, fp.pairCap);
+        if (i < nRefs) rf = refs[i];
+        const int nt = i < nRefs ? tile_range_count(rf.tx, rf.ty) : 0;
+        const int nSmall = nt <= kSmallTiles ? nt : 0;              // large ones: bin_big_kernel<1>
+        uint32_t where[kSmallTiles];
+#pragma unroll
+        for (int j = 0; j < kSmallTiles; ++j)
+            if (j < nSmall) where[j] = agg_insert(agg, small_tile(rf.tx, rf.ty, nSmall, j, fp.tilesX));
+        __syncthreads();
+        agg_flush<1>(agg, tileCursor);
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < kSmallTiles; ++j)
+            if (j < nSmall) {
+                const uint32_t slot = agg.val[where[j] & 0xffffu] + (where[j] >> 16);
+                if (slot < fp.pairCap) bins[slot] = rf.seq;
+            }
+        __syncthreads();
     }
 }
 

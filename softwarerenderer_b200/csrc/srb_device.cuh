@@ -7,6 +7,7 @@
 // The TU is additionally compiled with -fmad=false.  Fused operations appear
 // only where System.Numerics fuses (numerics_fma switch).
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/srb200.h"
@@ -257,6 +258,58 @@ __device__ __forceinline__ float frag_depth(float d0, float d1, float d2, float 
                                             float& w0f, float& w1f, float& w2f) {
     w0f = mul(w0, invArea); w1f = mul(w1, invArea); w2f = mul(w2, invArea);
     return add(add(mul(d0, w0f), mul(d1, w1f)), mul(d2, w2f));
+}
+
+// ---------------------------------------------------------------------------
+// Conservative triangle-vs-tile rejection (used when binning triangles that span many tiles).
+// Returns false only when NO pixel of [X0..X1]x[Y0..Y1] can pass the reference's inclusive test
+// (Rasterizer.cs:493-494) under its rounded, accumulated edge values.
+//
+// Proof sketch.  Let W_i(x,y) = a_i*(x-p_ix) + b_i*(y-p_iy) in real arithmetic on the float
+// constants a_i, b_i, p_i.  Every value the reference forms for a pixel of the region -- the
+// direct row base (:481-483) and each partial sum of its <= 15 + 15 rounded adds (:527-534) --
+// is W_i at a lattice point of the region up to accumulated rounding, so it is bounded by
+// B_i = max|a_i*(x-p_ix)| + max|b_i*(y-p_iy)| and the <= 35 roundings on the way add at most
+// 35*2^-24*B_i.  The corner values below are computed with 3 roundings (<= 3*2^-24*B_i) and
+// W_i is affine, so its extremes over the region are at the corners.  With E_i = 2^-16*B_i
+// (six times the sum of both error terms):
+//   max_corners W_i < -E_i for some i   =>  the reference's w_i < 0 everywhere: "all >= 0" fails;
+//   min_corners W_j > +E_j for some j   =>  "all <= 0" fails;
+//   min_corners (W_0+W_1+W_2) > sum E   =>  the three cannot all be <= 0 ("all <= 0" fails),
+//   max_corners (W_0+W_1+W_2) < -sum E  =>  "all >= 0" fails.
+// Both alternatives of the test failing means no pixel of the region is covered.  Any NaN/Inf
+// or huge magnitude makes every comparison false => the tile is kept.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ bool tile_may_cover(float s0x, float s0y, float s1x, float s1y, float s2x, float s2y,
+                                               int X0, int X1, int Y0, int Y1) {
+    const float fx0 = (float)X0, fx1 = (float)X1, fy0 = (float)Y0, fy1 = (float)Y1;
+    const float a[3] = {sub(s1y, s2y), sub(s2y, s0y), sub(s0y, s1y)};     // a12, a20, a01
+    const float b[3] = {sub(s2x, s1x), sub(s0x, s2x), sub(s1x, s0x)};     // b12, b20, b01
+    const float px[3] = {s1x, s2x, s0x}, py[3] = {s1y, s2y, s0y};
+    float sum[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    float sumE = 0.0f;
+    bool someNeg = false, somePos = false, sane = true;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const float ax0 = mul(a[i], sub(fx0, px[i])), ax1 = mul(a[i], sub(fx1, px[i]));
+        const float by0 = mul(b[i], sub(fy0, py[i])), by1 = mul(b[i], sub(fy1, py[i]));
+        const float w00 = add(ax0, by0), w10 = add(ax1, by0), w01 = add(ax0, by1), w11 = add(ax1, by1);
+        const float B = add(fmaxf(fabsf(ax0), fabsf(ax1)), fmaxf(fabsf(by0), fabsf(by1)));
+        const float E = mul(B, 1.52587890625e-05f);                       // 2^-16
+        sane = sane && (B < 1e30f);                                       // false for NaN as well
+        const float wmax = fmaxf(fmaxf(w00, w10), fmaxf(w01, w11));
+        const float wmin = fminf(fminf(w00, w10), fminf(w01, w11));
+        someNeg = someNeg || (wmax < -E);
+        somePos = somePos || (wmin > E);
+        sum[0] = add(sum[0], w00); sum[1] = add(sum[1], w10); sum[2] = add(sum[2], w01); sum[3] = add(sum[3], w11);
+        sumE = add(sumE, E);
+    }
+    if (!sane) return true;
+    const float smax = fmaxf(fmaxf(sum[0], sum[1]), fmaxf(sum[2], sum[3]));
+    const float smin = fminf(fminf(sum[0], sum[1]), fminf(sum[2], sum[3]));
+    const bool geImpossible = someNeg || (smax < -sumE);
+    const bool leImpossible = somePos || (smin > sumE);
+    return !(geImpossible && leImpossible);
 }
 
 }  // namespace srb

@@ -14,6 +14,7 @@ struct FrameParams {
     int totalV, totalT;
     uint32_t pairCap;             // capacity of the bin array
     uint32_t clipCap;             // capacity of the ClipAttr side buffer
+    uint32_t bigCap;              // capacity of the large-triangle queue
     float clearColor[4];
     int loadColor, loadDepth;     // 1 = keep existing framebuffer contents (no clear this frame)
     int depthMode;                // visibility path: the frame's common depth test
@@ -25,9 +26,10 @@ struct Counters {
     uint32_t nPairs;              // total (triangle,tile) pairs (from the scan)
     uint32_t nClipped;            // ClipAttr entries used
     uint32_t nClippedTris;        // triangles that entered the clipper
-    uint32_t overflow;            // bit0: bins, bit1: clip side buffer
+    uint32_t overflow;            // bit0: bins, bit1: clip side buffer, bit2: large-triangle queue
     uint32_t nVisibleDraws;
-    uint32_t _pad[2];
+    uint32_t nBig;                // entries in the large-triangle queue
+    uint32_t _pad;
 };
 
 // ---------------------------------------------------------------------------
@@ -176,17 +178,56 @@ __device__ __forceinline__ ClipVtx clipvtx_lerp(const ClipVtx& a, const ClipVtx&
 }
 
 // Result of per-thread setup handed to the binning helpers.
+// Screen-space geometry of an accepted triangle, kept for the conservative tile test applied
+// when a triangle that spans many tiles is binned (tile_may_cover).
+struct BinGeom {
+    float s0x, s0y, s1x, s1y, s2x, s2y;
+    uint32_t bx, by;       // clamped pixel bbox, packed as in TriRec
+};
 struct SetupOut {
     int n;                 // accepted triangles of this thread (0..2)
     uint32_t seq[2];
     uint32_t tx[2], ty[2]; // packed tile ranges
 };
+// Triangles that span more than kSmallTiles tiles are queued in shared memory and binned by the
+// whole CTA (cta_bin_big).
+constexpr int kSmallTiles = 4;
+struct __align__(16) BigEntry {
+    BinGeom g;
+    uint32_t seq, tx, ty, _pad;
+};
+static_assert(sizeof(BigEntry) == 48, "BigEntry is read as three float4");
+struct BigQueue {
+    BigEntry* q;
+    Counters* cnt;
+    uint32_t cap;
+};
+// Common tail of the accepted-triangle paths: band clamp, record store, big-queue push.
+__device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int minX, int maxX, int minY, int maxY,
+                                           const FrameParams& fp, const RecStore& recs, const BigQueue& bq,
+                                           SetupOut& out) {
+    const int ty0 = max(minY / kTile, fp.bandRow0), ty1 = min(maxY / kTile, fp.bandRow1 - 1);
+    if (ty0 > ty1) return;
+    store_rec(recs, seq, r);
+    const int k = out.n++;
+    out.seq[k] = seq;
+    out.tx[k] = (uint32_t)(minX / kTile) | ((uint32_t)(maxX / kTile) << 16);
+    out.ty[k] = (uint32_t)ty0 | ((uint32_t)ty1 << 16);
+    if ((maxX / kTile - minX / kTile + 1) * (ty1 - ty0 + 1) > kSmallTiles) {
+        const uint32_t slot = atomicAdd(&bq.cnt->nBig, 1u);
+        if (slot >= bq.cap) { atomicOr(&bq.cnt->overflow, 4u); return; }
+        BigEntry& e = bq.q[slot];
+        e.g = BinGeom{r.s0x, r.s0y, r.s1x, r.s1y, r.s2x, r.s2y, r.bx, r.by};
+        e.seq = seq; e.tx = out.tx[k]; e.ty = out.ty[k]; e._pad = 0u;
+    }
+}
 
 // Near-clipped triangle (Rasterizer.cs:95-160, 217-224).  Rare and divergent.
 __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int vbase, const int i3[3],
                                            const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
                                            const FrameParams& fp, const SrbUniforms& U, uint32_t gtri,
-                                           const RecStore& recs, ClipAttr* clipAttrs, Counters* cnt, SetupOut& out) {
+                                           const RecStore& recs, ClipAttr* clipAttrs, Counters* cnt, const BigQueue& bq,
+                                           SetupOut& out) {
     const bool fma = U.numerics_fma != 0;
     ClipVtx v[3];
 #pragma unroll
@@ -246,12 +287,7 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int 
         ca.draw = drawIndex;
         clipAttrs[slot] = ca;
         r.meta = 0x80000000u | slot;
-        uint32_t seq = 2u * gtri + (uint32_t)f;
-        store_rec(recs, seq, r);
-        int k = out.n++;
-        out.seq[k] = seq;
-        out.tx[k] = (uint32_t)(minX / kTile) | ((uint32_t)(maxX / kTile) << 16);
-        out.ty[k] = (uint32_t)ty0 | ((uint32_t)ty1 << 16);
+        accept_tri(r, 2u * gtri + (uint32_t)f, minX, maxX, minY, maxY, fp, recs, bq, out);
     }
 }
 

@@ -163,6 +163,28 @@ constexpr int kVisThreads = 128;
 constexpr int kVisWarps = kVisThreads / 32;
 constexpr int kVisFields = 15;
 
+// Walk one row of one triangle inside a tile: replay the reference's x accumulation
+// (Rasterizer.cs:485-535) and raise the per-pixel winner keys.
+// (Measured and rejected on city4k: a min3/max3 form of the inclusive test selected per row by a
+// finiteness check, and walking small footprints in the loading thread -- both slower.)
+template <int MODE>
+__device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const float a12, const float a20,
+                                             const float a01, const float invArea, const float d0, const float d1,
+                                             const float d2, const uint32_t seq, unsigned long long* krow,
+                                             const int sx, const int ex) {
+    for (int xx = sx; xx <= ex; ++xx) {
+        if (inside3(w0, w1, w2)) {
+            float w0f, w1f, w2f;
+            const float depth = frag_depth(d0, d1, d2, invArea, w0, w1, w2, w0f, w1f, w2f);
+            if (depth == depth) {                       // NaN never passes a depth test
+                const unsigned long long key = make_key<MODE>(depth, seq);
+                if (key > krow[xx]) atomicMax(krow + xx, key);
+            }
+        }
+        w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
+    }
+}
+
 struct VisSmem {
     unsigned long long keys[kTile * kTile];
     float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
@@ -259,18 +281,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const RasterArg
             const uint32_t seq = __float_as_uint(S[14][j]);
             const int sx = pk & 0xff, ex = (pk >> 8) & 0xff, row = (int)(pk >> 16) + dy;
             for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
-            unsigned long long* krow = keys + row * kTile;
-            for (int xx = sx; xx <= ex; ++xx) {
-                if (inside3(w0, w1, w2)) {
-                    float w0f, w1f, w2f;
-                    float depth = frag_depth(d0, d1, d2, invArea, w0, w1, w2, w0f, w1f, w2f);
-                    if (depth == depth) {                       // NaN never passes a depth test
-                        unsigned long long key = make_key<MODE>(depth, seq);
-                        if (key > krow[xx]) atomicMax(krow + xx, key);
-                    }
-                }
-                w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
-            }
+            vis_walk_row<MODE>(w0, w1, w2, a12, a20, a01, invArea, d0, d1, d2, seq, keys + row * kTile, sx, ex);
         }
         __syncthreads();
     }

@@ -80,3 +80,40 @@ def test_bands_equal_full_frame(oracle):
         y0, y1 = r0 * 16, min(r1 * 16, 720)
         assert np.array_equal(bc[y0:y1], fc[y0:y1])
         assert np.array_equal(bd[y0:y1], fd[y0:y1])
+
+
+def _random_triangle_scene(seed, W=512, H=384, n=400):
+    """Triangles of every shape straight in screen space: slivers, huge ones reaching far outside
+    the target, needle-thin diagonals, tiny ones -- the cases the conservative tile rejection and
+    the binning have to get exactly right."""
+    from tests.util import screen_tri_scene
+    rng = np.random.RandomState(seed)
+    tris, cols, zs = [], [], []
+    for k in range(n):
+        kind = k % 5
+        c = rng.uniform(-0.2, 1.2, 2) * (W, H)
+        if kind == 0:                                   # big
+            t = c + rng.uniform(-1.0, 1.0, (3, 2)) * (W, H)
+        elif kind == 1:                                 # thin diagonal needle
+            d = rng.uniform(-1, 1, 2) * (W, H)
+            nrm = np.array([-d[1], d[0]]) / (np.linalg.norm(d) + 1e-9)
+            t = np.stack([c, c + d, c + 0.5 * d + nrm * rng.uniform(0.05, 3.0)])
+        elif kind == 2:                                 # medium
+            t = c + rng.uniform(-40, 40, (3, 2))
+        elif kind == 3:                                 # tiny
+            t = c + rng.uniform(-2, 2, (3, 2))
+        else:                                           # huge, vertices far off-screen
+            t = c + rng.uniform(-30, 30, (3, 2)) * (W, H)
+        tris.append(np.round(t * 16) / 16)
+        cols.append((*rng.uniform(0.2, 1.0, 3), 1.0))
+        zs.append(rng.uniform(0.05, 0.95))
+    return screen_tri_scene(W, H, tris, colors=cols, ndc_z=zs, cull=0)
+
+
+@pytest.mark.parametrize("pipeline", [1, 2])
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_triangles_all_shapes(oracle, pipeline, seed):
+    sc = _random_triangle_scene(seed)
+    oc, od, _ = oracle.render_scene(sc, threads=8)
+    gc, gd, st = _render_gpu(sc, pipeline)
+    print(compare(gc, gd, oc, od), st.tile_pairs)
