@@ -75,7 +75,8 @@ struct SrbContext {
     DevBuf<TriRef> dRefs;
     DevBuf<ClipAttr> dClipAttrs;
     DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
-    DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dOrder, dBins, dBinScratch;
+    DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dBins, dBinScratch;
+    DevBuf<uint4> dOrder;             // tile launch order of the visibility kernel
     Counters* dCnt = nullptr;
     Counters* hCnt = nullptr;         // pinned
     DrawRec* hDraws = nullptr;        // pinned staging

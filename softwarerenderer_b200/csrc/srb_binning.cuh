@@ -212,7 +212,7 @@ constexpr int kScanCtas = 8;
 
 __global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
 scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
-                  uint32_t* __restrict__ tileCursor, uint32_t* __restrict__ order, int tile0, int nTiles,
+                  uint32_t* __restrict__ tileCursor, uint4* __restrict__ order, int tile0, int nTiles,
                   Counters* cnt, uint32_t pairCap) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
@@ -300,7 +300,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
                 if (hv) pos = oh + __popc(mh & lt);
                 else if (md) pos = th + om + __popc(mm & lt);
                 else pos = th + tm + orest + __popc(mv & ~mh & ~mm & lt);
-                order[pos] = (uint32_t)i;
+                order[pos] = make_uint4((uint32_t)i, excl, excl + c[k], 0u);      // tile, bin start, bin end
             }
             run += __shfl_sync(full, incl, 31);
             oh += __popc(mh); om += __popc(mm); orest += __popc(mv & ~mh & ~mm);

@@ -195,8 +195,9 @@ struct VisSmem {
 // One 16x16 tile, whole CTA.  Ends with every thread past its last shared-memory access
 // only after the caller's __syncthreads() (heavy-list CTAs loop over several tiles).
 template <int MODE>
-__device__ __forceinline__ void vis_process_tile(const int tile, const RasterArgs& A, const FrameParams& fp,
-                                                 const SrbUniforms& U, VisSmem& sm) {
+__device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t bs, const uint32_t be,
+                                                 const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U,
+                                                 VisSmem& sm) {
     unsigned long long* keys = sm.keys;
     float (*S)[kVisThreads] = sm.S;
     int* prefix = sm.prefix;
@@ -206,7 +207,6 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const RasterArg
     const int tx0 = tX * kTile, ty0 = tY * kTile;
     const int tileEndX = min(tx0 + kTile - 1, fp.W - 1), tileEndY = min(ty0 + kTile - 1, fp.H - 1);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const uint32_t bs = A.tileStart[tile], be = A.tileEnd[tile];
     const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
 
     if (bs == be) {
@@ -321,8 +321,11 @@ template <int MODE>
 __global__ void __launch_bounds__(kVisThreads)
 vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     __shared__ VisSmem sm;
+    // One load gives the tile and its bin range.  (Measured and rejected: clearing the frame on a second
+    // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
+    const uint4 o = __ldg(A.order + blockIdx.x);
     if (A.cnt->overflow) return;
-    vis_process_tile<MODE>((int)__ldg(A.order + blockIdx.x), A, fp, U, sm);
+    vis_process_tile<MODE>((int)o.x, o.y, o.z, A, fp, U, sm);
 }
 
 __global__ void texture_sample_kernel(const uchar4* __restrict__ tex, int tw, int th, const float2* __restrict__ uv,

@@ -14,7 +14,7 @@ struct RasterArgs {
     const uint32_t* tileStart;
     const uint32_t* tileEnd;      // == tileCursor after the fill pass
     uint32_t* bins;
-    const uint32_t* order;        // launch order of the band's tiles (scan kernel): heavy bins first
+    const uint4* order;           // launch order of the band's tiles (scan kernel), heavy bins first: {tile, bin start, bin end}
     float4* color;
     float* depth;
     const Counters* cnt;          // kernels bail out when a capacity overflowed (frame is re-run)
