@@ -250,7 +250,10 @@ __device__ __forceinline__ void row_base(const TriRec& r, const TriEq& e, int st
 }
 // centerInside (Rasterizer.cs:493-494): inclusive on every edge, either sign.
 __device__ __forceinline__ bool inside3(float w0, float w1, float w2) {
-    return (w0 >= 0 && w1 >= 0 && w2 >= 0) || (w0 <= 0 && w1 <= 0 && w2 <= 0);
+    // bitwise, not short-circuit: six predicated compares and no branches (NaN compares false either way)
+    const bool ge = (w0 >= 0.0f) & (w1 >= 0.0f) & (w2 >= 0.0f);
+    const bool le = (w0 <= 0.0f) & (w1 <= 0.0f) & (w2 <= 0.0f);
+    return ge | le;
 }
 // depth at a covered pixel (Rasterizer.cs:498-502).
 __device__ __forceinline__ float frag_depth(float d0, float d1, float d2, float invArea,

@@ -159,7 +159,10 @@ __device__ __forceinline__ unsigned long long clear_key() {
     return ((unsigned long long)hi << 32) | lo;
 }
 
-constexpr int kVisThreads = 128;
+#ifndef SRB_VIS_THREADS
+#define SRB_VIS_THREADS 128
+#endif
+constexpr int kVisThreads = SRB_VIS_THREADS;
 constexpr int kVisWarps = kVisThreads / 32;
 constexpr int kVisFields = 15;
 
@@ -172,6 +175,10 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
                                              const float a01, const float invArea, const float d0, const float d1,
                                              const float d2, const uint32_t seq, unsigned long long* krow,
                                              const int sx, const int ex) {
+    // (Measured and rejected: separating "advance to the next covered pixel" from the depth/key part
+    // so that lanes would run the expensive part together -- 139 -> 196 us, the lanes serialised.)
+    // (Measured and rejected: a straight-line body that always computes depth and key -- 139 -> 154 us;
+    // whole warps of uncovered pixels are common enough for the branch to pay.)
     for (int xx = sx; xx <= ex; ++xx) {
         if (inside3(w0, w1, w2)) {
             float w0f, w1f, w2f;
@@ -210,6 +217,9 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
 
     if (bs == be) {
+#ifdef SRB_EXP_SKIP_EMPTY
+        return;
+#endif
         // Empty bin: the fused clear is all there is (pure store bandwidth).
         for (int p = tid; p < kTile * kTile; p += kVisThreads) {
             const int x = tx0 + (p & 15), y = ty0 + (p >> 4);
@@ -294,7 +304,11 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         const unsigned long long key = keys[p];
         float4 outc = clearCol;
         float outd = kClearDepth;
+#ifdef SRB_EXP_SKIP_SHADE
+        if (false) {
+#else
         if (key != ckey) {
+#endif
             uint32_t lo = (uint32_t)key, hi = (uint32_t)(key >> 32);
             const uint32_t seq = (MODE & 1) ? (0xfffffffeu - lo) : (lo - 1u);
             if (MODE >= 2) hi = ~hi;

@@ -117,3 +117,27 @@ def test_random_triangles_all_shapes(oracle, pipeline, seed):
     oc, od, _ = oracle.render_scene(sc, threads=8)
     gc, gd, st = _render_gpu(sc, pipeline)
     print(compare(gc, gd, oc, od), st.tile_pairs)
+
+
+def test_city4k_full_size(oracle):
+    """BASELINE config 3 at its full size: 1,007,140 triangles, 1,332 draws, 3840x2160, device FrustumCuller."""
+    import os
+    from softwarerenderer_b200 import scene as S
+    sc = S.scene_city(3840, 2160)
+    oc, od, ost = oracle.render_scene(sc, threads=os.cpu_count() or 8)
+    gc, gd, st = _render_gpu(sc, 0)
+    stats = compare(gc, gd, oc, od)
+    assert st.triangles_setup == ost.triangles_drawn and st.draws_visible == sum(oracle.frustum_flags(sc))
+    print(stats)
+
+
+def test_stress8k_full_size(oracle):
+    """BASELINE config 5 at its full size on ONE GPU: 10,044,000 small triangles, 7680x4320, reference semantics."""
+    import os
+    from softwarerenderer_b200 import scene as S
+    sc = S.scene_stress(7680, 4320)
+    oc, od, ost = oracle.render_scene(sc, threads=os.cpu_count() or 8)
+    gc, gd, st = _render_gpu(sc, 0)
+    stats = compare(gc, gd, oc, od)
+    assert st.triangles_setup == ost.triangles_drawn
+    print(stats)
