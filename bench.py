@@ -48,7 +48,7 @@ def build_scene(name):
     return S.scene_stress(w["width"], w["height"])
 
 
-from softwarerenderer_b200.bands import band_rows, gather_bands  # noqa: E402
+from softwarerenderer_b200.bands import balanced_cuts, band_rows, gather_bands  # noqa: E402
 
 
 class ClockSampler:
@@ -63,7 +63,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
@@ -183,16 +183,31 @@ def run_gpu(args):
     tiles_y = (H + 15) // 16
     win = srb.MainWindow(W, H, device=local)
     ctx = win._ctx
-    r0, r1 = band_rows(tiles_y, world, rank)
-    if world > 1:
-        win.SetBand(r0, r1)
-    y0, y1 = r0 * 16, min(r1 * 16, H)
     if args.pipeline:
         win.SetPipeline(args.pipeline)
 
     # ---- first frame through the mirror API: uploads meshes/textures, settles capacities ----
     S.submit_scene(win, scene)
     st = win.Stats()
+    # ---- N>1: sort-first bands on tile-row boundaries.  Every rank rendered the whole frame once above,
+    # so all ranks derive the same cost-balanced cuts from the same per-row bin counts (no exchange).
+    cuts = [band_rows(tiles_y, world, r)[0] for r in range(world)] + [tiles_y]
+    if world > 1 and args.bands == "balanced":
+        w_rows = win.TileRowPairs().astype(np.float64) + 0.85 * ((W + 15) // 16)     # an empty tile costs about 0.85 pair
+        cuts = balanced_cuts(w_rows, world)
+    r0, r1 = cuts[rank], cuts[rank + 1]
+    fused = world > 1 and args.gather == "fused"
+    if world > 1:
+        win.SetBand(r0, r1)
+        if fused:
+            # rank 0 exports its colour buffer; band ranks store their final colour straight into it
+            box = [win.ExportColorHandle() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0)
+            if rank != 0:
+                win.SetColorTarget(box[0])
+        S.submit_scene(win, scene)              # settle band-sized capacities
+        st = win.Stats()
+    y0, y1 = r0 * 16, min(r1 * 16, H)
     # host-side command array for the e2e loop (what the C# shim would pin and pass)
     rows = []
     from softwarerenderer_b200.rasterizer import Rasterizer
@@ -213,8 +228,15 @@ def run_gpu(args):
     ext = torch.cuda.ExternalStream(L.srb_stream(ctx), device=dev)
     fb = torch.as_tensor(_DevArray(L.srb_device_color_ptr(ctx), (H, W, 4)), device=dev)
 
+    token = torch.zeros(1, device=dev)
+
     def gather():
-        gather_bands(fb, H, rank, world, dist)
+        if world == 1:
+            return
+        if fused:
+            dist.all_reduce(token)              # frame barrier only: the pixels already went over NVLink as peer stores
+        else:
+            gather_bands(fb, H, rank, world, dist, cuts=cuts)
 
     def step_resident():
         N.check(ctx, L.srb_replay_frame(ctx))
@@ -229,6 +251,8 @@ def run_gpu(args):
         gather()
         if rank == 0:
             N.check(ctx, L.srb_read_color(ctx, C.c_void_p(host.data_ptr())))
+        if fused:
+            dist.all_reduce(token)              # band ranks must not start the next frame while rank 0 still reads this one
 
     def timed(step, K, Wm, sampler=None):
         with torch.cuda.stream(ext):
@@ -280,6 +304,10 @@ def run_gpu(args):
             acc += np.array(list(buf))
     N.check(ctx, L.srb_set_profiling(ctx, 0))
     stage_ms = {n_: float(a / Kp) for n_, a in zip(STAGES, acc)}
+    stage_ms_ranks = None
+    if world > 1:
+        stage_ms_ranks = [None] * world
+        dist.all_gather_object(stage_ms_ranks, stage_ms)
 
     # ---- roofline bookkeeping ----
     depth = win.DepthBuffer
@@ -322,6 +350,10 @@ def run_gpu(args):
                        "draws_visible": int(sum(visible)), "triangles_setup": int(st.triangles_setup),
                        "tile_pairs": int(st.tile_pairs), "pipeline": "visibility" if st.pipeline_used == 2 else "ordered",
                        "parallelism": f"bands{world}" if world > 1 else "single",
+                       "bands": {"cuts_tile_rows": [int(x) for x in cuts], "policy": args.bands,
+                                 "gather": ("peer stores from the tile kernel into rank 0's buffer over NVLink + 4-byte "
+                                            "NCCL all-reduce as frame barrier") if fused else "NCCL grouped send/recv of float4 bands"}
+                       if world > 1 else None,
                        "l2": "no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
                              if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush"},
             "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES + 8 * n_geom_blocks),
@@ -330,6 +362,7 @@ def run_gpu(args):
             "gpu_launches": int(st.kernel_launches) * K,
             "clocks": clocks,
             "stage_ms": stage_ms,
+            "stage_ms_ranks": stage_ms_ranks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes": dom_bytes, "peak_source": peak_src},
             "roofline_frame": {"algorithmic_bytes": balg, "achieved": balg["total"] / (frame_ms / 1000.0) / 1e9,
@@ -376,13 +409,15 @@ def cpu_baseline(scene, budget_s=25.0):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="srb200", choices=["srb200", "reference"])
     ap.add_argument("--workload", default="city4k", choices=sorted(WORKLOADS))
     ap.add_argument("--pipeline", type=int, default=0, help="0 auto, 1 ordered, 2 visibility")
     ap.add_argument("--e2e-steps", type=int, default=30)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="fused", choices=["fused", "nccl"], help="N>1: how bands reach rank 0")
+    ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"], help="N>1: band cut policy")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

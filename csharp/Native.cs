@@ -46,6 +46,9 @@ namespace SoftwareRenderer
         [DllImport(Lib)] public static extern IntPtr srb_last_error(IntPtr ctx);
         [DllImport(Lib)] public static extern int srb_set_band(IntPtr ctx, int tileRow0, int tileRow1);
         [DllImport(Lib)] public static extern int srb_set_pipeline(IntPtr ctx, int pipeline);
+        [DllImport(Lib)] public static extern int srb_export_color_handle(IntPtr ctx, byte* handleOut64);
+        [DllImport(Lib)] public static extern int srb_set_color_target(IntPtr ctx, byte* handle64);
+        [DllImport(Lib)] public static extern int srb_get_tile_row_pairs(IntPtr ctx, uint* rowsOut, int n);
         [DllImport(Lib)] public static extern int srb_texture_create(IntPtr ctx, byte* rgba8, int w, int h, out int tex);
         [DllImport(Lib)] public static extern int srb_texture_destroy(IntPtr ctx, int tex);
         [DllImport(Lib)] public static extern int srb_texture_sample(IntPtr ctx, int tex, float* uv, int n, int filter, float* rgbaOut);

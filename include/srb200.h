@@ -113,6 +113,17 @@ const char* srb_last_error(SrbContext* ctx);                     /* ctx may be N
 /* Multi-GPU: restrict this context to tile rows [row0,row1) (16-px rows). */
 int srb_set_band(SrbContext* ctx, int tile_row0, int tile_row1);
 int srb_set_pipeline(SrbContext* ctx, int pipeline);
+/* Multi-GPU band gather fused into the tile kernel (no reference counterpart):
+ * rank 0 exports its colour buffer (CUDA IPC handle, 64 bytes); a band rank passes that handle as
+ * its colour target and from then on stores its band's final colour straight into rank 0's
+ * buffer over NVLink (peer stores), so that no separate gather copy is needed -- only a barrier.
+ * handle == NULL restores the local buffer.  Needs frames that clear colour. */
+#define SRB_IPC_HANDLE_BYTES 64
+int srb_export_color_handle(SrbContext* ctx, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]);
+int srb_set_color_target(SrbContext* ctx, const uint8_t handle[SRB_IPC_HANDLE_BYTES]);
+/* Work per 16-px tile row of the last completed frame: (triangle, tile) pairs binned into the
+ * row (out[0..n), n <= tile rows).  Input of cost-balanced band cuts. */
+int srb_get_tile_row_pairs(SrbContext* ctx, uint32_t* out, int n);
 
 /* ---- resources: Texture (Texture.cs:31-63), Mesh arrays (ModelLoader.cs:42-57) ---- */
 int srb_texture_create(SrbContext* ctx, const uint8_t* rgba8, int width, int height, SrbTexture* out);

@@ -77,7 +77,8 @@ assert DRAW_CMD_DTYPE.itemsize == 248, DRAW_CMD_DTYPE.itemsize
 # Every symbol include/srb200.h declares (checked by tests/test_abi.py).
 EXPORTS = [
     "srb_create", "srb_destroy", "srb_resize", "srb_get_size", "srb_last_error", "srb_set_band",
-    "srb_set_pipeline", "srb_texture_create", "srb_texture_destroy", "srb_texture_sample",
+    "srb_set_pipeline", "srb_export_color_handle", "srb_set_color_target", "srb_get_tile_row_pairs",
+    "srb_texture_create", "srb_texture_destroy", "srb_texture_sample",
     "srb_mesh_create", "srb_mesh_destroy", "srb_set_uniforms", "srb_begin_frame", "srb_draw",
     "srb_submit_draws", "srb_end_frame", "srb_replay_frame", "srb_sync", "srb_read_color",
     "srb_read_depth", "srb_read_color_rgba8", "srb_read_color_rows", "srb_get_pixel", "srb_set_pixel",
@@ -114,6 +115,9 @@ def lib() -> C.CDLL:
     L.srb_last_error.restype = C.c_char_p
     L.srb_set_band.argtypes = [vp, i32, i32]
     L.srb_set_pipeline.argtypes = [vp, i32]
+    L.srb_export_color_handle.argtypes = [vp, vp]
+    L.srb_set_color_target.argtypes = [vp, vp]
+    L.srb_get_tile_row_pairs.argtypes = [vp, vp, i32]
     L.srb_texture_create.argtypes = [vp, vp, i32, i32, C.POINTER(C.c_int32)]
     L.srb_texture_destroy.argtypes = [vp, C.c_int32]
     L.srb_texture_sample.argtypes = [vp, C.c_int32, vp, i32, i32, vp]

@@ -20,6 +20,30 @@ def band_rows(tiles_y: int, n: int, r: int):
     return r0, r0 + base + (1 if r < rem else 0)
 
 
+def balanced_cuts(row_weights, n: int):
+    """Cut points [c_0=0, c_1, ..., c_n=rows] over tile rows such that every band carries about
+    the same weight (the cost model of the caller: e.g. bin pairs + a constant per tile).  Every
+    band gets at least one row when rows >= n.  Deterministic: all ranks compute the same cuts."""
+    w = [float(x) for x in row_weights]
+    rows = len(w)
+    if n <= 0:
+        raise ValueError("balanced_cuts: n must be positive")
+    total = sum(w)
+    if total <= 0.0 or rows < n:
+        return [band_rows(rows, n, r)[0] for r in range(n)] + [rows]
+    cuts, acc, r = [0], 0.0, 0
+    for k in range(1, n):
+        target = total * k / n
+        while r < rows and (acc + w[r] * 0.5 <= target or r < cuts[-1] + 1):
+            acc += w[r]
+            r += 1
+        r = min(r, rows - (n - k))            # leave a row for each remaining band
+        acc = sum(w[:r])
+        cuts.append(r)
+    cuts.append(rows)
+    return cuts
+
+
 def band_pixels(height: int, n: int, r: int):
     """Pixel-row range [y0, y1) of rank r of n for a target `height` rows tall."""
     tiles_y = (height + TILE - 1) // TILE
@@ -27,22 +51,29 @@ def band_pixels(height: int, n: int, r: int):
     return r0 * TILE, min(r1 * TILE, height)
 
 
-def gather_bands(fb, height: int, rank: int, world: int, dist=None):
+def cut_pixels(height: int, cuts, r: int):
+    """Pixel-row range [y0, y1) of band r for explicit tile-row cuts (balanced_cuts)."""
+    return cuts[r] * TILE, min(cuts[r + 1] * TILE, height)
+
+
+def gather_bands(fb, height: int, rank: int, world: int, dist=None, cuts=None):
     """Gather every rank's band of `fb` ([H, W, C] tensor, full-size on every rank) into
     rank 0's `fb` with grouped point-to-point sends (bands differ in size, so this is a
-    gather-v, not an all-gather).  Works on NCCL (device tensors, over NVLink) and gloo."""
+    gather-v, not an all-gather).  Works on NCCL (device tensors, over NVLink) and gloo.
+    `cuts`: explicit tile-row cuts (default: the equal split of band_rows)."""
     if world == 1:
         return
     if dist is None:
         import torch.distributed as dist
+    span = (lambda r: cut_pixels(height, cuts, r)) if cuts is not None else (lambda r: band_pixels(height, world, r))
     ops = []
     if rank == 0:
         for r in range(1, world):
-            a, b = band_pixels(height, world, r)
+            a, b = span(r)
             if b > a:
                 ops.append(dist.P2POp(dist.irecv, fb[a:b], r))
     else:
-        a, b = band_pixels(height, world, rank)
+        a, b = span(rank)
         if b > a:
             ops.append(dist.P2POp(dist.isend, fb[a:b], 0))
     if ops:

@@ -53,6 +53,7 @@ struct SrbContext {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float4* color = nullptr;
     float* depth = nullptr;
+    float4* colorTarget = nullptr;    // peer buffer opened from an IPC handle (band gather), or null
     std::vector<MeshRes> meshes;      // handle = index + 1
     std::vector<TexRes> textures;
     std::mutex mu;
@@ -91,6 +92,10 @@ struct SrbContext {
 };
 
 namespace {
+
+void close_color_target(SrbContext* c) {
+    if (c->colorTarget) { cudaIpcCloseMemHandle(c->colorTarget); c->colorTarget = nullptr; }
+}
 
 int fail(SrbContext* c, int code, const std::string& msg) {
     if (c) c->err = msg; else g_createError = msg;
@@ -188,6 +193,11 @@ int launch_frame(SrbContext* c) {
     A.draws = c->dDraws.p; A.order = c->dOrder.p; A.wn = c->dWn.p; A.recs.R = c->dRecsR.p; A.recs.S = c->dRecsS.p;
     A.clipAttrs = c->dClipAttrs.p; A.tileStart = c->dTileStart.p; A.tileEnd = c->dTileCursor.p;
     A.bins = c->dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = c->dCnt;
+    A.colorOut = c->colorTarget ? c->colorTarget : c->color;
+#ifdef SRB_TILE_TIMING
+    if (c->dBinScratch.reserve((size_t)nTiles * 8) != cudaSuccess) return fail(c, SRB_ERR_CUDA, "dbg alloc");
+    A.dbg = (ulonglong4*)c->dBinScratch.p;
+#endif
     if (bandTiles > 0) {
         if (c->useVis) {
             mark(6);                       // no sort stage on the visibility path
@@ -312,6 +322,7 @@ int srb_destroy(SrbContext* c) {
     if (!c) return SRB_ERR_ARG;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    close_color_target(c);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
     c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dOrder.release(); c->dClip.release(); c->dWn.release();
@@ -354,6 +365,48 @@ int srb_set_band(SrbContext* c, int r0, int r1) {
     if (!c) return SRB_ERR_ARG;
     if (r0 < 0 || r1 < r0 || r1 > c->tilesY) return fail(c, SRB_ERR_ARG, "band rows out of range");
     c->band0 = r0; c->band1 = r1; c->bandSet = true;
+    return SRB_OK;
+}
+
+int srb_export_color_handle(SrbContext* c, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]) {
+    if (!c || !handle_out) return SRB_ERR_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == SRB_IPC_HANDLE_BYTES, "IPC handle size");
+    CK(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CK(c, cudaIpcGetMemHandle(&h, c->color));
+    std::memcpy(handle_out, &h, sizeof(h));
+    return SRB_OK;
+}
+
+int srb_set_color_target(SrbContext* c, const uint8_t handle[SRB_IPC_HANDLE_BYTES]) {
+    if (!c) return SRB_ERR_ARG;
+    if (c->inFrame) return fail(c, SRB_ERR_STATE, "colour target change inside a frame");
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    close_color_target(c);
+    if (!handle) return SRB_OK;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    CK(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->colorTarget = (float4*)p;
+    return SRB_OK;
+}
+
+int srb_get_tile_row_pairs(SrbContext* c, uint32_t* out, int n) {
+    if (!c || !out || n < 0) return SRB_ERR_ARG;
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    if (!c->haveFrame) return fail(c, SRB_ERR_STATE, "no completed frame");
+    const int nTiles = c->tilesX * c->tilesY;
+    std::vector<uint32_t> h((size_t)nTiles);
+    CK(c, cudaMemcpy(h.data(), c->dTileCount.p, (size_t)nTiles * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    for (int r = 0; r < n && r < c->tilesY; ++r) {
+        uint64_t s = 0;
+        for (int x = 0; x < c->tilesX; ++x) s += h[(size_t)r * c->tilesX + x];
+        out[r] = (uint32_t)std::min<uint64_t>(s, 0xffffffffu);
+    }
     return SRB_OK;
 }
 
@@ -585,6 +638,8 @@ int srb_end_frame(SrbContext* c) {
         if (!m.opaque || !texOpaque) eligible = false;
     }
     if (totalV > 0x3fffffff || totalT > 0x3fffffff) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
+    if (c->colorTarget && !(c->clearFlags & SRB_CLEAR_COLOR))
+        return fail(c, SRB_ERR_STATE, "a remote colour target needs frames that clear colour");
     if (c->pipeline == SRB_PIPELINE_ORDERED) eligible = false;
     if (c->pipeline == SRB_PIPELINE_VISIBILITY && !eligible && nDraws > 0)
         return fail(c, SRB_ERR_STATE, "frame is not eligible for the visibility pipeline");
@@ -779,6 +834,17 @@ int srb_get_stage_ms(SrbContext* c, float* out, int n) {
     for (int i = 0; i < n && i < SRB_N_STAGES; ++i) out[i] = c->stageMs[i];
     return SRB_OK;
 }
+
+#ifdef SRB_TILE_TIMING
+/* Diagnostic builds only (not declared in srb200.h): per-CTA timing of the last visibility tile kernel. */
+int srb_debug_tile_times(SrbContext* c, unsigned long long* out, int nTiles) {
+    if (!c || !out) return SRB_ERR_ARG;
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpy(out, c->dBinScratch.p, (size_t)nTiles * 32, cudaMemcpyDeviceToHost));
+    return SRB_OK;
+}
+#endif
 
 int srb_get_stats(SrbContext* c, SrbStats* out) {
     if (!c || !out) return SRB_ERR_ARG;

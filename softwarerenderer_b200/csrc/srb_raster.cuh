@@ -134,7 +134,7 @@ ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
         }
     }
     if (inb) {
-        A.color[pidx] = col;
+        A.colorOut[pidx] = col;
         A.depth[pidx] = dep;
     }
 }
@@ -165,6 +165,7 @@ __device__ __forceinline__ unsigned long long clear_key() {
 constexpr int kVisThreads = SRB_VIS_THREADS;
 constexpr int kVisWarps = kVisThreads / 32;
 constexpr int kVisFields = 15;
+constexpr int kKeyPitch = kTile + 1;     // 17 x 8 B = 34 banks: consecutive rows are two banks apart
 
 // Walk one row of one triangle inside a tile: replay the reference's x accumulation
 // (Rasterizer.cs:485-535) and raise the per-pixel winner keys.
@@ -193,7 +194,8 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
 }
 
 struct VisSmem {
-    unsigned long long keys[kTile * kTile];
+    unsigned long long keys[kTile * kKeyPitch]; // rows padded: lanes walk DIFFERENT rows at the same x, and an
+                                                // unpadded 128-byte row pitch would put them all on the same two banks
     float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
     int prefix[kVisThreads];               // exclusive prefix of rows per triangle
     int warpRows[kVisWarps];
@@ -202,7 +204,12 @@ struct VisSmem {
 // One 16x16 tile, whole CTA.  Ends with every thread past its last shared-memory access
 // only after the caller's __syncthreads() (heavy-list CTAs loop over several tiles).
 template <int MODE>
-__device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t bs, const uint32_t be,
+#ifdef SRB_EXP_CAP_BIN
+#define SRB_BE be_
+#else
+#define SRB_BE be
+#endif
+__device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t bs, const uint32_t SRB_BE,
                                                  const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U,
                                                  VisSmem& sm) {
     unsigned long long* keys = sm.keys;
@@ -216,7 +223,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
 
-    if (bs == be) {
+    if (bs == SRB_BE) {
 #ifdef SRB_EXP_SKIP_EMPTY
         return;
 #endif
@@ -225,15 +232,18 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
             const int x = tx0 + (p & 15), y = ty0 + (p >> 4);
             if (x < fp.W && y < fp.H) {
                 const size_t pidx = (size_t)y * fp.W + x;
-                __stcs(A.color + pidx, clearCol);
+                __stcs(A.colorOut + pidx, clearCol);
                 __stcs(A.depth + pidx, kClearDepth);
             }
         }
         return;
     }
 
+#ifdef SRB_EXP_CAP_BIN
+    const uint32_t be = min(be_, bs + (uint32_t)SRB_EXP_CAP_BIN);
+#endif
     const unsigned long long ckey = clear_key<MODE>();
-    for (int i = tid; i < kTile * kTile; i += kVisThreads) keys[i] = ckey;
+    for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
 
     for (uint32_t cb = bs; cb < be; cb += kVisThreads) {
         // ---- one triangle per thread: derive its raster constants for this tile ----
@@ -291,7 +301,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
             const uint32_t seq = __float_as_uint(S[14][j]);
             const int sx = pk & 0xff, ex = (pk >> 8) & 0xff, row = (int)(pk >> 16) + dy;
             for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
-            vis_walk_row<MODE>(w0, w1, w2, a12, a20, a01, invArea, d0, d1, d2, seq, keys + row * kTile, sx, ex);
+            vis_walk_row<MODE>(w0, w1, w2, a12, a20, a01, invArea, d0, d1, d2, seq, keys + row * kKeyPitch, sx, ex);
         }
         __syncthreads();
     }
@@ -301,7 +311,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         const int px = p & 15, py = p >> 4;
         const int x = tx0 + px, y = ty0 + py;
         if (x >= fp.W || y >= fp.H) continue;
-        const unsigned long long key = keys[p];
+        const unsigned long long key = keys[py * kKeyPitch + px];
         float4 outc = clearCol;
         float outd = kClearDepth;
 #ifdef SRB_EXP_SKIP_SHADE
@@ -326,20 +336,34 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
             outd = ord2f(hi);
         }
         const size_t pidx = (size_t)y * fp.W + x;
-        __stcs(A.color + pidx, outc);
+        __stcs(A.colorOut + pidx, outc);
         __stcs(A.depth + pidx, outd);
     }
 }
 
+#ifndef SRB_VIS_MINBLOCKS
+#define SRB_VIS_MINBLOCKS 8
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(kVisThreads)
+__global__ void __launch_bounds__(kVisThreads, SRB_VIS_MINBLOCKS)
 vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     __shared__ VisSmem sm;
     // One load gives the tile and its bin range.  (Measured and rejected: clearing the frame on a second
     // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
     const uint4 o = __ldg(A.order + blockIdx.x);
     if (A.cnt->overflow) return;
+#ifdef SRB_TILE_TIMING
+    unsigned long long t0, t1;
+    unsigned smid;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+#endif
     vis_process_tile<MODE>((int)o.x, o.y, o.z, A, fp, U, sm);
+#ifdef SRB_TILE_TIMING
+    __syncthreads();
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+    if (threadIdx.x == 0 && A.dbg) A.dbg[blockIdx.x] = make_ulonglong4(t0, t1, ((unsigned long long)o.x << 32) | (o.z - o.y), smid);
+#endif
 }
 
 __global__ void texture_sample_kernel(const uchar4* __restrict__ tex, int tw, int th, const float2* __restrict__ uv,

@@ -15,8 +15,12 @@ struct RasterArgs {
     const uint32_t* tileEnd;      // == tileCursor after the fill pass
     uint32_t* bins;
     const uint4* order;           // launch order of the band's tiles (scan kernel), heavy bins first: {tile, bin start, bin end}
-    float4* color;
+    float4* color;                // this context's colour buffer (read when a frame does not clear)
+    float4* colorOut;             // where final colour is stored: == color, or a peer GPU's buffer (band gather)
     float* depth;
+#ifdef SRB_TILE_TIMING
+    ulonglong4* dbg;              // per-CTA {start ns, end ns, tile<<32 | bin length, smid} (diagnostic builds only)
+#endif
     const Counters* cnt;          // kernels bail out when a capacity overflowed (frame is re-run)
 };
 

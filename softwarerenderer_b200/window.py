@@ -91,6 +91,28 @@ class MainWindow:
     def SetBand(self, tile_row0: int, tile_row1: int) -> None:
         N.check(self._ctx, N.lib().srb_set_band(self._ctx, tile_row0, tile_row1))
 
+    # -- multi-GPU band gather fused into the tile kernel -------
+    def ExportColorHandle(self) -> bytes:
+        """CUDA IPC handle of this window's colour buffer (rank 0 hands it to the band ranks)."""
+        buf = (C.c_uint8 * 64)()
+        N.check(self._ctx, N.lib().srb_export_color_handle(self._ctx, buf))
+        return bytes(buf)
+
+    def SetColorTarget(self, handle: Optional[bytes]) -> None:
+        """Store final colour into the buffer behind `handle` (a peer GPU's) instead of the local one."""
+        if handle is None:
+            N.check(self._ctx, N.lib().srb_set_color_target(self._ctx, None))
+        else:
+            buf = (C.c_uint8 * 64).from_buffer_copy(handle)
+            N.check(self._ctx, N.lib().srb_set_color_target(self._ctx, buf))
+
+    def TileRowPairs(self) -> np.ndarray:
+        """(triangle, tile) pairs binned into each 16-px tile row by the last frame."""
+        n = (self.RenderHeight + 15) // 16
+        out = np.zeros(n, dtype=np.uint32)
+        N.check(self._ctx, N.lib().srb_get_tile_row_pairs(self._ctx, N.ptr(out), n))
+        return out
+
     def SetPipeline(self, pipeline: int) -> None:
         N.check(self._ctx, N.lib().srb_set_pipeline(self._ctx, pipeline))
 

@@ -1,0 +1,64 @@
+"""-m gpu: the fused band gather.  Two processes share cuda:0 (host-level barriers only, no kernel waits
+on another process): rank 1 renders the lower band and stores its final colour straight into rank 0's
+colour buffer through a CUDA IPC mapping; rank 0's buffer must then hold the full frame."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_path):
+    import torch.distributed as dist
+
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.bands import balanced_cuts
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sc = S.scene_city(1280, 720, n_instances=24)
+        win = srb.MainWindow(sc.width, sc.height, device=0)
+        S.submit_scene(win, sc)                                   # full frame once: per-row work for the cuts
+        cuts = balanced_cuts(win.TileRowPairs().astype(np.float64) + 0.85 * 80, world)
+        win.SetBand(cuts[rank], cuts[rank + 1])
+        box = [win.ExportColorHandle() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            win.SetColorTarget(box[0])
+        dist.barrier()
+        S.submit_scene(win, sc)
+        win.Sync()
+        dist.barrier()                                            # every band has landed in rank 0's buffer
+        if rank == 0:
+            np.savez(out_path, color=win.ColorBuffer, cuts=np.array(cuts))
+        dist.barrier()
+        win.SetColorTarget(None)
+        win.Close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_fused_band_gather_reproduces_the_full_frame(tmp_path, oracle):
+    import torch.multiprocessing as mp
+
+    from softwarerenderer_b200 import scene as S
+    from tests.util import to_u8
+    out = str(tmp_path / "fused.npz")
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    z = np.load(out)
+    oc, od, _ = oracle.render_scene(S.scene_city(1280, 720, n_instances=24), threads=8)
+    cuts = z["cuts"].tolist()
+    assert cuts[0] == 0 and cuts[-1] == 45 and 0 < cuts[1] < 45
+    d8 = np.abs(to_u8(z["color"]) - to_u8(oc)).max(axis=-1)
+    assert (d8 <= 1).mean() >= 0.999 and d8.max() <= 1

@@ -96,3 +96,18 @@ def test_algorithmic_bytes_formula():
     assert b["texels"] == 4 * 2048 * 2048            # one unique texture bound by the five draws
     assert bench.algorithmic_bytes(sc, [True] * 5, p_cov=1000)["texels"] == 4000      # min(texture bytes, 4*P_cov)
     assert bench.algorithmic_bytes(sc, [False] * 5, p_cov=0)["geometry"] == 0
+
+
+def test_balanced_cuts():
+    from softwarerenderer_b200.bands import balanced_cuts
+    assert balanced_cuts([1] * 8, 4) == [0, 2, 4, 6, 8]
+    # all the work in the lower half: the upper bands shrink to keep every band's weight about equal
+    w = [0.1] * 60 + [10.0] * 8 + [0.1] * 67
+    for n in (2, 4, 8):
+        c = balanced_cuts(w, n)
+        assert c[0] == 0 and c[-1] == len(w) and all(b > a for a, b in zip(c, c[1:]))
+        loads = [sum(w[a:b]) for a, b in zip(c, c[1:])]
+        assert max(loads) <= sum(w) / n + 10.0            # within one heavy row of the ideal
+    assert balanced_cuts([0, 0, 0], 2) == [0, 2, 3]       # no information -> plain row split
+    assert balanced_cuts([5.0, 1.0], 2) == [0, 1, 2]
+    assert len(balanced_cuts([1.0] * 135, 8)) == 9
