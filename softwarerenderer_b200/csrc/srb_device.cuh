@@ -175,8 +175,8 @@ __device__ __forceinline__ float edge_fn(float ax, float ay, float bx, float by,
 
 // Monotone map float -> uint32 (greater float <=> greater uint); -0 canonicalised to +0.
 __device__ __forceinline__ uint32_t f2ord(float f) {
-    uint32_t u = __float_as_uint(f + 0.0f);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    const uint32_t u = __float_as_uint(f + 0.0f);
+    return u ^ ((uint32_t)((int)u >> 31) | 0x80000000u);     // negative: ~u, else u | sign
 }
 __device__ __forceinline__ float ord2f(uint32_t o) {
     uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;

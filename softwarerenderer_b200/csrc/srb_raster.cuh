@@ -181,13 +181,17 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
     // (Measured and rejected: a straight-line body that always computes depth and key -- 139 -> 154 us;
     // whole warps of uncovered pixels are common enough for the branch to pay.)
     for (int xx = sx; xx <= ex; ++xx) {
+        // (Measured and rejected: deciding by sign bits, (s0^s1)|(s0^s2) >= 0, with the exact compares only when
+        // an edge value is zero -- half the ALU-pipe work but one more branch level: 119 -> 141 us.)
         if (inside3(w0, w1, w2)) {
             float w0f, w1f, w2f;
             const float depth = frag_depth(d0, d1, d2, invArea, w0, w1, w2, w0f, w1f, w2f);
-            if (depth == depth) {                       // NaN never passes a depth test
-                const unsigned long long key = make_key<MODE>(depth, seq);
-                if (key > krow[xx]) atomicMax(krow + xx, key);
-            }
+            // NaN never passes a depth test: it becomes key 0, which loses to everything.  No pre-check of the
+            // stored key: atomicMax itself reads and compares before its CAS.  (Measured: the branchy form with
+            // a pre-check 119 us, this 117 us.  Rejected: a hand-written CAS loop reusing the loaded value,
+            // 123 -> 260 us -- the compiler's ATOMS.CAST.SPIN sequence is far better.)
+            const unsigned long long key = make_key<MODE>(depth, seq);
+            atomicMax(krow + xx, depth == depth ? key : 0ull);
         }
         w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
     }
@@ -197,8 +201,11 @@ struct VisSmem {
     unsigned long long keys[kTile * kKeyPitch]; // rows padded: lanes walk DIFFERENT rows at the same x, and an
                                                 // unpadded 128-byte row pitch would put them all on the same two banks
     float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
-    int prefix[kVisThreads];               // exclusive prefix of rows per triangle
     int warpRows[kVisWarps];
+    unsigned short items[kVisThreads * kTile];   // (triangle slot | row << 8) per work item of the chunk
+#ifdef SRB_TILE_TIMING
+    unsigned long long phase[2];           // diagnostic: time after the first chunk's load+scan, time before resolve
+#endif
 };
 
 // One 16x16 tile, whole CTA.  Ends with every thread past its last shared-memory access
@@ -214,7 +221,6 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
                                                  VisSmem& sm) {
     unsigned long long* keys = sm.keys;
     float (*S)[kVisThreads] = sm.S;
-    int* prefix = sm.prefix;
     int* warpRows = sm.warpRows;
     const unsigned full = 0xffffffffu;
     const int tX = tile % fp.tilesX, tY = tile / fp.tilesX;
@@ -284,17 +290,21 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
             if (w < wid) woff += v;
             total += v;
         }
-        prefix[tid] = woff + incl - nrows;
+        {   // expand the work items: cheaper than a search per item (123 -> 121 us)
+            unsigned short* it = sm.items + (woff + incl - nrows);
+            for (int r = 0; r < nrows; ++r) it[r] = (unsigned short)(tid | (r << 8));
+        }
         __syncthreads();
+#ifdef SRB_TILE_TIMING
+        if (tid == 0 && cb == bs) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(sm.phase[0]));
+#endif
         // ---- (triangle,row) work items spread over the whole CTA.  Consecutive lanes take consecutive rows
         // of the same triangle, which keeps a warp's row walks coherent.  (Measured and rejected: one
         // contiguous run of items per thread, reusing constants and the y accumulation -- 123 -> 190 us.) ----
+        // (Measured, no gain: splitting each row over 2 or 4 threads when a chunk has few items.)
         for (int i = tid; i < total; i += kVisThreads) {
-            int j = 0;
-#pragma unroll
-            for (int s = kVisThreads / 2; s > 0; s >>= 1)
-                if (prefix[j + s] <= i) j += s;               // largest j with prefix[j] <= i (always has rows)
-            const int dy = i - prefix[j];
+            const int itv = sm.items[i];
+            const int j = itv & 0xff, dy = itv >> 8;
             float w0 = S[0][j], w1 = S[1][j], w2 = S[2][j];
             const float a12 = S[3][j], a20 = S[4][j], a01 = S[5][j];
             const float b12 = S[6][j], b20 = S[7][j], b01 = S[8][j];
@@ -305,9 +315,13 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
             for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
             vis_walk_row<MODE>(w0, w1, w2, a12, a20, a01, invArea, d0, d1, d2, seq, keys + row * kKeyPitch, sx, ex);
         }
+        // (Measured, no effect: loading the next chunk's bin entries early and prefetching their records.)
         __syncthreads();
     }
 
+#ifdef SRB_TILE_TIMING
+    if (tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(sm.phase[1]));
+#endif
     // ---- resolve: shade each pixel's winner once, write colour + depth ----
     for (int p = tid; p < kTile * kTile; p += kVisThreads) {
         const int px = p & 15, py = p >> 4;
@@ -364,7 +378,11 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
 #ifdef SRB_TILE_TIMING
     __syncthreads();
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-    if (threadIdx.x == 0 && A.dbg) A.dbg[blockIdx.x] = make_ulonglong4(t0, t1, ((unsigned long long)o.x << 32) | (o.z - o.y), smid);
+    if (threadIdx.x == 0 && A.dbg) {
+        const unsigned long long pa = o.y == o.z ? 0ull : min(sm.phase[0] - t0, 0xfffffull);
+        const unsigned long long pb = o.y == o.z ? 0ull : min(sm.phase[1] - t0, 0xfffffull);
+        A.dbg[blockIdx.x] = make_ulonglong4(t0, t1, ((unsigned long long)o.x << 32) | (o.z - o.y), smid | (pa << 8) | (pb << 28));
+    }
 #endif
 }
 

@@ -9,6 +9,7 @@ and the source text.  Needs -lineinfo at compile time and --import-source on.
 """
 import csv
 import io
+import os
 import subprocess
 import sys
 
@@ -51,7 +52,11 @@ def main():
         a[1] += i
     for f, (s, i) in byfile.items():
         print(f"  {f:22s} samples {s / tot_s:6.1%}  instr {i / tot_i:6.1%}")
-    for s, i, f, ln, src, st in sorted(lines, reverse=True)[:top]:
+    if os.environ.get("BYINSTR"):
+        lines.sort(key=lambda x: -x[1])
+    else:
+        lines.sort(reverse=True)
+    for s, i, f, ln, src, st in lines[:top]:
         print(f"{s:7d} {s / tot_s:6.1%} {i:10d} {i / tot_i:6.1%}  {f}:{ln:>4s}  {src[:90]}   [{st}]")
 
 

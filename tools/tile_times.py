@@ -26,7 +26,9 @@ L.srb_debug_tile_times.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 N.check(win._ctx, L.srb_debug_tile_times(win._ctx, N.ptr(buf), n))
 t0, t1 = buf[:, 0].astype(np.int64), buf[:, 1].astype(np.int64)
 cnt = (buf[:, 2] & np.uint64(0xffffffff)).astype(np.int64)
-smid = buf[:, 3].astype(np.int64)
+smid = (buf[:, 3] & np.uint64(0xff)).astype(np.int64)
+pa = ((buf[:, 3] >> np.uint64(8)) & np.uint64(0xfffff)).astype(np.int64) / 1000.0    # start -> first chunk loaded + scanned
+pb = ((buf[:, 3] >> np.uint64(28)) & np.uint64(0xfffff)).astype(np.int64) / 1000.0   # start -> walk done
 base = t0.min()
 dur = (t1 - t0) / 1000.0
 print(f"kernel span {(t1.max() - base) / 1000.0:.1f} us, CTAs {n}, sum of CTA durations {dur.sum() / 1000.0:.1f} ms")
@@ -36,7 +38,8 @@ for a, b in zip(edges[:-1], edges[1:]):
     if m.any():
         print(f"bin [{a:5d},{b:10d}): tiles {m.sum():6d}  dur mean {dur[m].mean():7.2f} max {dur[m].max():7.2f} us  "
               f"start mean {(t0[m] - base).mean() / 1000:7.1f}  end max {(t1[m] - base).max() / 1000:7.1f} us  "
-              f"share of CTA time {dur[m].sum() / dur.sum():5.1%}")
+              f"share of CTA time {dur[m].sum() / dur.sum():5.1%}  "
+              f"phases load {pa[m].mean():5.2f} walk {(pb[m] - pa[m]).mean():5.2f} resolve {(dur[m] - pb[m]).mean():5.2f}")
 # concurrency over time
 ts = np.linspace(0, (t1.max() - base), 30)
 act = [int(((t0 - base) <= x).sum() - ((t1 - base) <= x).sum()) for x in ts]
