@@ -30,7 +30,8 @@ namespace SoftwareRenderer
     {
         public long DrawsSubmitted, DrawsVisible, TrianglesSubmitted, TrianglesSetup, TilePairs, ClippedTriangles;
         public int PipelineUsed, KernelLaunches;
-        public float GpuMs, Pad;
+        public float GpuMs;
+        public int TrianglesNoCoverage;
     }
 
     public static unsafe class Srb

@@ -95,13 +95,14 @@ typedef struct SrbStats {
     int64_t draws_submitted;
     int64_t draws_visible;        /* after the device frustum test */
     int64_t triangles_submitted;
-    int64_t triangles_setup;      /* survived behind/NaN/area/cull/bbox(/band) */
+    int64_t triangles_setup;      /* survived behind/NaN/area/cull/bbox(/band) and may cover a pixel */
     int64_t tile_pairs;           /* (triangle, tile) bin entries */
     int64_t clipped_triangles;    /* went through the near-plane clipper */
     int32_t pipeline_used;        /* SRB_PIPELINE_ORDERED or SRB_PIPELINE_VISIBILITY */
     int32_t kernel_launches;      /* CUDA kernels launched by the last end_frame */
     float   gpu_ms;               /* device time of the last end_frame (CUDA events) */
-    float   _pad;
+    int32_t triangles_no_coverage;/* accepted by the reference's setup, but at most 4x4 px and proven to pass its
+                                     coverage test nowhere: not binned (triangles_setup + this = the reference's count) */
 } SrbStats;
 
 /* ---- context / framebuffer: MainWindow buffers (MainWindow.cs:23-31, 298-361) ---- */

@@ -50,7 +50,7 @@ class SrbStats(C.Structure):
         ("pipeline_used", C.c_int32),
         ("kernel_launches", C.c_int32),
         ("gpu_ms", C.c_float),
-        ("_pad", C.c_float),
+        ("triangles_no_coverage", C.c_int32),
     ]
 
 

@@ -259,6 +259,7 @@ int complete_frame(SrbContext* c) {
     const Counters& k = *c->hCnt;
     c->stats.draws_visible = k.nVisibleDraws;
     c->stats.triangles_setup = k.nRefs;
+    c->stats.triangles_no_coverage = (int32_t)k.nNoCover;
     c->stats.tile_pairs = k.nPairs;
     c->stats.clipped_triangles = k.nClippedTris;
     float ms = 0.0f;

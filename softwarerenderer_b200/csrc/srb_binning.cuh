@@ -135,6 +135,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     const int t = blk.y + threadIdx.x;
     SetupOut out;
     out.n = 0;
+    out.nNoCover = 0;
     out.seq[0] = out.seq[1] = 0; out.tx[0] = out.tx[1] = 0; out.ty[0] = out.ty[1] = 0;
     if (t < d.n_triangles) {
         const int g = d.tbase + t;
@@ -165,6 +166,8 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         if (lane >= o) incl += v;
     }
     int total = __shfl_sync(full, incl, 31);
+    const int dropped = (int)__reduce_add_sync(full, (unsigned)out.nNoCover);
+    if (dropped > 0 && lane == 0) atomicAdd(&cnt->nNoCover, (uint32_t)dropped);
     if (total > 0) {                                          // uniform over the warp
         uint32_t base = 0;
         if (lane == 31) base = atomicAdd(&cnt->nRefs, (uint32_t)total);

@@ -315,4 +315,49 @@ __device__ __forceinline__ bool tile_may_cover(float s0x, float s0y, float s1x, 
     return !(geImpossible && leImpossible);
 }
 
+// ---------------------------------------------------------------------------
+// Conservative "covers no pixel at all" test for triangles whose clamped pixel bbox is at most
+// kSmallPx x kSmallPx: distant meshes produce many triangles that fall between pixel centres, and the
+// reference walks them without ever passing its test.  Same bound as tile_may_cover with the bbox as
+// the region, but evaluated per pixel: a pixel cannot pass when some edge value is provably < 0
+// (W_i < -E_i) AND some edge value is provably > 0 (W_j > +E_j).  Returns false only when that holds
+// for every pixel of the bbox; NaN/Inf/huge magnitudes keep the triangle.
+// ---------------------------------------------------------------------------
+constexpr int kSmallPx = 4;
+__device__ __forceinline__ bool small_tri_may_cover(float s0x, float s0y, float s1x, float s1y, float s2x, float s2y,
+                                                    int X0, int X1, int Y0, int Y1) {
+    const float a[3] = {sub(s1y, s2y), sub(s2y, s0y), sub(s0y, s1y)};     // a12, a20, a01
+    const float b[3] = {sub(s2x, s1x), sub(s0x, s2x), sub(s1x, s0x)};     // b12, b20, b01
+    const float px[3] = {s1x, s2x, s0x}, py[3] = {s1y, s2y, s0y};
+    float ax[3][kSmallPx], by[3][kSmallPx], E[3];
+    bool sane = true;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float mx = 0.0f, my = 0.0f;
+#pragma unroll
+        for (int k = 0; k < kSmallPx; ++k) {
+            ax[i][k] = mul(a[i], sub((float)min(X0 + k, X1), px[i]));
+            by[i][k] = mul(b[i], sub((float)min(Y0 + k, Y1), py[i]));
+            mx = fmaxf(mx, fabsf(ax[i][k]));
+            my = fmaxf(my, fabsf(by[i][k]));
+        }
+        const float B = add(mx, my);
+        sane = sane && (B < 1e30f);                                       // false for NaN as well
+        E[i] = mul(B, 1.52587890625e-05f);                                // 2^-16
+    }
+    if (!sane) return true;
+    bool may = false;
+#pragma unroll
+    for (int ky = 0; ky < kSmallPx; ++ky) {
+#pragma unroll
+        for (int kx = 0; kx < kSmallPx; ++kx) {                           // columns/rows past the bbox repeat its last one
+            const float w0 = add(ax[0][kx], by[0][ky]), w1 = add(ax[1][kx], by[1][ky]), w2 = add(ax[2][kx], by[2][ky]);
+            const bool geImpossible = (w0 < -E[0]) | (w1 < -E[1]) | (w2 < -E[2]);
+            const bool leImpossible = (w0 > E[0]) | (w1 > E[1]) | (w2 > E[2]);
+            may = may | !(geImpossible & leImpossible);
+        }
+    }
+    return may;
+}
+
 }  // namespace srb

@@ -29,7 +29,7 @@ struct Counters {
     uint32_t overflow;            // bit0: bins, bit1: clip side buffer, bit2: large-triangle queue
     uint32_t nVisibleDraws;
     uint32_t nBig;                // entries in the large-triangle queue
-    uint32_t _pad;
+    uint32_t nNoCover;            // small triangles dropped because they provably cover no pixel
 };
 
 // ---------------------------------------------------------------------------
@@ -186,6 +186,7 @@ struct BinGeom {
 };
 struct SetupOut {
     int n;                 // accepted triangles of this thread (0..2)
+    int nNoCover;          // triangles dropped by small_tri_may_cover (statistics only)
     uint32_t seq[2];
     uint32_t tx[2], ty[2]; // packed tile ranges
 };
@@ -208,6 +209,15 @@ __device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int mi
                                            SetupOut& out) {
     const int ty0 = max(minY / kTile, fp.bandRow0), ty1 = min(maxY / kTile, fp.bandRow1 - 1);
     if (ty0 > ty1) return;
+#ifndef SRB_EXP_NO_SMALLCULL
+    // Triangles of a few pixels that provably pass the reference's test nowhere are dropped here: they would
+    // only be walked for nothing (about 30 % of the accepted triangles of the city scene).
+    if (maxX - minX < kSmallPx && maxY - minY < kSmallPx &&
+        !small_tri_may_cover(r.s0x, r.s0y, r.s1x, r.s1y, r.s2x, r.s2y, minX, maxX, minY, maxY)) {
+        ++out.nNoCover;
+        return;
+    }
+#endif
     store_rec(recs, seq, r);
     const int k = out.n++;
     out.seq[k] = seq;
