@@ -218,6 +218,8 @@ __device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int mi
         return;
     }
 #endif
+    // (Measured and rejected: applying tile_may_cover to the 2..4 tiles of small triangles as well and handing
+    // the fill pass a mask -- 9 % fewer pairs, raster 113.3 -> 112.7 us, but setup 44 -> 50 us.)
     store_rec(recs, seq, r);
     const int k = out.n++;
     out.seq[k] = seq;
