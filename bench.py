@@ -243,8 +243,25 @@ def run_gpu(args):
         gather()
 
     host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+    host_rgb = [torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True) for _ in range(2)]
+    e2e_count = [0]
 
     def step_e2e():
+        """Host draw list in, presentable frame out (MainWindow.OnRender's packed RGB float array,
+        MainWindow.cs:232-246), every step.  The D2H copy of frame k runs on the library's copy stream while
+        frame k+1 is submitted and rendered; two pinned host frames alternate."""
+        N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
+        N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
+        N.check(ctx, L.srb_end_frame(ctx))
+        gather()
+        if rank == 0:
+            N.check(ctx, L.srb_present_rgb_async(ctx, C.c_void_p(host_rgb[e2e_count[0] & 1].data_ptr())))
+            e2e_count[0] += 1
+        if fused:
+            dist.all_reduce(token)              # band ranks must not start the next frame before rank 0 has flattened this one
+
+    def step_e2e_colorbuffer():
+        """Same, but the result is the float4 ColorBuffer itself, read synchronously (srb_read_color)."""
         N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
         N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
         N.check(ctx, L.srb_end_frame(ctx))
@@ -252,7 +269,7 @@ def run_gpu(args):
         if rank == 0:
             N.check(ctx, L.srb_read_color(ctx, C.c_void_p(host.data_ptr())))
         if fused:
-            dist.all_reduce(token)              # band ranks must not start the next frame while rank 0 still reads this one
+            dist.all_reduce(token)
 
     def timed(step, K, Wm, sampler=None):
         with torch.cuda.stream(ext):
@@ -290,7 +307,10 @@ def run_gpu(args):
     # e2e: host buffers in, host frame out, every step (wall clock: it includes host work by design)
     Ke = max(5, min(K, args.e2e_steps))
     ms_e, wall_e, _ = timed(step_e2e, Ke, 3)
-    fps_e = Ke / max(wall_e, ms_e / 1000.0)
+    fps_e = Ke / max(wall_e, ms_e / 1000.0)          # timed() ends with a device-wide synchronize: the last copies are inside
+    N.check(ctx, L.srb_present_wait(ctx))
+    ms_c, wall_c, _ = timed(step_e2e_colorbuffer, Ke, 3)
+    fps_c = Ke / max(wall_c, ms_c / 1000.0)
 
     # ---- per-stage device times (CUDA events on the pipeline stream), one synced frame at a time ----
     N.check(ctx, L.srb_set_profiling(ctx, 1))
@@ -357,9 +377,13 @@ def run_gpu(args):
                        "l2": "no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
                              if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush"},
             "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES + 8 * n_geom_blocks),
-                    "d2h_bytes_per_step": int(W * H * 16), "steps": Ke, "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke,
-                    "mpixels_per_sec": W * H * fps_e / 1e6},
-            "gpu_launches": int(st.kernel_launches) * K,
+                    "d2h_bytes_per_step": int(W * H * 12), "steps": Ke, "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke,
+                    "mpixels_per_sec": W * H * fps_e / 1e6,
+                    "result": "packed RGB float frame, the array MainWindow.OnRender uploads (MainWindow.cs:232-246), "
+                              "srb_present_rgb_async into two alternating pinned host frames; D2H of frame k overlaps frame k+1",
+                    "colorbuffer_float4_sync": {"value": fps_c, "unit": "frames/s", "d2h_bytes_per_step": int(W * H * 16),
+                                                "call": "srb_read_color"}},
+            "gpu_launches": int(st.kernel_launches) * K,          # timed region of `value`; each e2e step adds the flatten kernel
             "clocks": clocks,
             "stage_ms": stage_ms,
             "stage_ms_ranks": stage_ms_ranks,

@@ -153,7 +153,15 @@ int srb_sync(SrbContext* ctx);
 /* ---- readback: MainWindow.ColorBuffer/DepthBuffer + accessors (MainWindow.cs:378-436) ---- */
 int srb_read_color(SrbContext* ctx, float* rgba_out);            /* W*H*4 floats */
 int srb_read_depth(SrbContext* ctx, float* depth_out);           /* W*H floats */
-int srb_read_color_rgba8(SrbContext* ctx, uint8_t* rgba8_out);   /* present-format step, MainWindow.cs:234-250 */
+int srb_read_color_rgba8(SrbContext* ctx, uint8_t* rgba8_out);   /* 8-bit convenience copy (the parity metric's format) */
+/* Present path: MainWindow.OnRender flattens ColorBuffer to packed Vector3 and uploads it with
+ * TexSubImage2D(Rgb, Float) (MainWindow.cs:226-246).  srb_present_rgb delivers exactly that array
+ * (W*H*3 floats) to the host.  The _async form returns once the copy is queued on a second stream, so
+ * the next frame can be submitted and rendered while it runs; two copies may be outstanding (two
+ * different, preferably pinned, host buffers); srb_present_wait returns when they have landed. */
+int srb_present_rgb(SrbContext* ctx, float* rgb_out);
+int srb_present_rgb_async(SrbContext* ctx, float* rgb_out);
+int srb_present_wait(SrbContext* ctx);
 int srb_read_color_rows(SrbContext* ctx, float* rgba_out, int y0, int y1);
 int srb_get_pixel(SrbContext* ctx, int x, int y, float rgba_out[4]);   /* :390-398 */
 int srb_set_pixel(SrbContext* ctx, int x, int y, const float rgba[4]); /* :382-388 */

@@ -54,6 +54,13 @@ struct SrbContext {
     float4* color = nullptr;
     float* depth = nullptr;
     float4* colorTarget = nullptr;    // peer buffer opened from an IPC handle (band gather), or null
+    // present path: packed RGB float copies of finished frames, double buffered so that the D2H copy of
+    // frame k (copy stream) overlaps the rendering of frame k+1 (pipeline stream)
+    cudaStream_t copyStream = nullptr;
+    DevBuf<float> dPresent[2];
+    cudaEvent_t presentReady[2] = {}, presentCopied[2] = {};
+    bool presentBusy[2] = {false, false};
+    int presentSlot = 0;
     std::vector<MeshRes> meshes;      // handle = index + 1
     std::vector<TexRes> textures;
     std::mutex mu;
@@ -329,6 +336,12 @@ int srb_destroy(SrbContext* c) {
     c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dOrder.release(); c->dClip.release(); c->dWn.release();
     c->dRecsR.release(); c->dRecsS.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dBigQ.release(); c->dTileCount.release();
     c->dTileStart.release(); c->dTileCursor.release(); c->dBins.release(); c->dBinScratch.release();
+    if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
+    for (int s = 0; s < 2; ++s) {
+        c->dPresent[s].release();
+        if (c->presentReady[s]) cudaEventDestroy(c->presentReady[s]);
+        if (c->presentCopied[s]) cudaEventDestroy(c->presentCopied[s]);
+    }
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
     if (c->dCnt) cudaFree(c->dCnt);
@@ -785,6 +798,51 @@ int srb_read_color_rgba8(SrbContext* c, uint8_t* out) {
     CK(c, cudaMemcpyAsync(out, c->dBinScratch.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
     return SRB_OK;
+}
+
+/* Present path (MainWindow.cs:226-246).  Flatten on the device, copy on a second stream: the call returns
+ * once the copy is queued, and the next frame may be submitted and rendered while it runs. */
+int srb_present_rgb_async(SrbContext* c, float* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    int rc = srb_sync(c);                                  // frame finished and capacity overflows settled
+    if (rc != SRB_OK) return rc;
+    const size_t n = (size_t)c->W * c->H;
+    if (!c->copyStream) CK(c, cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
+    const int s = c->presentSlot;
+    c->presentSlot ^= 1;
+    if (!c->presentReady[s]) {
+        CK(c, cudaEventCreateWithFlags(&c->presentReady[s], cudaEventDisableTiming));
+        CK(c, cudaEventCreateWithFlags(&c->presentCopied[s], cudaEventDisableTiming));
+    }
+    if (c->presentBusy[s]) {                               // the copy that used this slot two frames ago
+        CK(c, cudaEventSynchronize(c->presentCopied[s]));
+        c->presentBusy[s] = false;
+    }
+    CK(c, c->dPresent[s].reserve(n * 3 + 16));
+    present_rgb_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color, c->dPresent[s].p, n);
+    CK(c, cudaGetLastError());
+    CK(c, cudaEventRecord(c->presentReady[s], c->stream));
+    CK(c, cudaStreamWaitEvent(c->copyStream, c->presentReady[s], 0));
+    CK(c, cudaMemcpyAsync(out, c->dPresent[s].p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->copyStream));
+    CK(c, cudaEventRecord(c->presentCopied[s], c->copyStream));
+    c->presentBusy[s] = true;
+    return SRB_OK;
+}
+
+int srb_present_wait(SrbContext* c) {
+    if (!c) return SRB_ERR_ARG;
+    CK(c, cudaSetDevice(c->device));
+    for (int s = 0; s < 2; ++s)
+        if (c->presentBusy[s]) {
+            CK(c, cudaEventSynchronize(c->presentCopied[s]));
+            c->presentBusy[s] = false;
+        }
+    return SRB_OK;
+}
+
+int srb_present_rgb(SrbContext* c, float* out) {
+    int rc = srb_present_rgb_async(c, out);
+    return rc != SRB_OK ? rc : srb_present_wait(c);
 }
 
 int srb_frustum_test(SrbContext* c, const float* spheres, const float* models, const float view[16],

@@ -125,11 +125,13 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
              uint32_t* __restrict__ tileCount, Counters* cnt) {
     const unsigned full = 0xffffffffu;
     __shared__ TileAgg agg;
+    __shared__ uint32_t sNoCover;
     const int2 blk = __ldg(tblocks + blockIdx.x);
     const int di = blk.x;
     const DrawRec& d = draws[di];
     if (!d.visible) return;                                   // uniform over the CTA
     agg_clear(agg);
+    if (threadIdx.x == 0) sNoCover = 0u;
     __syncthreads();
     const BigQueue bq{bigQ, cnt, fp.bigCap};
     const int t = blk.y + threadIdx.x;
@@ -166,8 +168,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         if (lane >= o) incl += v;
     }
     int total = __shfl_sync(full, incl, 31);
-    const int dropped = (int)__reduce_add_sync(full, (unsigned)out.nNoCover);
-    if (dropped > 0 && lane == 0) atomicAdd(&cnt->nNoCover, (uint32_t)dropped);
+    if (out.nNoCover) atomicAdd(&sNoCover, (uint32_t)out.nNoCover);      // statistics; flushed once per CTA below
     if (total > 0) {                                          // uniform over the warp
         uint32_t base = 0;
         if (lane == 31) base = atomicAdd(&cnt->nRefs, (uint32_t)total);
@@ -186,6 +187,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     }
     __syncthreads();
     agg_flush<0>(agg, tileCount);
+    if (threadIdx.x == 0 && sNoCover) atomicAdd(&cnt->nNoCover, sNoCover);
 }
 
 // ---------------------------------------------------------------------------

@@ -29,8 +29,14 @@ struct Counters {
     uint32_t overflow;            // bit0: bins, bit1: clip side buffer, bit2: large-triangle queue
     uint32_t nVisibleDraws;
     uint32_t nBig;                // entries in the large-triangle queue
+    uint32_t _pad0;
+    // Statistics only, on a cache line of their own: nRefs / nBig above are on the critical path of every
+    // setup warp (atomics with a return value), and one more counter on their line cost setup 5 us.
+    uint32_t _gap[24];
     uint32_t nNoCover;            // small triangles dropped because they provably cover no pixel
+    uint32_t _pad1[31];
 };
+static_assert(sizeof(Counters) == 256, "Counters layout");
 
 // ---------------------------------------------------------------------------
 // FrustumCuller.IsSphereInFrustum (FrustumCuller.cs:153-224, Plane ctor :19-28)

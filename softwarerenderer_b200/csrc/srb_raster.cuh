@@ -404,4 +404,23 @@ __global__ void pack_rgba8_kernel(const float4* __restrict__ color, uchar4* __re
     out[i] = make_uchar4(q(c.x), q(c.y), q(c.z), q(c.w));
 }
 
+// MainWindow.OnRender's flatten (MainWindow.cs:232-238): Vector4 colour -> packed Vector3, the layout the
+// reference hands to TexSubImage2D(Rgb, Float).  Four pixels per thread: 4 x 128-bit loads, 3 x 128-bit stores.
+__global__ void present_rgb_kernel(const float4* __restrict__ color, float* __restrict__ out, size_t n) {
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = q * 4;
+    if (i + 3 < n) {
+        const float4 a = color[i], b = color[i + 1], c = color[i + 2], d = color[i + 3];
+        float4* o = reinterpret_cast<float4*>(out) + q * 3;
+        __stcs(o, make_float4(a.x, a.y, a.z, b.x));
+        __stcs(o + 1, make_float4(b.y, b.z, c.x, c.y));
+        __stcs(o + 2, make_float4(c.z, d.x, d.y, d.z));
+    } else {
+        for (size_t k = i; k < n; ++k) {
+            const float4 a = color[k];
+            out[3 * k] = a.x; out[3 * k + 1] = a.y; out[3 * k + 2] = a.z;
+        }
+    }
+}
+
 }  // namespace srb

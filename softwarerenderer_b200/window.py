@@ -189,6 +189,18 @@ class MainWindow:
         N.check(self._ctx, N.lib().srb_read_color_rgba8(self._ctx, N.ptr(out)))
         return out
 
+    def PresentRgb(self, out: np.ndarray = None, wait: bool = True) -> np.ndarray:
+        """The array OnRender uploads (MainWindow.cs:232-246): ColorBuffer flattened to packed RGB floats.
+        wait=False queues the copy and returns (pass a pinned `out`; call PresentWait before reading it)."""
+        if out is None:
+            out = np.empty((self.RenderHeight, self.RenderWidth, 3), dtype=np.float32)
+        fn = N.lib().srb_present_rgb if wait else N.lib().srb_present_rgb_async
+        N.check(self._ctx, fn(self._ctx, N.ptr(out)))
+        return out
+
+    def PresentWait(self) -> None:
+        N.check(self._ctx, N.lib().srb_present_wait(self._ctx))
+
     # -- accessors (MainWindow.cs:378-427) ----------------------------------------
     def GetPixel(self, x: int, y: int) -> np.ndarray:
         out = (C.c_float * 4)()

@@ -141,3 +141,27 @@ def test_stress8k_full_size(oracle):
     stats = compare(gc, gd, oc, od)
     assert st.triangles_setup + st.triangles_no_coverage == ost.triangles_drawn
     print(stats)
+
+
+def test_present_rgb_matches_colorbuffer():
+    """srb_present_rgb[_async] delivers ColorBuffer[..., :3] (MainWindow.cs:232-246), also when two copies are
+    in flight and the next frame is already rendering."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import submit_scene
+    frames = [S.scene_model("Gun", 642, 361, view=S.gun_camera(k)) for k in (0, 3)]     # odd size: scalar tail path
+    win = srb.MainWindow(642, 361)
+    try:
+        want = []
+        for sc in frames:
+            submit_scene(win, sc)
+            want.append(win.ColorBuffer[..., :3].copy())
+            assert np.array_equal(win.PresentRgb(), want[-1])
+        outs = [np.zeros((361, 642, 3), np.float32) for _ in range(2)]
+        for k in range(6):                              # async, slots reused three times
+            submit_scene(win, frames[k & 1])
+            win.PresentRgb(outs[k & 1], wait=False)
+        win.PresentWait()
+        assert np.array_equal(outs[0], want[0]) and np.array_equal(outs[1], want[1])
+    finally:
+        win.Close()
