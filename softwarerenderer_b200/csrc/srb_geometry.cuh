@@ -22,17 +22,17 @@ struct FrameParams {
 
 // Device-side counters of one frame.
 struct Counters {
-    uint32_t nRefs;               // accepted triangles (compact list length)
+    uint32_t nRefs;               // accepted triangles (compact list length)   } one 64-bit word: the setup kernel
+    uint32_t nBig;                // entries in the large-triangle queue         } reserves both with ONE atomic per CTA
     uint32_t nPairs;              // total (triangle,tile) pairs (from the scan)
     uint32_t nClipped;            // ClipAttr entries used
     uint32_t nClippedTris;        // triangles that entered the clipper
     uint32_t overflow;            // bit0: bins, bit1: clip side buffer, bit2: large-triangle queue
     uint32_t nVisibleDraws;
-    uint32_t nBig;                // entries in the large-triangle queue
-    uint32_t _pad0;
+    uint32_t _pad0, _pad00;
     // Statistics only, on a cache line of their own: nRefs / nBig above are on the critical path of every
     // setup warp (atomics with a return value), and one more counter on their line cost setup 5 us.
-    uint32_t _gap[24];
+    uint32_t _gap[23];
     uint32_t nNoCover;            // small triangles dropped because they provably cover no pixel
     uint32_t _pad1[31];
 };
@@ -74,6 +74,7 @@ __device__ bool sphere_in_frustum(const float* sphere, const float* M, const flo
     return ok;
 }
 
+// (Measured, no effect on the 12 us stage: eight lanes per draw with one frustum plane each.)
 __global__ void frustum_draws_kernel(DrawRec* draws, int nDraws, int fma, Counters* cnt) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nDraws) return;
@@ -195,6 +196,7 @@ struct SetupOut {
     int nNoCover;          // triangles dropped by small_tri_may_cover (statistics only)
     uint32_t seq[2];
     uint32_t tx[2], ty[2]; // packed tile ranges
+    uint32_t bigMask;      // bit k: triangle k spans more than kSmallTiles tiles (goes to the large-triangle queue)
 };
 // Triangles that span more than kSmallTiles tiles are queued in shared memory and binned by the
 // whole CTA (cta_bin_big).
@@ -204,15 +206,9 @@ struct __align__(16) BigEntry {
     uint32_t seq, tx, ty, _pad;
 };
 static_assert(sizeof(BigEntry) == 48, "BigEntry is read as three float4");
-struct BigQueue {
-    BigEntry* q;
-    Counters* cnt;
-    uint32_t cap;
-};
-// Common tail of the accepted-triangle paths: band clamp, record store, big-queue push.
+// Common tail of the accepted-triangle paths: band clamp, no-coverage test, record store.
 __device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int minX, int maxX, int minY, int maxY,
-                                           const FrameParams& fp, const RecStore& recs, const BigQueue& bq,
-                                           SetupOut& out) {
+                                           const FrameParams& fp, const RecStore& recs, SetupOut& out) {
     const int ty0 = max(minY / kTile, fp.bandRow0), ty1 = min(maxY / kTile, fp.bandRow1 - 1);
     if (ty0 > ty1) return;
 #ifndef SRB_EXP_NO_SMALLCULL
@@ -225,27 +221,20 @@ __device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int mi
     }
 #endif
     // (Measured and rejected: applying tile_may_cover to the 2..4 tiles of small triangles as well and handing
-    // the fill pass a mask -- 9 % fewer pairs, raster 113.3 -> 112.7 us, but setup 44 -> 50 us.)
+    // the fill pass a mask -- 9 % fewer pairs, but raster only 113.3 -> 112.7 us.)
     store_rec(recs, seq, r);
     const int k = out.n++;
     out.seq[k] = seq;
     out.tx[k] = (uint32_t)(minX / kTile) | ((uint32_t)(maxX / kTile) << 16);
     out.ty[k] = (uint32_t)ty0 | ((uint32_t)ty1 << 16);
-    if ((maxX / kTile - minX / kTile + 1) * (ty1 - ty0 + 1) > kSmallTiles) {
-        const uint32_t slot = atomicAdd(&bq.cnt->nBig, 1u);
-        if (slot >= bq.cap) { atomicOr(&bq.cnt->overflow, 4u); return; }
-        BigEntry& e = bq.q[slot];
-        e.g = BinGeom{r.s0x, r.s0y, r.s1x, r.s1y, r.s2x, r.s2y, r.bx, r.by};
-        e.seq = seq; e.tx = out.tx[k]; e.ty = out.ty[k]; e._pad = 0u;
-    }
+    if ((maxX / kTile - minX / kTile + 1) * (ty1 - ty0 + 1) > kSmallTiles) out.bigMask |= 1u << k;
 }
 
 // Near-clipped triangle (Rasterizer.cs:95-160, 217-224).  Rare and divergent.
 __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int vbase, const int i3[3],
                                            const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
                                            const FrameParams& fp, const SrbUniforms& U, uint32_t gtri,
-                                           const RecStore& recs, ClipAttr* clipAttrs, Counters* cnt, const BigQueue& bq,
-                                           SetupOut& out) {
+                                           const RecStore& recs, ClipAttr* clipAttrs, Counters* cnt, SetupOut& out) {
     const bool fma = U.numerics_fma != 0;
     ClipVtx v[3];
 #pragma unroll
@@ -305,7 +294,7 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int 
         ca.draw = drawIndex;
         clipAttrs[slot] = ca;
         r.meta = 0x80000000u | slot;
-        accept_tri(r, 2u * gtri + (uint32_t)f, minX, maxX, minY, maxY, fp, recs, bq, out);
+        accept_tri(r, 2u * gtri + (uint32_t)f, minX, maxX, minY, maxY, fp, recs, out);
     }
 }
 
