@@ -66,6 +66,14 @@ __device__ __forceinline__ void agg_flush(TileAgg& a, uint32_t* __restrict__ til
 // spread over every SM.  Each (triangle, tile) pair passes the conservative tile test first
 // (about a quarter of the bbox tiles of large triangles drop out).
 // MODE 0 = count (tileCount += 1), MODE 1 = fill (bins[cursor++] = seq).
+constexpr int kBigSplit = 128;             // tiles per queue entry = one pass of the warp's 4 x 32 lanes
+__device__ __forceinline__ int big_rows(uint32_t tx) {                 // tile rows per entry
+    return max(1, kBigSplit / ((int)(tx >> 16) - (int)(tx & 0xffff) + 1));
+}
+__device__ __forceinline__ int big_parts(uint32_t tx, uint32_t ty) {   // queue entries of one large triangle
+    const int rows = big_rows(tx), ny = (int)(ty >> 16) - (int)(ty & 0xffff) + 1;
+    return (ny + rows - 1) / rows;
+}
 template <int MODE>
 __global__ void __launch_bounds__(256)
 bin_big_kernel(const BigEntry* __restrict__ q, const Counters* __restrict__ cnt, FrameParams fp,
@@ -163,7 +171,12 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     // (every reservation is a round trip on the same L2 address).  (Measured: one reservation per CTA
     // instead -- two more barriers -- city4k setup 44.3 -> 45.8 us, stress8k 703 -> 656 us.)
     const int lane = threadIdx.x & 31;
-    const int n = out.n, nb = __popc(out.bigMask);
+    // A large triangle takes one queue entry per <= kBigSplit tiles (whole tile rows): bin_big_kernel gives an
+    // entry to one warp, and the few triangles that span thousands of tiles would otherwise be its tail.
+    int nb = 0;
+    for (int k = 0; k < out.n; ++k)
+        if (out.bigMask >> k & 1u) nb += big_parts(out.tx[k], out.ty[k]);
+    const int n = out.n;
     uint32_t incl = (uint32_t)n | ((uint32_t)nb << 16);
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -185,14 +198,20 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
             rf.seq = out.seq[k]; rf.tx = out.tx[k]; rf.ty = out.ty[k]; rf._pad = 0;
             refs[ri] = rf;
             if (out.bigMask >> k & 1u) {
-                if (bi >= fp.bigCap) { atomicOr(&cnt->overflow, 4u); continue; }
+                const int parts = big_parts(out.tx[k], out.ty[k]);
+                if (bi + parts > fp.bigCap) { atomicOr(&cnt->overflow, 4u); bi += parts; continue; }
                 // the record this thread stored a moment ago: plain (coherent) loads, not the read-only path
                 const volatile float4* q = recs.R + 3 * (size_t)out.seq[k];
                 const float ax = q[0].x, ay = q[0].y, az = q[0].z, aw = q[0].w, bx = q[1].x, by = q[1].y;
                 const float cz = q[2].z, cw = q[2].w;
-                BigEntry& e = bigQ[bi++];
-                e.g = BinGeom{ax, ay, az, aw, bx, by, __float_as_uint(cz), __float_as_uint(cw)};
-                e.seq = out.seq[k]; e.tx = out.tx[k]; e.ty = out.ty[k]; e._pad = 0u;
+                const int y0 = out.ty[k] & 0xffff, y1 = out.ty[k] >> 16, rows = big_rows(out.tx[k]);
+                for (int y = y0; y <= y1; y += rows) {
+                    BigEntry& e = bigQ[bi++];
+                    e.g = BinGeom{ax, ay, az, aw, bx, by, __float_as_uint(cz), __float_as_uint(cw)};
+                    e.seq = out.seq[k]; e.tx = out.tx[k];
+                    e.ty = (uint32_t)y | ((uint32_t)min(y + rows - 1, y1) << 16);
+                    e._pad = 0u;
+                }
             }
         }
     }
