@@ -191,9 +191,19 @@ int launch_frame(SrbContext* c) {
         // grid-stride over the accepted-triangle list (its length is only known on the device)
         size_t maxRefs = 2 * (size_t)fp.totalT;
         unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
-        fill_bins_kernel<<<grid, 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
-        bin_big_kernel<1><<<c->smCount * 4, 256, 0, c->stream>>>(c->dBigQ.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
-        launches += 2;
+        // One launch or two: decided from the last completed frame's counters (a heuristic only -- both
+        // orders of filling give the same bins up to order, which no consumer depends on).
+        const uint32_t prevRefs = c->hCnt->nRefs, prevBig = c->hCnt->nBig;
+        const unsigned wave = (unsigned)c->smCount * 4;
+        if (prevBig > 0 && prevRefs <= wave * 256u) {
+            fill_merged_kernel<<<2 * wave, 256, 0, c->stream>>>(c->dRefs.p, c->dBigQ.p, c->dCnt, fp, c->dTileCursor.p,
+                                                               c->dBins.p, wave);
+        } else {
+            fill_bins_kernel<<<grid, 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
+            bin_big_kernel<1><<<wave, 256, 0, c->stream>>>(c->dBigQ.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
+            ++launches;
+        }
+        ++launches;
     }
     mark(5);
     RasterArgs A;

@@ -74,14 +74,16 @@ __device__ __forceinline__ int big_parts(uint32_t tx, uint32_t ty) {   // queue 
     const int rows = big_rows(tx), ny = (int)(ty >> 16) - (int)(ty & 0xffff) + 1;
     return (ny + rows - 1) / rows;
 }
+// (Measured, no gain: keeping the count pass's verdicts in the entry for the fill pass -- the passes wait
+// on their atomics, not on the test.)
 template <int MODE>
-__global__ void __launch_bounds__(256)
-bin_big_kernel(const BigEntry* __restrict__ q, const Counters* __restrict__ cnt, FrameParams fp,
-               uint32_t* __restrict__ tileCounter, uint32_t* __restrict__ bins) {
+__device__ __forceinline__ void bin_big_body(const BigEntry* __restrict__ q, const Counters* __restrict__ cnt,
+                                             const FrameParams& fp, uint32_t* __restrict__ tileCounter,
+                                             uint32_t* __restrict__ bins, const uint32_t block, const uint32_t nBlocks) {
     if (cnt->overflow) return;
     const uint32_t nq = min(cnt->nBig, fp.bigCap);
     const int lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nWarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t warp = (block * blockDim.x + threadIdx.x) >> 5, nWarps = (nBlocks * blockDim.x) >> 5;
     for (uint32_t e = warp; e < nq; e += nWarps) {
         const float4* p = reinterpret_cast<const float4*>(q + e);
         const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
@@ -116,6 +118,13 @@ bin_big_kernel(const BigEntry* __restrict__ q, const Counters* __restrict__ cnt,
             }
         }
     }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256)
+bin_big_kernel(const BigEntry* __restrict__ q, const Counters* __restrict__ cnt, FrameParams fp,
+               uint32_t* __restrict__ tileCounter, uint32_t* __restrict__ bins) {
+    bin_big_body<MODE>(q, cnt, fp, tileCounter, bins, blockIdx.x, gridDim.x);
 }
 
 // ---------------------------------------------------------------------------
@@ -358,13 +367,13 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
 // seq ids in arbitrary order (the visibility path is order-independent; the
 // ordered path sorts each bin by seq before use).
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-fill_bins_kernel(const TriRef* __restrict__ refs, const Counters* __restrict__ cnt, FrameParams fp,
-                 uint32_t* __restrict__ tileCursor, uint32_t* __restrict__ bins) {
-    __shared__ TileAgg agg;
+__device__ __forceinline__ void fill_small_body(const TriRef* __restrict__ refs, const Counters* __restrict__ cnt,
+                                                const FrameParams& fp, uint32_t* __restrict__ tileCursor,
+                                                uint32_t* __restrict__ bins, TileAgg& agg, const uint32_t block,
+                                                const uint32_t nBlocks) {
     const uint32_t nRefs = cnt->nRefs;
-    const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t base = blockIdx.x * blockDim.x; base < nRefs; base += stride) {     // uniform over the CTA
+    const uint32_t stride = nBlocks * blockDim.x;
+    for (uint32_t base = block * blockDim.x; base < nRefs; base += stride) {     // uniform over the CTA
         agg_clear(agg);
         __syncthreads();
         const uint32_t i = base + threadIdx.x;
@@ -372,7 +381,7 @@ fill_bins_kernel(const TriRef* __restrict__ refs, const Counters* __restrict__ c
         rf.seq = 0; rf.tx = 0; rf.ty = 0; rf._pad = 0;
         if (i < nRefs) rf = refs[i];
         const int nt = i < nRefs ? tile_range_count(rf.tx, rf.ty) : 0;
-        const int nSmall = nt <= kSmallTiles ? nt : 0;              // large ones: bin_big_kernel<1>
+        const int nSmall = nt <= kSmallTiles ? nt : 0;              // large ones: bin_big_body<1>
         uint32_t where[kSmallTiles];
 #pragma unroll
         for (int j = 0; j < kSmallTiles; ++j)
@@ -388,6 +397,25 @@ fill_bins_kernel(const TriRef* __restrict__ refs, const Counters* __restrict__ c
             }
         __syncthreads();
     }
+}
+
+__global__ void __launch_bounds__(256)
+fill_bins_kernel(const TriRef* __restrict__ refs, const Counters* __restrict__ cnt, FrameParams fp,
+                 uint32_t* __restrict__ tileCursor, uint32_t* __restrict__ bins) {
+    __shared__ TileAgg agg;
+    fill_small_body(refs, cnt, fp, tileCursor, bins, agg, blockIdx.x, gridDim.x);
+}
+
+// Both fill passes in one launch, for frames whose accepted list fits one wave: the two are independent and
+// each is a chain of atomic round trips that leaves the SMs mostly idle (city4k: 24 us as two launches,
+// 20 us as one).  The large-triangle CTAs come first so that both roles are resident together.  Frames with
+// millions of small triangles keep the lean fill kernel at full occupancy (this one needs twice the registers).
+__global__ void __launch_bounds__(256, 4)
+fill_merged_kernel(const TriRef* __restrict__ refs, const BigEntry* __restrict__ bigQ, const Counters* __restrict__ cnt,
+                   FrameParams fp, uint32_t* __restrict__ tileCursor, uint32_t* __restrict__ bins, const uint32_t nBigBlocks) {
+    __shared__ TileAgg agg;
+    if (blockIdx.x < nBigBlocks) bin_big_body<1>(bigQ, cnt, fp, tileCursor, bins, blockIdx.x, nBigBlocks);
+    else fill_small_body(refs, cnt, fp, tileCursor, bins, agg, blockIdx.x - nBigBlocks, gridDim.x - nBigBlocks);
 }
 
 }  // namespace srb
