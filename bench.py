@@ -194,7 +194,10 @@ def run_gpu(args):
     cuts = [band_rows(tiles_y, world, r)[0] for r in range(world)] + [tiles_y]
     if world > 1 and args.bands == "balanced":
         w_rows = win.TileRowPairs().astype(np.float64) + 0.85 * ((W + 15) // 16)     # an empty tile costs about 0.85 pair
-        cuts = balanced_cuts(w_rows, world)
+        # fused gather: the pixels of bands 1.. go to rank 0 as peer stores over NVLink, which costs their
+        # tile kernel about --remote-cost pairs per tile; band 0 takes correspondingly more rows
+        extra = args.remote_cost * ((W + 15) // 16) if args.gather == "fused" else 0.0
+        cuts = balanced_cuts(w_rows, world, remote_extra=extra)
     r0, r1 = cuts[rank], cuts[rank + 1]
     fused = world > 1 and args.gather == "fused"
     if world > 1:
@@ -441,6 +444,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=30)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"], help="N>1: how bands reach rank 0")
+    ap.add_argument("--remote-cost", type=float, default=12.0,
+                    help="N>1, fused gather: extra cost of a tile whose pixels are stored to rank 0 over NVLink, in bin pairs")
     ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"], help="N>1: band cut policy")
     args = ap.parse_args()
     if args.impl == "reference":

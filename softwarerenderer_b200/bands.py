@@ -20,10 +20,27 @@ def band_rows(tiles_y: int, n: int, r: int):
     return r0, r0 + base + (1 if r < rem else 0)
 
 
-def balanced_cuts(row_weights, n: int):
+def _cuts_for_limit(w, n, limit, remote_extra):
+    """Greedy fill: band k takes rows while its cost stays <= limit (rows of bands k >= 1 cost
+    remote_extra more).  Returns the cuts, or None when the rows do not fit into n bands."""
+    rows, cuts, r = len(w), [0], 0
+    for k in range(n):
+        extra = remote_extra if k > 0 else 0.0
+        acc, first = 0.0, r
+        last_allowed = rows - (n - 1 - k)                 # leave a row for each remaining band
+        while r < last_allowed and (r == first or acc + w[r] + extra <= limit):
+            acc += w[r] + extra
+            r += 1
+        cuts.append(r)
+    return cuts if r == rows else None
+
+
+def balanced_cuts(row_weights, n: int, remote_extra: float = 0.0):
     """Cut points [c_0=0, c_1, ..., c_n=rows] over tile rows such that every band carries about
     the same weight (the cost model of the caller: e.g. bin pairs + a constant per tile).  Every
-    band gets at least one row when rows >= n.  Deterministic: all ranks compute the same cuts."""
+    band gets at least one row when rows >= n.  Deterministic: all ranks compute the same cuts.
+    remote_extra > 0: every row of bands 1..n-1 costs that much more (their pixels travel to
+    rank 0 over NVLink); the cuts then minimise the largest band cost, so band 0 grows."""
     w = [float(x) for x in row_weights]
     rows = len(w)
     if n <= 0:
@@ -31,6 +48,17 @@ def balanced_cuts(row_weights, n: int):
     total = sum(w)
     if total <= 0.0 or rows < n:
         return [band_rows(rows, n, r)[0] for r in range(n)] + [rows]
+    if remote_extra > 0.0 and n > 1:
+        lo, hi = 0.0, total + remote_extra * rows
+        best = _cuts_for_limit(w, n, hi, remote_extra)
+        for _ in range(48):
+            mid = 0.5 * (lo + hi)
+            c = _cuts_for_limit(w, n, mid, remote_extra)
+            if c is None:
+                lo = mid
+            else:
+                hi, best = mid, c
+        return best
     cuts, acc, r = [0], 0.0, 0
     for k in range(1, n):
         target = total * k / n

@@ -161,7 +161,8 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), c->stream));
     if (c->profiling) cudaEventRecord(c->stageEv[0], c->stream);
     if (fp.nDraws > 0) {
-        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt);
+        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt, fp.H, fp.bandRow0,
+                                                                                    fp.bandRow1, fp.tilesY);
         ++launches;
     }
     mark(1);

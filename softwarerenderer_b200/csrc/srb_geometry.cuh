@@ -74,17 +74,63 @@ __device__ bool sphere_in_frustum(const float* sphere, const float* M, const flo
     return ok;
 }
 
+// Sort-first bands (multi-GPU): a context that renders only tile rows [bandRow0, bandRow1) can skip a draw whose
+// bounding sphere lies entirely above or below its band -- every triangle of it would fail the band clamp in
+// setup anyway (coverage is only ever evaluated inside a triangle's pixel bbox), so the image is unchanged and
+// the vertex / setup work of a rank shrinks with its band.  Same sphere-vs-plane form as the culler, the
+// +-1 of the top/bottom planes replaced by the band's NDC bounds.  Deliberately loose: one pixel row of slack
+// on either side, 1 % on the radius and a relative epsilon on the distance, because a wrongly kept draw costs
+// nothing but time while a wrongly dropped one would be a wrong image.
+__device__ bool sphere_misses_band(const float* sphere, const float* M, const float* V, const float* P,
+                                   int H, int bandRow0, int bandRow1, int tilesY) {
+    if (bandRow0 <= 0 && bandRow1 >= tilesY) return false;
+    const float4 wc = transform4<false>(make_float4(sphere[0], sphere[1], sphere[2], 1.0f), M);
+    const float s0 = sqrtf(M[0] * M[0] + M[1] * M[1] + M[2] * M[2]);
+    const float s1 = sqrtf(M[4] * M[4] + M[5] * M[5] + M[6] * M[6]);
+    const float s2 = sqrtf(M[8] * M[8] + M[9] * M[9] + M[10] * M[10]);
+    const float r = sphere[3] * fmaxf(fmaxf(s0, s1), s2);
+    float VP[16];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float4 row = transform4<false>(make_float4(V[4 * i], V[4 * i + 1], V[4 * i + 2], V[4 * i + 3]), P);
+        VP[4 * i] = row.x; VP[4 * i + 1] = row.y; VP[4 * i + 2] = row.z; VP[4 * i + 3] = row.w;
+    }
+    bool miss = false;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        if (side == 0 && bandRow0 <= 0) continue;              // nothing above the first row
+        if (side == 1 && bandRow1 >= tilesY) continue;
+        // pixel row y  <->  ndc_y = 1 - 2 y / H  (setup_tri); inside the band: ndc_y <= nyTop and ndc_y >= nyBot
+        const float yPix = side == 0 ? (float)(bandRow0 * kTile - 1) : (float)(bandRow1 * kTile + 1);
+        const float ny = 1.0f - 2.0f * yPix / (float)H;
+        const float sg = side == 0 ? 1.0f : -1.0f;             // inside: sg * (ny * w - y) >= 0
+        const float a = sg * (ny * VP[3] - VP[1]), b = sg * (ny * VP[7] - VP[5]);
+        const float c = sg * (ny * VP[11] - VP[9]), d = sg * (ny * VP[15] - VP[13]);
+        const float mag = sqrtf(a * a + b * b + c * c);
+        if (!(mag > 0.0f) || !isfinite(mag)) continue;
+        const float sd = (a * wc.x + b * wc.y + c * wc.z + d) / mag;
+        const float slack = 1.01f * r + 1e-3f * (fabsf(d) / mag + fabsf(wc.x) + fabsf(wc.y) + fabsf(wc.z)) + 1e-4f;
+        if (sd < -slack) miss = true;                          // false for NaN
+    }
+    return miss;
+}
+
 // (Measured, no effect on the 12 us stage: eight lanes per draw with one frustum plane each.)
-__global__ void frustum_draws_kernel(DrawRec* draws, int nDraws, int fma, Counters* cnt) {
+__global__ void frustum_draws_kernel(DrawRec* draws, int nDraws, int fma, Counters* cnt, int H, int bandRow0,
+                                     int bandRow1, int tilesY) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nDraws) return;
     DrawRec& d = draws[i];
     int vis = 1;
-    if (d.flags & SRB_DRAW_FRUSTUM_CULL)
+    if (d.flags & SRB_DRAW_FRUSTUM_CULL) {
         vis = fma ? sphere_in_frustum<true>(d.sphere, d.model, d.view, d.proj)
                   : sphere_in_frustum<false>(d.sphere, d.model, d.view, d.proj);
+        if (vis) atomicAdd(&cnt->nVisibleDraws, 1u);           // the reference's count, whatever the band
+        if (vis && sphere_misses_band(d.sphere, d.model, d.view, d.proj, H, bandRow0, bandRow1, tilesY)) vis = 0;
+    } else {
+        atomicAdd(&cnt->nVisibleDraws, 1u);
+    }
     d.visible = vis;
-    if (vis) atomicAdd(&cnt->nVisibleDraws, 1u);
 }
 
 __global__ void frustum_batch_kernel(const float* spheres, const float* models, const float* viewproj,
