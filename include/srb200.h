@@ -161,6 +161,13 @@ int srb_read_color_rgba8(SrbContext* ctx, uint8_t* rgba8_out);   /* 8-bit conven
  * different, preferably pinned, host buffers); srb_present_wait returns when they have landed. */
 int srb_present_rgb(SrbContext* ctx, float* rgb_out);
 int srb_present_rgb_async(SrbContext* ctx, float* rgb_out);
+/* Rows [y0,y1) only, written at their place in the full-frame array rgb_out points to.  Multi-GPU: every band
+ * rank delivers its own rows to one shared (pinned) host frame over its own PCIe link, in parallel. */
+int srb_present_rgb_rows_async(SrbContext* ctx, float* rgb_out, int y0, int y1);
+/* Device-side fence: work queued on the pipeline stream (srb_stream) after this call starts only when the
+ * present copies queued so far have landed.  A collective placed behind it is a "frame delivered" barrier
+ * across band ranks that never blocks the host. */
+int srb_present_fence(SrbContext* ctx);
 int srb_present_wait(SrbContext* ctx);
 int srb_read_color_rows(SrbContext* ctx, float* rgba_out, int y0, int y1);
 int srb_get_pixel(SrbContext* ctx, int x, int y, float rgba_out[4]);   /* :390-398 */

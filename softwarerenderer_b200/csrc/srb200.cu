@@ -813,11 +813,13 @@ int srb_read_color_rgba8(SrbContext* c, uint8_t* out) {
 
 /* Present path (MainWindow.cs:226-246).  Flatten on the device, copy on a second stream: the call returns
  * once the copy is queued, and the next frame may be submitted and rendered while it runs. */
-int srb_present_rgb_async(SrbContext* c, float* out) {
+int srb_present_rgb_rows_async(SrbContext* c, float* out, int y0, int y1) {
     if (!c || !out) return SRB_ERR_ARG;
+    if (y0 < 0 || y1 < y0 || y1 > c->H) return fail(c, SRB_ERR_ARG, "row range out of bounds");
     int rc = srb_sync(c);                                  // frame finished and capacity overflows settled
     if (rc != SRB_OK) return rc;
-    const size_t n = (size_t)c->W * c->H;
+    if (y1 == y0) return SRB_OK;
+    const size_t n = (size_t)c->W * (y1 - y0), first = (size_t)c->W * y0;
     if (!c->copyStream) CK(c, cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
     const int s = c->presentSlot;
     c->presentSlot ^= 1;
@@ -830,14 +832,18 @@ int srb_present_rgb_async(SrbContext* c, float* out) {
         c->presentBusy[s] = false;
     }
     CK(c, c->dPresent[s].reserve(n * 3 + 16));
-    present_rgb_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color, c->dPresent[s].p, n);
+    present_rgb_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color + first, c->dPresent[s].p, n);
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(c->presentReady[s], c->stream));
     CK(c, cudaStreamWaitEvent(c->copyStream, c->presentReady[s], 0));
-    CK(c, cudaMemcpyAsync(out, c->dPresent[s].p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->copyStream));
+    CK(c, cudaMemcpyAsync(out + first * 3, c->dPresent[s].p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->copyStream));
     CK(c, cudaEventRecord(c->presentCopied[s], c->copyStream));
     c->presentBusy[s] = true;
     return SRB_OK;
+}
+
+int srb_present_rgb_async(SrbContext* c, float* out) {
+    return c ? srb_present_rgb_rows_async(c, out, 0, c->H) : SRB_ERR_ARG;
 }
 
 int srb_present_wait(SrbContext* c) {
@@ -848,6 +854,14 @@ int srb_present_wait(SrbContext* c) {
             CK(c, cudaEventSynchronize(c->presentCopied[s]));
             c->presentBusy[s] = false;
         }
+    return SRB_OK;
+}
+
+int srb_present_fence(SrbContext* c) {
+    if (!c) return SRB_ERR_ARG;
+    CK(c, cudaSetDevice(c->device));
+    for (int s = 0; s < 2; ++s)
+        if (c->presentBusy[s]) CK(c, cudaStreamWaitEvent(c->stream, c->presentCopied[s], 0));
     return SRB_OK;
 }
 

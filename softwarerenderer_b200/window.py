@@ -198,6 +198,10 @@ class MainWindow:
         N.check(self._ctx, fn(self._ctx, N.ptr(out)))
         return out
 
+    def PresentRgbRows(self, out: np.ndarray, y0: int, y1: int) -> None:
+        """Queue the copy of rows [y0,y1) into the full-frame array `out` (band ranks, shared host frame)."""
+        N.check(self._ctx, N.lib().srb_present_rgb_rows_async(self._ctx, N.ptr(out), int(y0), int(y1)))
+
     def PresentWait(self) -> None:
         N.check(self._ctx, N.lib().srb_present_wait(self._ctx))
 
