@@ -157,7 +157,7 @@ class _DevArray:
 
 
 STAGES = ["frustum", "vertex", "setup_count", "scan", "fill", "sort", "tile_raster"]
-DRAW_REC_BYTES = 280
+DRAW_REC_BYTES = 352
 
 
 def run_gpu(args):

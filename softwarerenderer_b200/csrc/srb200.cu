@@ -20,7 +20,7 @@ namespace {
 
 thread_local std::string g_createError;
 
-struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
+struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; float4* blockSpheres = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
 struct TexRes { uchar4* px = nullptr; int w = 0, h = 0; bool opaque = true, alive = false; };
 
 template <typename T>
@@ -161,7 +161,7 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), c->stream));
     if (c->profiling) cudaEventRecord(c->stageEv[0], c->stream);
     if (fp.nDraws > 0) {
-        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt, fp.H, fp.bandRow0,
+        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt, fp.W, fp.H, fp.bandRow0,
                                                                                     fp.bandRow1, fp.tilesY);
         ++launches;
     }
@@ -342,7 +342,7 @@ int srb_destroy(SrbContext* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     close_color_target(c);
-    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); }
+    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
     c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dOrder.release(); c->dClip.release(); c->dWn.release();
     c->dRecsR.release(); c->dRecsS.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dBigQ.release(); c->dTileCount.release();
@@ -515,6 +515,32 @@ int srb_mesh_create(SrbContext* c, const float* vertices, int nV, const uint16_t
     CK(c, cudaMalloc((void**)&m.idx, std::max<size_t>((size_t)nI * 2, 16)));
     CK(c, cudaMemcpy(m.vtx, vertices, (size_t)nV * 48, cudaMemcpyHostToDevice));
     if (nI > 0) CK(c, cudaMemcpy(m.idx, indices, (size_t)nI * 2, cudaMemcpyHostToDevice));
+    {   // object-space bounding sphere of every run of kGeomBlock triangles (block culling in the setup kernel)
+        const int nT = nI / 3, nB = (nT + kGeomBlock - 1) / kGeomBlock;
+        std::vector<float4> sph((size_t)std::max(nB, 1), make_float4(0.0f, 0.0f, 0.0f, 3.0e38f));
+        for (int b = 0; b < nB; ++b) {
+            const int t0 = b * kGeomBlock, t1 = std::min(nT, t0 + kGeomBlock);
+            float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+            bool finite = true;
+            for (int i = 3 * t0; i < 3 * t1; ++i)
+                for (int k = 0; k < 3; ++k) {
+                    const float v = vertices[12 * (size_t)indices[i] + k];
+                    finite = finite && std::isfinite(v);
+                    lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v);
+                }
+            if (!finite) continue;                                        // radius stays huge: never culled
+            const double cx = 0.5 * ((double)lo[0] + hi[0]), cy = 0.5 * ((double)lo[1] + hi[1]), cz = 0.5 * ((double)lo[2] + hi[2]);
+            double r2 = 0.0;
+            for (int i = 3 * t0; i < 3 * t1; ++i) {
+                const float* v = vertices + 12 * (size_t)indices[i];
+                const double dx = v[0] - cx, dy = v[1] - cy, dz = v[2] - cz;
+                r2 = std::max(r2, dx * dx + dy * dy + dz * dz);
+            }
+            sph[b] = make_float4((float)cx, (float)cy, (float)cz, (float)(std::sqrt(r2) * 1.0001 + 1e-6));
+        }
+        CK(c, cudaMalloc((void**)&m.blockSpheres, sph.size() * sizeof(float4)));
+        CK(c, cudaMemcpy(m.blockSpheres, sph.data(), sph.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    }
     m.alive = true;
     std::lock_guard<std::mutex> lk(c->mu);
     c->meshes.push_back(m);
@@ -531,6 +557,7 @@ int srb_mesh_destroy(SrbContext* c, SrbMesh mesh) {
     cudaStreamSynchronize(c->stream);
     cudaFree(c->meshes[mesh - 1].vtx);
     cudaFree(c->meshes[mesh - 1].idx);
+    cudaFree(c->meshes[mesh - 1].blockSpheres);
     c->meshes[mesh - 1] = MeshRes();
     c->haveFrame = false;
     return SRB_OK;
@@ -652,6 +679,8 @@ int srb_end_frame(SrbContext* c) {
         d.vbase = (int32_t)totalV; d.tbase = (int32_t)totalT;
         d.cull = q.cull; d.depth_test = q.depth_test; d.blend = q.blend;
         d.flags = q.flags; d.visible = 1; d._pad = 0;
+        d.tblockSpheres = m.blockSpheres;
+        for (int k = 0; k < 4; ++k) d.planes[k] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
         for (int f = 0; f < m.nV; f += kGeomBlock) hV[iv++] = make_int2(i, f);
         for (int f = 0; f < m.nI / 3; f += kGeomBlock) hT[it++] = make_int2(i, f);
         totalV += m.nV; totalT += m.nI / 3;

@@ -147,6 +147,10 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     const int di = blk.x;
     const DrawRec& d = draws[di];
     if (!d.visible) return;                                   // uniform over the CTA
+#ifndef SRB_EXP_NO_BLOCKCULL
+    if ((fp.bandRow0 > 0 || fp.bandRow1 < fp.tilesY) && block_outside(d, blk.y / kGeomBlock))
+        return;                                               // uniform too: the whole block is off band / off screen
+#endif
     agg_clear(agg);
     if (threadIdx.x == 0) sNoCover = 0u;
     __syncthreads();

@@ -36,7 +36,11 @@ struct DrawRec {
     uint32_t flags;
     int32_t visible;          // written by the frustum kernel
     int32_t _pad;
+    const float4* tblockSpheres;  // object-space bounding sphere of every run of kGeomBlock triangles (mesh upload)
+    float4 planes[4];         // written by the frustum kernel: object-space half-spaces left/right/top/bottom of the
+                              // screen (top/bottom: of this context's band), nx,ny,nz,d normalised; inside: n.p + d >= 0
 };
+static_assert(sizeof(DrawRec) == 352, "DrawRec layout");
 
 // ---- triangle setup record, slot = 2*global_triangle + fan ----
 // s = screen coords of outputs {v2,v1,v0} (Rasterizer.cs:367,383-386),
