@@ -259,6 +259,13 @@ __device__ __forceinline__ bool inside3(float w0, float w1, float w2) {
     const bool le = (w0 <= 0.0f) & (w1 <= 0.0f) & (w2 <= 0.0f);
     return ge | le;
 }
+// The same decision for every input without a NaN, as two three-input min/max and two compares
+// (FMNMX3 on sm_100).  min/max skip a NaN operand where the compares above would all be false, so a NaN
+// edge value can be reported inside: the caller's interpolated depth is then NaN and must be rejected
+// there (which is what the reference's all-false compares amount to).
+__device__ __forceinline__ bool inside3_minmax(float w0, float w1, float w2) {
+    return (fminf(fminf(w0, w1), w2) >= 0.0f) | (fmaxf(fmaxf(w0, w1), w2) <= 0.0f);
+}
 // depth at a covered pixel (Rasterizer.cs:498-502).
 __device__ __forceinline__ float frag_depth(float d0, float d1, float d2, float invArea,
                                             float w0, float w1, float w2,
