@@ -78,15 +78,26 @@ struct SrbContext {
     DevBuf<DrawRec> dDraws;
     DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels
     int nVBlocks = 0, nTBlocks = 0;
-    DevBuf<float4> dClip, dWn;
-    DevBuf<float4> dRecsR, dRecsS;    // split setup records (RecStore)
+    DevBuf<float4> dClip;
     DevBuf<TriRef> dRefs;
-    DevBuf<ClipAttr> dClipAttrs;
     DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
-    DevBuf<uint32_t> dTileCount, dTileStart, dTileCursor, dBins, dBinScratch;
-    DevBuf<uint4> dOrder;             // tile launch order of the visibility kernel
-    Counters* dCnt = nullptr;
-    Counters* hCnt = nullptr;         // pinned
+    DevBuf<uint32_t> dTileCount, dBinScratch;
+    // Frame pipelining: the geometry stages of frame N+1 run on their own stream while the tile kernel of
+    // frame N is still running on `stream`.  Everything the tile kernel reads and the geometry stages write
+    // exists twice; frames alternate between the two sets.
+    struct FrameBufs {
+        DevBuf<float4> dWn;               // world normals (vertex stage -> shading)
+        DevBuf<float4> dRecsR, dRecsS;    // split setup records (RecStore)
+        DevBuf<ClipAttr> dClipAttrs;
+        DevBuf<uint32_t> dTileStart, dTileCursor, dBins;
+        DevBuf<uint4> dOrder;             // tile launch order of the visibility kernel
+        Counters* dCnt = nullptr;
+        Counters* hCnt = nullptr;         // pinned
+    } fb[2];
+    int slot = 0;                         // set used by the most recently launched frame
+    cudaStream_t geomStream = nullptr;
+    cudaEvent_t geomDone[2] = {}, rasterDone[2] = {}, inputsReady = nullptr;
+    bool rasterRecorded[2] = {false, false}, inputsDirty = false;
     DrawRec* hDraws = nullptr;        // pinned staging
     int2* hBlocks = nullptr;          // pinned staging: vertex blocks then triangle blocks
     size_t hDrawsCap = 0, hBlocksCap = 0;
@@ -152,39 +163,50 @@ int launch_frame(SrbContext* c) {
     const int bandTiles = (fp.bandRow1 - fp.bandRow0) * fp.tilesX;
     int launches = 0;
     int stage = 0;
-    auto mark = [&](int next) {       // close stages [stage, next) at this point of the stream
+    const uint32_t prevRefs = c->fb[c->slot].hCnt->nRefs, prevBig = c->fb[c->slot].hCnt->nBig;   // last launched frame (heuristics only)
+    const int s = c->slot ^ 1;
+    c->slot = s;
+    SrbContext::FrameBufs& B = c->fb[s];
+    cudaStream_t gs = c->geomStream;      // geometry + binning; the tile kernel stays on c->stream
+    auto mark = [&](int next) {       // close stages [stage, next) at this point of the pipeline
         if (!c->profiling) return;
-        for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], c->stream);
+        for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], stage + 1 <= 5 ? gs : c->stream);
     };
-    CK(c, cudaEventRecord(c->ev0, c->stream));
-    CK(c, cudaMemsetAsync(c->dCnt, 0, sizeof(Counters), c->stream));
-    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), c->stream));
-    if (c->profiling) cudaEventRecord(c->stageEv[0], c->stream);
+    if (c->inputsDirty) {             // draw table / block tables were uploaded on c->stream
+        CK(c, cudaEventRecord(c->inputsReady, c->stream));
+        CK(c, cudaStreamWaitEvent(gs, c->inputsReady, 0));
+        c->inputsDirty = false;
+    }
+    if (c->rasterRecorded[s]) CK(c, cudaStreamWaitEvent(gs, c->rasterDone[s], 0));   // the frame before last used this set
+    CK(c, cudaEventRecord(c->ev0, gs));
+    CK(c, cudaMemsetAsync(B.dCnt, 0, sizeof(Counters), gs));
+    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), gs));
+    if (c->profiling) cudaEventRecord(c->stageEv[0], gs);
     if (fp.nDraws > 0) {
-        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, c->stream>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, c->dCnt, fp.W, fp.H, fp.bandRow0,
+        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, gs>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
                                                                                     fp.bandRow1, fp.tilesY);
         ++launches;
     }
     mark(1);
     if (c->nVBlocks > 0) {
         if (U.numerics_fma)
-            vertex_kernel<true><<<c->nVBlocks, kGeomBlock, 0, c->stream>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, c->dWn.p);
+            vertex_kernel<true><<<c->nVBlocks, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, B.dWn.p);
         else
-            vertex_kernel<false><<<c->nVBlocks, kGeomBlock, 0, c->stream>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, c->dWn.p);
+            vertex_kernel<false><<<c->nVBlocks, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, B.dWn.p);
         ++launches;
     }
     mark(2);
     if (c->nTBlocks > 0) {
-        setup_kernel<<<c->nTBlocks, kGeomBlock, 0, c->stream>>>(
-            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, c->dWn.p, RecStore{c->dRecsR.p, c->dRecsS.p}, c->dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
-            c->dTileCount.p, c->dCnt);
-        bin_big_kernel<0><<<c->smCount * 4, 256, 0, c->stream>>>(c->dBigQ.p, c->dCnt, fp, c->dTileCount.p, nullptr);
+        setup_kernel<<<c->nTBlocks, kGeomBlock, 0, gs>>>(
+            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
+            c->dTileCount.p, B.dCnt);
+        bin_big_kernel<0><<<c->smCount * 4, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
         launches += 2;
     }
     mark(3);
     if (bandTiles > 0) {
-        scan_tiles_kernel<<<kScanCtas, 1024, 0, c->stream>>>(c->dTileCount.p, c->dTileStart.p, c->dTileCursor.p, c->dOrder.p,
-                                                     fp.bandRow0 * fp.tilesX, bandTiles, c->dCnt, fp.pairCap);
+        scan_tiles_kernel<<<kScanCtas, 1024, 0, gs>>>(c->dTileCount.p, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p,
+                                                     fp.bandRow0 * fp.tilesX, bandTiles, B.dCnt, fp.pairCap);
         ++launches;
     }
     mark(4);
@@ -194,23 +216,24 @@ int launch_frame(SrbContext* c) {
         unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
         // One launch or two: decided from the last completed frame's counters (a heuristic only -- both
         // orders of filling give the same bins up to order, which no consumer depends on).
-        const uint32_t prevRefs = c->hCnt->nRefs, prevBig = c->hCnt->nBig;
         const unsigned wave = (unsigned)c->smCount * 4;
         if (prevBig > 0 && prevRefs <= wave * 256u) {
-            fill_merged_kernel<<<2 * wave, 256, 0, c->stream>>>(c->dRefs.p, c->dBigQ.p, c->dCnt, fp, c->dTileCursor.p,
-                                                               c->dBins.p, wave);
+            fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(c->dRefs.p, c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
+                                                               B.dBins.p, wave);
         } else {
-            fill_bins_kernel<<<grid, 256, 0, c->stream>>>(c->dRefs.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
-            bin_big_kernel<1><<<wave, 256, 0, c->stream>>>(c->dBigQ.p, c->dCnt, fp, c->dTileCursor.p, c->dBins.p);
+            fill_bins_kernel<<<grid, 256, 0, gs>>>(c->dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
+            bin_big_kernel<1><<<wave, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
             ++launches;
         }
         ++launches;
     }
     mark(5);
+    CK(c, cudaEventRecord(c->geomDone[s], gs));
+    CK(c, cudaStreamWaitEvent(c->stream, c->geomDone[s], 0));
     RasterArgs A;
-    A.draws = c->dDraws.p; A.order = c->dOrder.p; A.wn = c->dWn.p; A.recs.R = c->dRecsR.p; A.recs.S = c->dRecsS.p;
-    A.clipAttrs = c->dClipAttrs.p; A.tileStart = c->dTileStart.p; A.tileEnd = c->dTileCursor.p;
-    A.bins = c->dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = c->dCnt;
+    A.draws = c->dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p;
+    A.clipAttrs = B.dClipAttrs.p; A.tileStart = B.dTileStart.p; A.tileEnd = B.dTileCursor.p;
+    A.bins = B.dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = B.dCnt;
     A.colorOut = c->colorTarget ? c->colorTarget : c->color;
 #ifdef SRB_TILE_TIMING
     if (c->dBinScratch.reserve((size_t)nTiles * 8) != cudaSuccess) return fail(c, SRB_ERR_CUDA, "dbg alloc");
@@ -227,8 +250,8 @@ int launch_frame(SrbContext* c) {
             }
             ++launches;
         } else {
-            sort_bins_kernel<<<bandTiles, 256, 0, c->stream>>>(c->dTileStart.p, c->dTileCursor.p, c->dBins.p,
-                                                              c->dBinScratch.p, fp.bandRow0 * fp.tilesX, c->dCnt);
+            sort_bins_kernel<<<bandTiles, 256, 0, c->stream>>>(B.dTileStart.p, B.dTileCursor.p, B.dBins.p,
+                                                              c->dBinScratch.p, fp.bandRow0 * fp.tilesX, B.dCnt);
             mark(6);
             ordered_tile_kernel<<<bandTiles, 256, 0, c->stream>>>(A, fp, U);
             launches += 2;
@@ -236,7 +259,9 @@ int launch_frame(SrbContext* c) {
     }
     mark(7);
     CK(c, cudaGetLastError());
-    CK(c, cudaMemcpyAsync(c->hCnt, c->dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaMemcpyAsync(B.hCnt, B.dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaEventRecord(c->rasterDone[s], c->stream));
+    c->rasterRecorded[s] = true;
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches = launches;
     c->stats.pipeline_used = c->useVis ? SRB_PIPELINE_VISIBILITY : SRB_PIPELINE_ORDERED;
@@ -249,20 +274,20 @@ int complete_frame(SrbContext* c) {
     CK(c, cudaStreamSynchronize(c->stream));
     if (!c->framePending) return SRB_OK;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        const Counters& k = *c->hCnt;
+        const Counters& k = *c->fb[c->slot].hCnt;
         if (!k.overflow) break;
         if (c->fp.loadColor || c->fp.loadDepth)
             return fail(c, SRB_ERR_STATE, "bin overflow on a frame that preserves the framebuffer; cannot re-run");
         if (k.overflow & 1u) {
             size_t want = (size_t)k.nPairs + k.nPairs / 8 + 1024;
-            CK(c, c->dBins.reserve(want));
-            CK(c, c->dBinScratch.reserve(c->dBins.cap));
-            c->fp.pairCap = (uint32_t)std::min<size_t>(c->dBins.cap, 0xffffffffu);
+            for (auto& b : c->fb) CK(c, b.dBins.reserve(want));
+            CK(c, c->dBinScratch.reserve(c->fb[0].dBins.cap));
+            c->fp.pairCap = (uint32_t)std::min<size_t>(std::min(c->fb[0].dBins.cap, c->fb[1].dBins.cap), 0xffffffffu);
         }
         if (k.overflow & 2u) {
             size_t want = std::max<size_t>(4 * (size_t)k.nClipped, 4096);
-            CK(c, c->dClipAttrs.reserve(want));
-            c->fp.clipCap = (uint32_t)c->dClipAttrs.cap;
+            for (auto& b : c->fb) CK(c, b.dClipAttrs.reserve(want));
+            c->fp.clipCap = (uint32_t)std::min(c->fb[0].dClipAttrs.cap, c->fb[1].dClipAttrs.cap);
         }
         if (k.overflow & 4u) {
             CK(c, c->dBigQ.reserve((size_t)k.nBig + k.nBig / 4 + 1024));
@@ -272,9 +297,9 @@ int complete_frame(SrbContext* c) {
         if (rc != SRB_OK) return rc;
         CK(c, cudaStreamSynchronize(c->stream));
     }
-    if (c->hCnt->overflow) return fail(c, SRB_ERR_CUDA, "bin capacity overflow persisted after regrow");
+    if (c->fb[c->slot].hCnt->overflow) return fail(c, SRB_ERR_CUDA, "bin capacity overflow persisted after regrow");
     c->framePending = false;
-    const Counters& k = *c->hCnt;
+    const Counters& k = *c->fb[c->slot].hCnt;
     c->stats.draws_visible = k.nVisibleDraws;
     c->stats.triangles_setup = k.nRefs;
     c->stats.triangles_no_coverage = (int32_t)k.nNoCover;
@@ -328,9 +353,19 @@ int srb_create(int device, int width, int height, SrbContext** out_ctx) {
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail("cudaEventCreate", e);
-    if ((e = cudaMalloc((void**)&c->dCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc", e);
-    if ((e = cudaMallocHost((void**)&c->hCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMallocHost", e);
-    std::memset(c->hCnt, 0, sizeof(Counters));
+    {   // geometry kernels are short and latency-bound: let their CTAs go ahead of the queued tile CTAs of the previous frame
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        if ((e = cudaStreamCreateWithPriority(&c->geomStream, cudaStreamNonBlocking, hi)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    }
+    if ((e = cudaEventCreateWithFlags(&c->inputsReady, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    for (int s = 0; s < 2; ++s) {
+        if ((e = cudaEventCreateWithFlags(&c->geomDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->rasterDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaMalloc((void**)&c->fb[s].dCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc", e);
+        if ((e = cudaMallocHost((void**)&c->fb[s].hCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMallocHost", e);
+        std::memset(c->fb[s].hCnt, 0, sizeof(Counters));
+    }
     int rc = alloc_framebuffer(c, width, height);
     if (rc != SRB_OK) { g_createError = c->err; delete c; return rc; }
     *out_ctx = c;
@@ -344,9 +379,20 @@ int srb_destroy(SrbContext* c) {
     close_color_target(c);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
-    c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dOrder.release(); c->dClip.release(); c->dWn.release();
-    c->dRecsR.release(); c->dRecsS.release(); c->dRefs.release(); c->dClipAttrs.release(); c->dBigQ.release(); c->dTileCount.release();
-    c->dTileStart.release(); c->dTileCursor.release(); c->dBins.release(); c->dBinScratch.release();
+    c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dClip.release();
+    c->dRefs.release(); c->dBigQ.release(); c->dTileCount.release(); c->dBinScratch.release();
+    for (auto& b : c->fb) {
+        b.dWn.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
+        b.dTileCursor.release(); b.dBins.release(); b.dOrder.release();
+        if (b.dCnt) cudaFree(b.dCnt);
+        if (b.hCnt) cudaFreeHost(b.hCnt);
+    }
+    for (int s = 0; s < 2; ++s) {
+        if (c->geomDone[s]) cudaEventDestroy(c->geomDone[s]);
+        if (c->rasterDone[s]) cudaEventDestroy(c->rasterDone[s]);
+    }
+    if (c->inputsReady) cudaEventDestroy(c->inputsReady);
+    if (c->geomStream) { cudaStreamSynchronize(c->geomStream); cudaStreamDestroy(c->geomStream); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
     for (int s = 0; s < 2; ++s) {
         c->dPresent[s].release();
@@ -355,8 +401,6 @@ int srb_destroy(SrbContext* c) {
     }
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
-    if (c->dCnt) cudaFree(c->dCnt);
-    if (c->hCnt) cudaFreeHost(c->hCnt);
     if (c->hDraws) cudaFreeHost(c->hDraws);
     if (c->hBlocks) cudaFreeHost(c->hBlocks);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -709,19 +753,21 @@ int srb_end_frame(SrbContext* c) {
     CK(c, c->dDraws.reserve((size_t)nDraws + 1));
     CK(c, c->dVBlocks.reserve(nVB + 1));
     CK(c, c->dTBlocks.reserve(nTB + 1));
-    CK(c, c->dOrder.reserve(nTiles));
+    for (auto& b : c->fb) CK(c, b.dOrder.reserve(nTiles));
     CK(c, c->dClip.reserve((size_t)totalV + 1));
-    CK(c, c->dWn.reserve((size_t)totalV + 1));
-    CK(c, c->dRecsR.reserve(3 * (2 * (size_t)totalT + 2)));
-    CK(c, c->dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
+    for (auto& b : c->fb) {
+        CK(c, b.dWn.reserve((size_t)totalV + 1));
+        CK(c, b.dRecsR.reserve(3 * (2 * (size_t)totalT + 2)));
+        CK(c, b.dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
+        CK(c, b.dClipAttrs.reserve(4096));
+        CK(c, b.dTileStart.reserve(nTiles));
+        CK(c, b.dTileCursor.reserve(nTiles));
+        CK(c, b.dBins.reserve(std::max<size_t>(1u << 20, 3 * (size_t)totalT)));
+    }
     CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
-    CK(c, c->dClipAttrs.reserve(4096));
     CK(c, c->dBigQ.reserve(1u << 16));
     CK(c, c->dTileCount.reserve(nTiles));
-    CK(c, c->dTileStart.reserve(nTiles));
-    CK(c, c->dTileCursor.reserve(nTiles));
-    CK(c, c->dBins.reserve(std::max<size_t>(1u << 20, 3 * (size_t)totalT)));
-    CK(c, c->dBinScratch.reserve(c->dBins.cap));
+    CK(c, c->dBinScratch.reserve(std::max(c->fb[0].dBins.cap, c->fb[1].dBins.cap)));
     if (nDraws > 0) {
         CK(c, cudaMemcpyAsync(c->dDraws.p, c->hDraws, (size_t)nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, c->stream));
     }
@@ -732,8 +778,8 @@ int srb_end_frame(SrbContext* c) {
     fp.W = c->W; fp.H = c->H; fp.tilesX = c->tilesX; fp.tilesY = c->tilesY;
     fp.bandRow0 = c->band0; fp.bandRow1 = c->band1;
     fp.nDraws = nDraws; fp.totalV = (int)totalV; fp.totalT = (int)totalT;
-    fp.pairCap = (uint32_t)std::min<size_t>(c->dBins.cap, 0xffffffffu);
-    fp.clipCap = (uint32_t)c->dClipAttrs.cap;
+    fp.pairCap = (uint32_t)std::min<size_t>(std::min(c->fb[0].dBins.cap, c->fb[1].dBins.cap), 0xffffffffu);
+    fp.clipCap = (uint32_t)std::min(c->fb[0].dClipAttrs.cap, c->fb[1].dClipAttrs.cap);
     fp.bigCap = (uint32_t)c->dBigQ.cap;
     std::memcpy(fp.clearColor, c->clear, 16);
     fp.loadColor = (c->clearFlags & SRB_CLEAR_COLOR) ? 0 : 1;
@@ -742,6 +788,7 @@ int srb_end_frame(SrbContext* c) {
     c->stats.draws_submitted = nDraws;
     c->stats.triangles_submitted = totalT;
     c->haveFrame = true;
+    c->inputsDirty = true;            // the uploads above are on c->stream; the geometry stream waits for them
     return launch_frame(c);
 }
 
@@ -750,7 +797,7 @@ int srb_replay_frame(SrbContext* c) {
     if (!c->haveFrame || c->inFrame) return fail(c, SRB_ERR_STATE, "no resident frame to replay");
     if (c->fp.loadColor || c->fp.loadDepth) return fail(c, SRB_ERR_STATE, "cannot replay a frame that preserves the framebuffer");
     CK(c, cudaSetDevice(c->device));
-    if (c->framePending && c->hCnt->overflow) {       // conservative: settle capacities first
+    if (c->framePending && c->fb[c->slot].hCnt->overflow) {       // conservative: settle capacities first
         int rc = complete_frame(c);
         if (rc != SRB_OK) return rc;
     }
