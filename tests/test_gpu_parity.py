@@ -165,3 +165,33 @@ def test_present_rgb_matches_colorbuffer():
         assert np.array_equal(outs[0], want[0]) and np.array_equal(outs[1], want[1])
     finally:
         win.Close()
+
+
+def test_pipelined_frames_do_not_disturb_each_other():
+    """Frames are pipelined (geometry of frame N+1 beside the tile kernel of frame N, two buffer sets): a burst
+    of frames without any synchronisation in between -- replays of one scene, then two different scenes
+    alternating -- must leave exactly the image of the last frame."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import submit_scene
+    a = S.scene_city(1280, 720, n_instances=12)
+    b = S.scene_model("Gun", 1280, 720, view=S.gun_camera(4))
+    win = srb.MainWindow(1280, 720)
+    try:
+        submit_scene(win, a)
+        want_a = (win.ColorBuffer.copy(), win.DepthBuffer.copy())
+        submit_scene(win, b)
+        want_b = (win.ColorBuffer.copy(), win.DepthBuffer.copy())
+        submit_scene(win, a)
+        for _ in range(25):
+            win.ReplayFrame()
+        assert np.array_equal(win.ColorBuffer, want_a[0]) and np.array_equal(win.DepthBuffer, want_a[1])
+        for k in range(9):                                  # a b a b ... a b a, no read-back in between
+            submit_scene(win, a if k % 2 == 0 else b)
+        assert np.array_equal(win.ColorBuffer, want_a[0]) and np.array_equal(win.DepthBuffer, want_a[1])
+        submit_scene(win, b)
+        for _ in range(7):
+            win.ReplayFrame()
+        assert np.array_equal(win.ColorBuffer, want_b[0]) and np.array_equal(win.DepthBuffer, want_b[1])
+    finally:
+        win.Close()
