@@ -495,7 +495,7 @@ def main():
     ap.add_argument("--impl", default="srb200", choices=["srb200", "reference"])
     ap.add_argument("--workload", default="city4k", choices=sorted(WORKLOADS))
     ap.add_argument("--pipeline", type=int, default=0, help="0 auto, 1 ordered, 2 visibility")
-    ap.add_argument("--e2e-steps", type=int, default=30)
+    ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"], help="N>1: how bands reach rank 0")
     ap.add_argument("--remote-cost", type=float, default=12.0,

