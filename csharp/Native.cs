@@ -20,7 +20,8 @@ namespace SoftwareRenderer
         public int NumericsFma;                 // 1 on FMA hardware under net9.0
         public int TexFilter;                   // 0 = Texture.Sample (nearest, repeat)
         public int NExtraLights;
-        public fixed int Pad[2];
+        public int DebugMode;                   // (int)Rasterizer.RenderDebugMode: 0 None, 1 Wireframe
+        public int Pad;
         public fixed float ExtraDir[16];
         public fixed float ExtraColor[16];
     }

@@ -41,6 +41,8 @@ enum { SRB_CULL_NONE = 0, SRB_CULL_BACK = 1, SRB_CULL_FRONT = 2 };
 enum { SRB_DEPTH_DISABLED = 0, SRB_DEPTH_LESS = 1, SRB_DEPTH_LESS_EQUAL = 2, SRB_DEPTH_GREATER = 3,
        SRB_DEPTH_GREATER_EQUAL = 4, SRB_DEPTH_EQUAL = 5, SRB_DEPTH_NOT_EQUAL = 6, SRB_DEPTH_ALWAYS = 7 };
 enum { SRB_BLEND_NONE = 0, SRB_BLEND_ALPHA = 1, SRB_BLEND_ADDITIVE = 2, SRB_BLEND_MULTIPLY = 3 };
+/* Rasterizer.DebugMode (Rasterizer.cs:14-18), same values. */
+enum { SRB_DEBUG_NONE = 0, SRB_DEBUG_WIREFRAME = 1 };
 
 /* srb_begin_frame flags */
 #define SRB_CLEAR_COLOR 1u     /* MainWindow.ClearColorBuffer (MainWindow.cs:400-407) */
@@ -70,7 +72,9 @@ typedef struct SrbUniforms {
     int32_t numerics_fma;     /* 1 = System.Numerics Transform/Lerp fused (net9.0 on FMA hardware) */
     int32_t tex_filter;       /* 0 nearest+repeat (Texture.cs:42-63); 1 bilinear+repeat (extension) */
     int32_t n_extra_lights;   /* extension: 0..4 extra directional lights */
-    int32_t _pad[2];
+    int32_t debug_mode;       /* Rasterizer.RenderDebugMode (Rasterizer.cs:14-22): 0 None, 1 Wireframe (every triangle is
+                                 drawn as three DrawLine calls, Rasterizer.cs:419-425, 232-340; ordered pipeline only) */
+    int32_t _pad;
     float extra_dir[4][4];
     float extra_color[4][4];
 } SrbUniforms;

@@ -369,7 +369,7 @@ inline void interpolate(const SetupTri& t, float w0, float w1, float w2,
 struct LocalStats { int64_t tested = 0, shaded = 0; };
 
 // Pixel loops of RasterizeTriangle for one tile (Rasterizer.cs:466-536).
-inline void raster_tile(OrcWindow& win, const SetupTri& t, const OrcDraw& d, const OrcUniforms& U,
+inline void raster_tile_fill(OrcWindow& win, const SetupTri& t, const OrcDraw& d, const OrcUniforms& U,
                         int tileX, int tileY, LocalStats& st) {
     const int W = win.W, H = win.H;
     int tsx = tileX * kTile, tsy = tileY * kTile;
@@ -411,6 +411,66 @@ inline void raster_tile(OrcWindow& win, const SetupTri& t, const OrcDraw& d, con
         }
         w0Row += t.b12; w1Row += t.b20; w2Row += t.b01;                       // :532-534
     }
+}
+
+
+// DebugMode.Wireframe (Rasterizer.cs:419-425): the triangle is three DrawLine calls (Rasterizer.cs:232-340)
+// over (s0,s1), (s1,s2), (s2,s0) -- every one of them with depths[0..1] and outputs[0..1] of the triangle,
+// as the reference passes them.  This is the part of those three calls that falls into one tile; pixels are
+// independent of each other, so running line after line per tile is the reference's per-pixel order.
+inline void raster_tile_wire(OrcWindow& win, const SetupTri& t, const OrcDraw& d, const OrcUniforms& U,
+                             int tileX, int tileY, LocalStats& st) {
+    const int W = win.W, H = win.H;
+    int tsx = tileX * kTile, tsy = tileY * kTile;
+    int tex_ = tsx + kTile - 1; if (tex_ > W - 1) tex_ = W - 1;
+    int tey = tsy + kTile - 1; if (tey > H - 1) tey = H - 1;
+    SetupTri ends = t;                                   // Interpolate(outputs[0], outputs[1], outputs[0], 1-t, t, 0) (:314)
+    ends.cz[2] = t.cz[0]; ends.cw[2] = t.cw[0]; ends.col[2] = t.col[0]; ends.uv[2] = t.uv[0]; ends.wn[2] = t.wn[0];
+    for (int k = 0; k < 3; ++k) {
+        const V2 p0 = t.s[k], p1 = t.s[(k + 1) % 3];
+        int minX = sat_int(net_max(net_min(p0.x, p1.x), 0.0f));                    // :242-245
+        int maxX = sat_int(net_min(net_max(p0.x, p1.x), (float)(W - 1)));
+        int minY = sat_int(net_max(net_min(p0.y, p1.y), 0.0f));
+        int maxY = sat_int(net_min(net_max(p0.y, p1.y), (float)(H - 1)));
+        if (minX > maxX || minY > maxY) continue;                                  // :247
+        int startX = minX > tsx ? minX : tsx, endX = maxX < tex_ ? maxX : tex_;    // :274-277
+        int startY = minY > tsy ? minY : tsy, endY = maxY < tey ? maxY : tey;
+        if (startX > endX || startY > endY) continue;
+        float dx = p1.x - p0.x, dy = p1.y - p0.y;                                  // :257-259
+        float lenSq = dx * dx + dy * dy;
+        for (int y = startY; y <= endY; ++y) {
+            for (int x = startX; x <= endX; ++x) {
+                float cx = (float)x + 0.5f, cy = (float)y + 0.5f;
+                float px = cx - p0.x, py = cy - p0.y;                              // :296-297
+                float tt = 0.0f;
+                if (lenSq > 0) tt = (px * dx + py * dy) / lenSq;                   // :299-301
+                tt = net_max(0.0f, net_min(1.0f, tt));                             // :303
+                float closestX = p0.x + tt * dx, closestY = p0.y + tt * dy;
+                float distX = cx - closestX, distY = cy - closestY;
+                float distSq = distX * distX + distY * distY;
+                if (!(distSq <= 0.25f)) continue;                                  // :312-313
+                ++st.tested;
+                float omt = 1.0f - tt;
+                float depth = 1.0f / (t.d[0] * omt + t.d[1] * tt);                 // :315
+                size_t idx = (size_t)y * W + x;
+                if (!depth_pass(d.depth_test, depth, win.depth[idx])) continue;    // :318-319
+                ++st.shaded;
+                V3 wn; V4 col; V2 uv; float cz;
+                interpolate(ends, omt, tt, 0.0f, wn, col, uv, cz);
+                V4 c = fragment_shader(wn, col, uv, cz, d, U);
+                if (c.w != 0.0f) {                                                 // :325 (W != 0, not > 0)
+                    win.color[idx] = blend(c, win.color[idx], d.blend);
+                    if (d.depth_test != 0) win.depth[idx] = depth;                 // :331-332
+                }
+            }
+        }
+    }
+}
+
+inline void raster_tile(OrcWindow& win, const SetupTri& t, const OrcDraw& d, const OrcUniforms& U,
+                        int tileX, int tileY, LocalStats& st) {
+    if (U.debug_mode == 1) raster_tile_wire(win, t, d, U, tileX, tileY, st);
+    else raster_tile_fill(win, t, d, U, tileX, tileY, st);
 }
 
 // Body of the Parallel.For lambda in RenderMesh (Rasterizer.cs:200-229):

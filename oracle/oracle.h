@@ -34,7 +34,8 @@ typedef struct OrcUniforms {
     int32_t numerics_fma;    /* 1: System.Numerics Transform/Lerp fused (net9 on FMA hw) */
     int32_t tex_filter;      /* 0 nearest+repeat (reference); 1 bilinear+repeat (extension) */
     int32_t n_extra_lights;  /* extension: extra directional lights, 0..4 */
-    int32_t _pad[2];
+    int32_t debug_mode;      /* Rasterizer.RenderDebugMode: 0 None, 1 Wireframe (Rasterizer.cs:419-425) */
+    int32_t _pad;
     float extra_dir[4][4];
     float extra_color[4][4];
 } OrcUniforms;

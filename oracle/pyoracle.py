@@ -21,7 +21,7 @@ class OrcUniforms(C.Structure):
         ("light_dir", C.c_float * 4), ("light_color", C.c_float * 4), ("fog_color", C.c_float * 4),
         ("fog_start", C.c_float), ("fog_end", C.c_float), ("near_clip", C.c_float),
         ("numerics_fma", C.c_int32), ("tex_filter", C.c_int32), ("n_extra_lights", C.c_int32),
-        ("_pad", C.c_int32 * 2), ("extra_dir", (C.c_float * 4) * 4), ("extra_color", (C.c_float * 4) * 4),
+        ("debug_mode", C.c_int32), ("_pad", C.c_int32), ("extra_dir", (C.c_float * 4) * 4), ("extra_color", (C.c_float * 4) * 4),
     ]
 
 
@@ -88,6 +88,7 @@ def make_uniforms(scene) -> OrcUniforms:
         u.fog_color[i] = float(scene.fog_color[i])
     u.fog_start, u.fog_end, u.near_clip = scene.fog_start, scene.fog_end, scene.near_clip
     u.numerics_fma, u.tex_filter = scene.numerics_fma, scene.tex_filter
+    u.debug_mode = int(getattr(scene, "debug_mode", 0))
     u.n_extra_lights = len(scene.extra_lights)
     for k, (d, col) in enumerate(scene.extra_lights[:4]):
         for i in range(3):

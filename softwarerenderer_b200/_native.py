@@ -33,7 +33,8 @@ class SrbUniforms(C.Structure):
         ("numerics_fma", C.c_int32),
         ("tex_filter", C.c_int32),
         ("n_extra_lights", C.c_int32),
-        ("_pad", C.c_int32 * 2),
+        ("debug_mode", C.c_int32),
+        ("_pad", C.c_int32),
         ("extra_dir", (C.c_float * 4) * 4),
         ("extra_color", (C.c_float * 4) * 4),
     ]

@@ -616,6 +616,8 @@ int srb_set_uniforms(SrbContext* c, const SrbUniforms* u) {
     if (!c || !u) return SRB_ERR_ARG;
     if (u->n_extra_lights < 0 || u->n_extra_lights > 4) return fail(c, SRB_ERR_ARG, "n_extra_lights must be 0..4");
     if (u->tex_filter < 0 || u->tex_filter > 1) return fail(c, SRB_ERR_ARG, "tex_filter must be 0 or 1");
+    if (u->debug_mode != SRB_DEBUG_NONE && u->debug_mode != SRB_DEBUG_WIREFRAME)
+        return fail(c, SRB_ERR_ARG, "debug_mode must be 0 (None) or 1 (Wireframe)");
     c->uniforms = *u;
     return SRB_OK;
 }
@@ -743,6 +745,7 @@ int srb_end_frame(SrbContext* c) {
     if (totalV > 0x3fffffff || totalT > 0x3fffffff) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
     if (c->colorTarget && !(c->clearFlags & SRB_CLEAR_COLOR))
         return fail(c, SRB_ERR_STATE, "a remote colour target needs frames that clear colour");
+    if (c->uniforms.debug_mode == SRB_DEBUG_WIREFRAME) eligible = false;   // DrawLine: depth 1/d, W != 0 writes -- ordered replay only
     if (c->pipeline == SRB_PIPELINE_ORDERED) eligible = false;
     if (c->pipeline == SRB_PIPELINE_VISIBILITY && !eligible && nDraws > 0)
         return fail(c, SRB_ERR_STATE, "frame is not eligible for the visibility pipeline");
@@ -790,6 +793,7 @@ int srb_end_frame(SrbContext* c) {
     fp.loadColor = (c->clearFlags & SRB_CLEAR_COLOR) ? 0 : 1;
     fp.loadDepth = (c->clearFlags & SRB_CLEAR_DEPTH) ? 0 : 1;
     fp.depthMode = commonDepth;
+    fp.wireframe = c->uniforms.debug_mode == SRB_DEBUG_WIREFRAME ? 1 : 0;
     c->stats.draws_submitted = nDraws;
     c->stats.triangles_submitted = totalT;
     c->haveFrame = true;

@@ -100,9 +100,10 @@ __device__ __forceinline__ void bin_big_body(const BigEntry* __restrict__ q, con
                 const int i = i0 + 32 * u;
                 const int yy = i / nx, xx = i - yy * nx;
                 const int tX = x0 + xx, tY = y0 + yy;
-                const bool keep = i < n && tile_may_cover(a.x, a.y, a.z, a.w, b.x, b.y,
+                const bool keep = i < n && (fp.wireframe ||     // lines are not bound by the fill test; the bbox tiles are kept
+                                           tile_may_cover(a.x, a.y, a.z, a.w, b.x, b.y,
                                                           max(minX, tX * kTile), min(maxX, tX * kTile + kTile - 1),
-                                                          max(minY, tY * kTile), min(maxY, tY * kTile + kTile - 1));
+                                                          max(minY, tY * kTile), min(maxY, tY * kTile + kTile - 1)));
                 tile[u] = keep ? tY * fp.tilesX + tX : -1;
             }
 #pragma unroll

@@ -18,6 +18,7 @@ struct FrameParams {
     float clearColor[4];
     int loadColor, loadDepth;     // 1 = keep existing framebuffer contents (no clear this frame)
     int depthMode;                // visibility path: the frame's common depth test
+    int wireframe;                // Rasterizer.RenderDebugMode == Wireframe (Rasterizer.cs:419-425): ordered path only
 };
 
 // Device-side counters of one frame.
@@ -310,7 +311,7 @@ __device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int mi
 #ifndef SRB_EXP_NO_SMALLCULL
     // Triangles of a few pixels that provably pass the reference's test nowhere are dropped here: they would
     // only be walked for nothing (about 30 % of the accepted triangles of the city scene).
-    if (maxX - minX < kSmallPx && maxY - minY < kSmallPx &&
+    if (!fp.wireframe && maxX - minX < kSmallPx && maxY - minY < kSmallPx &&
         !small_tri_may_cover(r.s0x, r.s0y, r.s1x, r.s1y, r.s2x, r.s2y, minX, maxX, minY, maxY)) {
         ++out.nNoCover;
         return;

@@ -74,6 +74,47 @@ sort_bins_kernel(const uint32_t* __restrict__ tileStart, const uint32_t* __restr
 }
 
 // ---------------------------------------------------------------------------
+// DebugMode.Wireframe (Rasterizer.cs:419-425): one pixel against the three DrawLine calls of a triangle
+// (Rasterizer.cs:232-340), in call order (s0,s1), (s1,s2), (s2,s0).  Every call receives the triangle's
+// depths[] and outputs[] arrays and reads elements 0 and 1 of them, whichever edge it draws -- kept as is.
+// Line fragments differ from filled ones: pixel centres at +0.5, depth = 1/lerp(d0,d1,t) (positive),
+// written when alpha != 0, and no BlendMode.None row break.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void wire_pixel(const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U, const TriRec& r,
+                                        const uint32_t seq, const int x, const int y, const int depthTest,
+                                        const int blendMode, float4& col, float& dep) {
+    const float cx = add((float)x, 0.5f), cy = add((float)y, 0.5f);
+#pragma unroll 1
+    for (int k = 0; k < 3; ++k) {
+        const float p0x = k == 0 ? r.s0x : k == 1 ? r.s1x : r.s2x, p0y = k == 0 ? r.s0y : k == 1 ? r.s1y : r.s2y;
+        const float p1x = k == 0 ? r.s1x : k == 1 ? r.s2x : r.s0x, p1y = k == 0 ? r.s1y : k == 1 ? r.s2y : r.s0y;
+        const int minX = sat_int(net_max(net_min(p0x, p1x), 0.0f));                 // :242-245
+        const int maxX = sat_int(net_min(net_max(p0x, p1x), (float)(fp.W - 1)));
+        const int minY = sat_int(net_max(net_min(p0y, p1y), 0.0f));
+        const int maxY = sat_int(net_min(net_max(p0y, p1y), (float)(fp.H - 1)));
+        if (x < minX || x > maxX || y < minY || y > maxY) continue;
+        const float dx = sub(p1x, p0x), dy = sub(p1y, p0y);                         // :257-259
+        const float lenSq = add(mul(dx, dx), mul(dy, dy));
+        const float px = sub(cx, p0x), py = sub(cy, p0y);                           // :296-297
+        float t = 0.0f;
+        if (lenSq > 0.0f) t = fdiv(add(mul(px, dx), mul(py, dy)), lenSq);           // :299-301
+        t = net_max(0.0f, net_min(1.0f, t));                                        // :303
+        const float distX = sub(cx, add(p0x, mul(t, dx))), distY = sub(cy, add(p0y, mul(t, dy)));
+        const float distSq = add(mul(distX, distX), mul(distY, distY));
+        if (!(distSq <= 0.25f)) continue;                                           // :312-313
+        const float omt = sub(1.0f, t);
+        const float depth = fdiv(1.0f, add(mul(r.d0, omt), mul(r.d1, t)));          // :315
+        if (!depth_pass(depthTest, depth, dep)) continue;                           // :318-319
+        int dtmp;
+        const float4 c = shade_fragment<true>(A, fp, U, r, seq, omt, t, 0.0f, dtmp);
+        if (c.w != 0.0f) {                                                          // :325
+            col = blend_px(c, col, blendMode);
+            if (depthTest != SRB_DEPTH_DISABLED) dep = depth;                       // :331-332
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
 // Ordered tile rasterizer: pixel loops of RasterizeTriangle (Rasterizer.cs:
 // 466-536) replayed per pixel in submission order.
 // ---------------------------------------------------------------------------
@@ -103,6 +144,11 @@ ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
         if (startX > endX || startY > endY) continue;            // uniform over the CTA
         const int di = (r.meta & 0x80000000u) ? A.clipAttrs[r.meta & 0x7fffffffu].draw : (int)r.meta;
         const int depthTest = A.draws[di].depth_test, blendMode = A.draws[di].blend;
+        if (fp.wireframe) {                                         // uniform over the frame
+            if (inb && x >= startX && x <= endX && y >= startY && y <= endY)    // the lines' boxes lie inside the triangle's
+                wire_pixel(A, fp, U, r, seq, x, y, depthTest, blendMode, col, dep);
+            continue;
+        }
         bool pass = false, writeOk = false;
         float depth = 0.0f;
         float4 c = make_float4(0, 0, 0, 0);

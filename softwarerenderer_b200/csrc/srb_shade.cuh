@@ -66,6 +66,9 @@ __device__ __forceinline__ float4 tex_bilinear(const uchar4* tex, int tw, int th
 // Rasterizer.Interpolate (:566-640) + InterpolateData (:643-707, WorldNormal key)
 // + Renderer.FragmentShader (Renderer.cs:848-860).  Returns the fragment colour;
 // `drawOut` receives the draw index (for blend/depth state).
+// LINE: the DrawLine call site, Interpolate(outputs[0], outputs[1], outputs[0], 1-t, t, 0) (Rasterizer.cs:314):
+// corner 2 is corner 0 again.
+template <bool LINE = false>
 __device__ __forceinline__ float4 shade_fragment(const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U,
                                                  const TriRec& r, uint32_t seq, float w0f, float w1f, float w2f,
                                                  int& drawOut) {
@@ -98,13 +101,22 @@ __device__ __forceinline__ float4 shade_fragment(const RasterArgs& A, const Fram
     }
     drawOut = di;
     const DrawRec& d = A.draws[di];
+    float cz2 = r.cz2, cw2 = r.cw2;
+    if (LINE) {
+        cz2 = r.cz0; cw2 = r.cw0;
+        uv[2][0] = uv[0][0]; uv[2][1] = uv[0][1];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) col[2][j] = col[0][j];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) wn[2][j] = wn[0][j];
+    }
     // Interpolate (:576-585)
-    float ra = fdiv(w0f, r.cw0), rb = fdiv(w1f, r.cw1), rc = fdiv(w2f, r.cw2);
+    float ra = fdiv(w0f, r.cw0), rb = fdiv(w1f, r.cw1), rc = fdiv(w2f, cw2);
     float sum = add(add(ra, rb), rc);
     float w = fdiv(1.0f, sum);
     float wa = mul(ra, w), wb = mul(rb, w), wc = mul(rc, w);
     auto persp = [&](float a, float b, float c) { return mul(add(add(mul(a, ra), mul(b, rb)), mul(c, rc)), w); };
-    float clipZ = persp(r.cz0, r.cz1, r.cz2);
+    float clipZ = persp(r.cz0, r.cz1, cz2);
     float tu = persp(uv[0][0], uv[1][0], uv[2][0]), tv = persp(uv[0][1], uv[1][1], uv[2][1]);
     float cr = persp(col[0][0], col[1][0], col[2][0]), cg = persp(col[0][1], col[1][1], col[2][1]);
     float cb = persp(col[0][2], col[1][2], col[2][2]), cA = persp(col[0][3], col[1][3], col[2][3]);

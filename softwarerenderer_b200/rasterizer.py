@@ -76,8 +76,6 @@ class Rasterizer:
         (Renderer.cs:446) onto the device for this draw."""
         if window.RenderWidth <= 0 or window.RenderHeight <= 0:      # :176 silent return
             return
-        if Rasterizer.RenderDebugMode != DebugMode.None_:
-            raise NotImplementedError("DebugMode.Wireframe is outside the accelerated path (SURVEY.md N4)")
         vs_ok = vertexShader is Shaders.StockVertexShader or isinstance(vertexShader, Shaders.StockVertexShader)
         if not vs_ok or not isinstance(fragmentShader, Shaders.StockFragmentShader):
             raise NotImplementedError(

@@ -186,6 +186,7 @@ class Scene:
     tex_filter: int = 0
     extra_lights: list = field(default_factory=list)
     name: str = ""
+    debug_mode: int = 0          # Rasterizer.RenderDebugMode (0 None, 1 Wireframe)
 
     def __post_init__(self):
         if self.light_dir is None:
@@ -214,12 +215,24 @@ def submit_scene(window, scene: Scene) -> None:
     u.NumericsFma, u.TexFilter, u.ExtraLights = scene.numerics_fma, scene.tex_filter, list(scene.extra_lights)
     window.ClearDepthBuffer()
     window.ClearColorBuffer(scene.clear_color)
+    saved_mode = Rasterizer.RenderDebugMode
+    Rasterizer.RenderDebugMode = Rasterizer.DebugMode(scene.debug_mode)
+    try:
+        _submit_draws(window, scene)
+        window.RenderFrame(near_clip=scene.near_clip)
+    finally:
+        Rasterizer.RenderDebugMode = saved_mode
+
+
+def _submit_draws(window, scene: Scene) -> None:
+    from .rasterizer import Rasterizer
+    from .shaders import Shaders
+
     for i, d in enumerate(scene.draws):
         Rasterizer.RenderMesh(window, d.mesh.Vertices, d.mesh.Indices, d.model, d.view, d.proj,
                               Shaders.StockVertexShader, Shaders.StockFragmentShader(d.mesh.Texture),
                               d.cull, d.depth, d.blend, submissionIndex=i,
                               sphereBounds=d.mesh.SphereBounds if d.frustum_cull else None)
-    window.RenderFrame(near_clip=scene.near_clip)
 
 
 def _repo_assets() -> str:

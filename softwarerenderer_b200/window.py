@@ -30,7 +30,7 @@ class Uniforms:
         self.TexFilter = 0            # 0 nearest (reference), 1 bilinear (extension)
         self.ExtraLights = []         # extension: list of (direction3, color3)
 
-    def to_struct(self, near_clip: float) -> N.SrbUniforms:
+    def to_struct(self, near_clip: float, debug_mode: int = 0) -> N.SrbUniforms:
         u = N.SrbUniforms()
         for i in range(3):
             u.light_dir[i] = float(self.LightDirection[i])
@@ -39,6 +39,7 @@ class Uniforms:
             u.fog_color[i] = float(self.FogColor[i])
         u.fog_start, u.fog_end, u.near_clip = float(self.FogStart), float(self.FogEnd), float(near_clip)
         u.numerics_fma, u.tex_filter = int(self.NumericsFma), int(self.TexFilter)
+        u.debug_mode = int(debug_mode)
         u.n_extra_lights = len(self.ExtraLights)
         for k, (d, col) in enumerate(self.ExtraLights[:4]):
             for i in range(3):
@@ -154,7 +155,10 @@ class MainWindow:
         from .rasterizer import Rasterizer
 
         L = N.lib()
-        u = self.Uniforms.to_struct(Rasterizer.NearClip if near_clip is None else near_clip)
+        # Rasterizer.RenderDebugMode is a static the reference reads while rasterizing (Rasterizer.cs:419);
+        # here it is captured when the frame is submitted.
+        u = self.Uniforms.to_struct(Rasterizer.NearClip if near_clip is None else near_clip,
+                                    int(Rasterizer.RenderDebugMode))
         N.check(self._ctx, L.srb_set_uniforms(self._ctx, C.byref(u)))
         cc = (C.c_float * 4)(*[float(x) for x in self._clear_color])
         N.check(self._ctx, L.srb_begin_frame(self._ctx, cc, self._clear_flags))

@@ -47,3 +47,45 @@ def coverage_by_tile_walk(tri_screen_submitted, W, H):
                     w0, w1, w2 = F(w0 + a12), F(w1 + a20), F(w2 + a01)                           # :527-529
                 w0r, w1r, w2r = F(w0r + b12), F(w1r + b20), F(w2r + b01)                         # :532-534
     return cov
+
+
+def wireframe_depth(tri_screen_submitted, depths_submitted, W, H, depth_test="lequal"):
+    """Independent float32 restatement of DebugMode.Wireframe for ONE triangle on a cleared target
+    (Rasterizer.cs:419-425 -> three DrawLine calls, Rasterizer.cs:232-340).  `depths_submitted` are
+    the per-vertex depths[] values (ndc.z+1)/2 in SUBMISSION order.  Returns (depth[H,W], hits[H,W]):
+    the stored depth (clear = float.MinValue) and how many of the three lines touched each pixel.
+    Alpha is assumed non-zero (every touched pixel that passes the depth test is written)."""
+    t = np.asarray(tri_screen_submitted, dtype=np.float32)
+    s = [t[2], t[1], t[0]]                                          # :367 reorder {v2, v1, v0}
+    dd = np.asarray(depths_submitted, dtype=np.float32)
+    d0, d1 = dd[2], dd[1]                                           # every call reads depths[0], depths[1] (:315)
+    depth = np.full((H, W), F(-3.4028235e38), dtype=np.float32)
+    hits = np.zeros((H, W), dtype=np.int32)
+    for a, b in ((0, 1), (1, 2), (2, 0)):                           # :421-423
+        p0, p1 = s[a], s[b]
+        minX = int(max(min(p0[0], p1[0]), F(0)))                    # :242-245 (truncation)
+        maxX = int(min(max(p0[0], p1[0]), F(W - 1)))
+        minY = int(max(min(p0[1], p1[1]), F(0)))
+        maxY = int(min(max(p0[1], p1[1]), F(H - 1)))
+        if minX > maxX or minY > maxY:
+            continue
+        dx, dy = F(p1[0] - p0[0]), F(p1[1] - p0[1])
+        len_sq = F(F(dx * dx) + F(dy * dy))
+        for y in range(minY, maxY + 1):
+            for x in range(minX, maxX + 1):
+                cx, cy = F(F(x) + F(0.5)), F(F(y) + F(0.5))
+                px, py = F(cx - p0[0]), F(cy - p0[1])
+                tt = F(0)
+                if len_sq > 0:
+                    tt = F(F(F(px * dx) + F(py * dy)) / len_sq)
+                tt = max(F(0), min(F(1), tt))
+                ddx = F(cx - F(p0[0] + F(tt * dx)))
+                ddy = F(cy - F(p0[1] + F(tt * dy)))
+                if F(F(ddx * ddx) + F(ddy * ddy)) <= F(0.25):
+                    hits[y, x] += 1
+                    nd = F(F(1) / F(F(d0 * F(F(1) - tt)) + F(d1 * tt)))
+                    old = depth[y, x]
+                    ok = nd >= old if depth_test == "lequal" else True       # :542-559 (LessEqual is new >= old)
+                    if ok:
+                        depth[y, x] = nd
+    return depth, hits

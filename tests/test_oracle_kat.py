@@ -413,3 +413,113 @@ def test_numerics_switch_changes_only_low_bits(oracle):
     both = (d0 != CLEAR_DEPTH) & (d1 != CLEAR_DEPTH)
     assert ((d0 != CLEAR_DEPTH) != (d1 != CLEAR_DEPTH)).mean() < 1e-3
     assert np.abs(d0[both] - d1[both]).max() < 1e-5
+
+
+# --------------------------------------------------------------------------
+# N4: DebugMode.Wireframe = three DrawLine calls per triangle (Rasterizer.cs:419-425, 232-340)
+# --------------------------------------------------------------------------
+def _ndc_z_to_depth(z):
+    return F((F(z) + F(1.0)) * F(0.5))          # depths[i] = (ndc.z + 1) * 0.5 (:388)
+
+
+def test_wireframe_draws_only_the_three_edges(oracle):
+    tri = [(5.0, 5.0), (58.0, 9.0), (30.0, 56.0)]
+    sc = screen_tri_scene(64, 64, [tri], cull=0)
+    sc.debug_mode = 1
+    c, d, st = _render(oracle, sc)
+    covered = d != CLEAR_DEPTH
+    fill = screen_tri_scene(64, 64, [tri], cull=0)
+    _, dfill, _ = _render(oracle, fill)
+    filled = dfill != CLEAR_DEPTH
+    assert 100 < covered.sum() < 0.25 * filled.sum()          # an outline, not the interior
+    assert not covered[30, 30] and filled[30, 30]
+    # a line fragment lies within half a pixel of its segment, measured from the pixel CENTRE (:296-313)
+    ys, xs = np.nonzero(covered)
+    P = np.array(tri, dtype=np.float64)
+    def seg_dist(px, py, a, b):
+        ab, ap = b - a, np.array([px, py]) - a
+        t = min(1.0, max(0.0, ap.dot(ab) / ab.dot(ab)))
+        return np.linalg.norm(ap - t * ab)
+    for x, y in zip(xs, ys):
+        dmin = min(seg_dist(x + 0.5, y + 0.5, P[i], P[(i + 1) % 3]) for i in range(3))
+        assert dmin <= 0.5 + 1e-4
+    # the line depth is 1/lerp(depths[0], depths[1], t): positive, unlike the negated fill depth (:315 vs :502)
+    assert (d[covered] > 0).all() and (dfill[filled] < 0).all()
+    assert np.allclose(d[covered], 1.0 / _ndc_z_to_depth(0.5), rtol=1e-6)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4])
+def test_wireframe_matches_an_independent_restatement(oracle, seed):
+    from tests.ref_walk import wireframe_depth
+    rng = np.random.default_rng(seed)
+    for _ in range(6):
+        tri = np.round(rng.uniform(-6, 70, size=(3, 2)) * 4) / 4          # partly off-target: bbox clamps and truncation
+        z = np.round(rng.uniform(-0.5, 0.9, size=3) * 64) / 64
+        sc = screen_tri_scene(64, 64, [np.concatenate([tri, z[:, None]], axis=1)], cull=0)
+        sc.debug_mode = 1
+        _, d, st = _render(oracle, sc)
+        want, hits = wireframe_depth(tri, [_ndc_z_to_depth(v) for v in z], 64, 64)
+        if st.triangles_drawn == 0:                                           # zero area: rejected before the lines (:396)
+            assert not (d != CLEAR_DEPTH).any()
+            continue
+        assert np.array_equal(d, want)
+        assert st.fragments_tested == hits.sum()
+
+
+def test_wireframe_every_edge_uses_the_first_two_depths_and_outputs(oracle):
+    # DrawLine is handed the triangle's depths[]/outputs[] and always reads elements 0 and 1 (:315, :321):
+    # on the edge (s2,s0) = (v0,v2) the depth at the v0 end is v2's, not v0's.  Kept as the reference has it.
+    tri = [(8.5, 40.5, -0.5), (40.5, 40.5, 0.25), (24.5, 8.5, 0.75)]         # v0, v1, v2 with distinct depths
+    red, green, blue = (1, 0, 0, 1), (0, 1, 0, 1), (0, 0, 1, 1)
+    sc = screen_tri_scene(64, 64, [tri], colors=[[red, green, blue]], cull=0, depth=7)   # Always: last line wins
+    sc.debug_mode = 1
+    c, d, _ = _render(oracle, sc)
+    d_v2, d_v1 = _ndc_z_to_depth(0.75), _ndc_z_to_depth(0.25)
+    # pixel (8,40) has its centre exactly on v0; it is touched by line 1 (s1,s2)=(v1,v0) at t=1 and then by
+    # line 2 (s2,s0)=(v0,v2) at t=0, which wins under Always: depth 1/depths[0] = 1/d(v2), colour of v2.
+    assert d[40, 8] == F(1.0) / d_v2
+    # before line 2, the same pixel held 1/depths[1] (line 1 at t=1): check with LessEqual, where 1/d(v1) > 1/d(v2) stays
+    sc2 = screen_tri_scene(64, 64, [tri], colors=[[red, green, blue]], cull=0, depth=2)
+    sc2.debug_mode = 1
+    c2, d2, _ = _render(oracle, sc2)
+    assert d2[40, 8] == F(1.0) / d_v1
+    k = 0.1 + 0.9 * 0.5                           # normal (0,0,1), L = (0.5,-0.7071,-0.5): dot(N,-L) = 0.5 (Renderer.cs:851-857)
+    assert np.allclose(c[40, 8, :3], np.array(blue[:3]) * k, atol=1e-6)
+    assert np.allclose(c2[40, 8, :3], np.array(green[:3]) * k, atol=1e-6)
+
+
+def test_wireframe_writes_when_alpha_is_nonzero_and_has_no_row_break(oracle):
+    # fill: write iff alpha > 0 (:511); line: iff alpha != 0 (:325) -- a negative alpha is written by DrawLine only
+    tri = [(4.5, 4.5), (28.5, 4.5), (16.5, 26.5)]
+    sc = screen_tri_scene(32, 32, [tri], colors=[(1, 1, 1, -0.5)], cull=0, blend=0)
+    sc.debug_mode = 1
+    _, d, _ = _render(oracle, sc)
+    assert (d != CLEAR_DEPTH).sum() > 40
+    sc0 = screen_tri_scene(32, 32, [tri], colors=[(1, 1, 1, 0.0)], cull=0, blend=0)
+    sc0.debug_mode = 1
+    _, d0, st0 = _render(oracle, sc0)
+    assert not (d0 != CLEAR_DEPTH).any() and st0.fragments_shaded == st0.fragments_tested > 40   # no early-out: all shaded
+    fill = screen_tri_scene(32, 32, [tri], colors=[(1, 1, 1, -0.5)], cull=0, blend=0)
+    _, df, _ = _render(oracle, fill)
+    assert not (df != CLEAR_DEPTH).any()
+
+
+def test_wireframe_respects_cull_mode(oracle):
+    tri = [(5.0, 5.0), (58.0, 9.0), (30.0, 56.0)]
+    drawn = []
+    for cull in (1, 2):
+        sc = screen_tri_scene(64, 64, [tri], cull=cull)
+        sc.debug_mode = 1
+        _, d, _ = _render(oracle, sc)
+        drawn.append(bool((d != CLEAR_DEPTH).any()))
+    assert sorted(drawn) == [False, True]          # the cull test precedes the wireframe branch (:414-425)
+
+
+def test_wireframe_tile_parallel_variant_is_bit_identical(oracle):
+    from softwarerenderer_b200 import scene as S
+    sc = S.scene_model("Gun", 320, 180)
+    sc.debug_mode = 1
+    c0, d0, _ = oracle.render_scene(sc, threads=0)
+    c1, d1, _ = oracle.render_scene(sc, threads=3)
+    assert np.array_equal(d0, d1) and np.array_equal(c0, c1)
+    assert 0.005 < (d0 != CLEAR_DEPTH).mean() < 0.5
