@@ -263,6 +263,21 @@ def run_gpu(args):
         if fused:
             dist.all_reduce(token)              # band ranks must not start the next frame before rank 0 has flattened this one
 
+    host_rgba8 = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+
+    def step_e2e_rgba8():
+        """Same loop, the frame delivered at display precision (srb_present_rgba8_async: what the reference's blit
+        leaves in the window's 8-bit framebuffer, MainWindow.cs:251-253)."""
+        N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
+        N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
+        N.check(ctx, L.srb_end_frame(ctx))
+        gather()
+        if rank == 0:
+            N.check(ctx, L.srb_present_rgba8_async(ctx, C.c_void_p(host_rgba8[e2e_count[0] & 1].data_ptr())))
+            e2e_count[0] += 1
+        if fused:
+            dist.all_reduce(token)
+
     def step_e2e_colorbuffer():
         """Same, but the result is the float4 ColorBuffer itself, read synchronously (srb_read_color)."""
         N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
@@ -314,6 +329,15 @@ def run_gpu(args):
     N.check(ctx, L.srb_present_wait(ctx))
     ms_c, wall_c, _ = timed(step_e2e_colorbuffer, Ke, 3)
     fps_c = Ke / max(wall_c, ms_c / 1000.0)
+    K8 = max(Ke, min(K, 4 * args.e2e_steps))
+    ms_8, wall_8, _ = timed(step_e2e_rgba8, K8, 3)
+    fps_8 = K8 / max(wall_8, ms_8 / 1000.0)
+    N.check(ctx, L.srb_present_wait(ctx))
+    rgba8_ok = None
+    if rank == 0:
+        cb = win.ColorBuffer
+        rgba8_ok = bool(np.array_equal(host_rgba8[(e2e_count[0] - 1) & 1].numpy(),
+                                       np.rint(np.clip(cb, 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)))
 
     # ---- N>1 e2e: every band rank delivers its own rows to ONE shared pinned host frame over its own PCIe
     # link (srb_present_rgb_rows_async); no NVLink gather on this path, the frame is assembled in host memory.
@@ -432,7 +456,11 @@ def run_gpu(args):
                     "result": "packed RGB float frame, the array MainWindow.OnRender uploads (MainWindow.cs:232-246), "
                               "srb_present_rgb_async into two alternating pinned host frames; D2H of frame k overlaps frame k+1",
                     "colorbuffer_float4_sync": {"value": fps_c, "unit": "frames/s", "d2h_bytes_per_step": int(W * H * 16),
-                                                "call": "srb_read_color"}},
+                                                "call": "srb_read_color"},
+                    "rgba8_present": {"value": fps_8, "unit": "frames/s", "d2h_bytes_per_step": int(W * H * 4), "steps": K8,
+                                      "call": "srb_present_rgba8_async", "verified": rgba8_ok,
+                                      "result": "the same frame at display precision (clamp, x255, round to nearest: what the "
+                                                "reference's blit leaves in the window's 8-bit framebuffer, MainWindow.cs:251-253)"}},
             "e2e_parallel_present": e2e_parallel,     # N>1: promoted to `e2e` below; the gather-to-GPU-0 loop is kept beside it
             "gpu_launches": int(st.kernel_launches) * K,          # timed region of `value`; each e2e step adds the flatten kernel
             "clocks": clocks,

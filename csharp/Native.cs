@@ -69,6 +69,9 @@ namespace SoftwareRenderer
         [DllImport(Lib)] public static extern int srb_present_rgb(IntPtr ctx, float* rgbOut);
         [DllImport(Lib)] public static extern int srb_present_rgb_async(IntPtr ctx, float* rgbOut);
         [DllImport(Lib)] public static extern int srb_present_rgb_rows_async(IntPtr ctx, float* rgbOut, int y0, int y1);
+        [DllImport(Lib)] public static extern int srb_present_rgba8(IntPtr ctx, byte* rgba8Out);
+        [DllImport(Lib)] public static extern int srb_present_rgba8_async(IntPtr ctx, byte* rgba8Out);
+        [DllImport(Lib)] public static extern int srb_present_rgba8_rows_async(IntPtr ctx, byte* rgba8Out, int y0, int y1);
         [DllImport(Lib)] public static extern int srb_present_wait(IntPtr ctx);
         [DllImport(Lib)] public static extern int srb_present_fence(IntPtr ctx);
         [DllImport(Lib)] public static extern int srb_read_color_rows(IntPtr ctx, float* rgbaOut, int y0, int y1);

@@ -168,6 +168,13 @@ int srb_present_rgb_async(SrbContext* ctx, float* rgb_out);
 /* Rows [y0,y1) only, written at their place in the full-frame array rgb_out points to.  Multi-GPU: every band
  * rank delivers its own rows to one shared (pinned) host frame over its own PCIe link, in parallel. */
 int srb_present_rgb_rows_async(SrbContext* ctx, float* rgb_out, int y0, int y1);
+/* The presented frame at display precision: the reference draws its float texture into
+ * the window's 8-bit framebuffer (MainWindow.cs:251-253), so what reaches the screen is clamp(c,0,1)*255
+ * rounded to nearest -- W*H*4 bytes R,G,B,A, a quarter of the float4 buffer.  Same queueing rules as the
+ * float forms (they share the two present slots); the host side uploads it as (Rgba, UnsignedByte). */
+int srb_present_rgba8(SrbContext* ctx, uint8_t* rgba8_out);
+int srb_present_rgba8_async(SrbContext* ctx, uint8_t* rgba8_out);
+int srb_present_rgba8_rows_async(SrbContext* ctx, uint8_t* rgba8_out, int y0, int y1);
 /* Device-side fence: work queued on the pipeline stream (srb_stream) after this call starts only when the
  * present copies queued so far have landed.  A collective placed behind it is a "frame delivered" barrier
  * across band ranks that never blocks the host. */

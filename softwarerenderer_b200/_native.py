@@ -82,7 +82,8 @@ EXPORTS = [
     "srb_texture_create", "srb_texture_destroy", "srb_texture_sample",
     "srb_mesh_create", "srb_mesh_destroy", "srb_set_uniforms", "srb_begin_frame", "srb_draw",
     "srb_submit_draws", "srb_end_frame", "srb_replay_frame", "srb_sync", "srb_read_color",
-    "srb_read_depth", "srb_read_color_rgba8", "srb_present_rgb", "srb_present_rgb_async", "srb_present_rgb_rows_async", "srb_present_wait", "srb_present_fence",
+    "srb_read_depth", "srb_read_color_rgba8", "srb_present_rgb", "srb_present_rgb_async", "srb_present_rgb_rows_async",
+    "srb_present_rgba8", "srb_present_rgba8_async", "srb_present_rgba8_rows_async", "srb_present_wait", "srb_present_fence",
     "srb_read_color_rows", "srb_get_pixel", "srb_set_pixel",
     "srb_get_depth", "srb_set_depth", "srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream",
     "srb_frustum_test", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
@@ -138,6 +139,9 @@ def lib() -> C.CDLL:
     L.srb_present_rgb.argtypes = [vp, vp]
     L.srb_present_rgb_async.argtypes = [vp, vp]
     L.srb_present_rgb_rows_async.argtypes = [vp, vp, C.c_int, C.c_int]
+    L.srb_present_rgba8.argtypes = [vp, vp]
+    L.srb_present_rgba8_async.argtypes = [vp, vp]
+    L.srb_present_rgba8_rows_async.argtypes = [vp, vp, C.c_int, C.c_int]
     L.srb_present_wait.argtypes = [vp]
     L.srb_present_fence.argtypes = [vp]
     L.srb_read_color_rows.argtypes = [vp, vp, i32, i32]

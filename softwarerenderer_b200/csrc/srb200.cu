@@ -898,7 +898,7 @@ int srb_read_color_rgba8(SrbContext* c, uint8_t* out) {
 
 /* Present path (MainWindow.cs:226-246).  Flatten on the device, copy on a second stream: the call returns
  * once the copy is queued, and the next frame may be submitted and rendered while it runs. */
-int srb_present_rgb_rows_async(SrbContext* c, float* out, int y0, int y1) {
+static int present_rows_async(SrbContext* c, void* out, int y0, int y1, bool rgba8) {
     if (!c || !out) return SRB_ERR_ARG;
     if (y0 < 0 || y1 < y0 || y1 > c->H) return fail(c, SRB_ERR_ARG, "row range out of bounds");
     int rc = srb_sync(c);                                  // frame finished and capacity overflows settled
@@ -916,16 +916,32 @@ int srb_present_rgb_rows_async(SrbContext* c, float* out, int y0, int y1) {
         CK(c, cudaEventSynchronize(c->presentCopied[s]));
         c->presentBusy[s] = false;
     }
-    CK(c, c->dPresent[s].reserve(n * 3 + 16));
-    present_rgb_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color + first, c->dPresent[s].p, n);
+    CK(c, c->dPresent[s].reserve((rgba8 ? n : n * 3) + 16));
+    if (rgba8)
+        present_rgba8_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color + first, (uint32_t*)c->dPresent[s].p, n);
+    else
+        present_rgb_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color + first, c->dPresent[s].p, n);
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(c->presentReady[s], c->stream));
     CK(c, cudaStreamWaitEvent(c->copyStream, c->presentReady[s], 0));
     // (Measured, no gain: the copy as two halves on two streams -- one stream already reaches the link rate, 54.7 GB/s.)
-    CK(c, cudaMemcpyAsync(out + first * 3, c->dPresent[s].p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->copyStream));
+    if (rgba8)
+        CK(c, cudaMemcpyAsync((uint8_t*)out + first * 4, c->dPresent[s].p, n * 4, cudaMemcpyDeviceToHost, c->copyStream));
+    else
+        CK(c, cudaMemcpyAsync((float*)out + first * 3, c->dPresent[s].p, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->copyStream));
     CK(c, cudaEventRecord(c->presentCopied[s], c->copyStream));
     c->presentBusy[s] = true;
     return SRB_OK;
+}
+
+int srb_present_rgb_rows_async(SrbContext* c, float* out, int y0, int y1) { return present_rows_async(c, out, y0, y1, false); }
+int srb_present_rgba8_rows_async(SrbContext* c, uint8_t* out, int y0, int y1) { return present_rows_async(c, out, y0, y1, true); }
+int srb_present_rgba8_async(SrbContext* c, uint8_t* out) {
+    return c ? present_rows_async(c, out, 0, c->H, true) : SRB_ERR_ARG;
+}
+int srb_present_rgba8(SrbContext* c, uint8_t* out) {
+    int rc = srb_present_rgba8_async(c, out);
+    return rc != SRB_OK ? rc : srb_present_wait(c);
 }
 
 int srb_present_rgb_async(SrbContext* c, float* out) {

@@ -450,6 +450,24 @@ __global__ void pack_rgba8_kernel(const float4* __restrict__ color, uchar4* __re
     out[i] = make_uchar4(q(c.x), q(c.y), q(c.z), q(c.w));
 }
 
+// The same step at display precision: the reference draws its RGBA32F texture into the window's 8-bit
+// framebuffer (MainWindow.cs:251-253), i.e. clamp to [0,1] and round to the nearest of 255 steps -- the format
+// of the parity gate.  Four pixels per thread: 4 x 128-bit loads, one 128-bit store.
+__device__ __forceinline__ uint32_t pack_unorm8(const float4 c) {
+    auto q = [](float v) { return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.0f), 1.0f) * 255.0f); };   // NaN -> 0
+    return q(c.x) | (q(c.y) << 8) | (q(c.z) << 16) | (q(c.w) << 24);
+}
+__global__ void present_rgba8_kernel(const float4* __restrict__ color, uint32_t* __restrict__ out, size_t n) {
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = q * 4;
+    if (i + 3 < n) {
+        const float4 a = color[i], b = color[i + 1], c = color[i + 2], d = color[i + 3];
+        __stcs(reinterpret_cast<uint4*>(out) + q, make_uint4(pack_unorm8(a), pack_unorm8(b), pack_unorm8(c), pack_unorm8(d)));
+    } else {
+        for (size_t k = i; k < n; ++k) out[k] = pack_unorm8(color[k]);
+    }
+}
+
 // MainWindow.OnRender's flatten (MainWindow.cs:232-238): Vector4 colour -> packed Vector3, the layout the
 // reference hands to TexSubImage2D(Rgb, Float).  Four pixels per thread: 4 x 128-bit loads, 3 x 128-bit stores.
 __global__ void present_rgb_kernel(const float4* __restrict__ color, float* __restrict__ out, size_t n) {

@@ -206,6 +206,22 @@ class MainWindow:
         """Queue the copy of rows [y0,y1) into the full-frame array `out` (band ranks, shared host frame)."""
         N.check(self._ctx, N.lib().srb_present_rgb_rows_async(self._ctx, N.ptr(out), int(y0), int(y1)))
 
+    def PresentRgba8(self, out: np.ndarray = None, wait: bool = True, rows=None) -> np.ndarray:
+        """The presented frame at display precision (what the reference's blit leaves in the window's 8-bit
+        framebuffer, MainWindow.cs:251-253): uint8 [H, W, 4].  rows=(y0, y1) copies only those rows, at their
+        place in `out`."""
+        if out is None:
+            out = np.empty((self.RenderHeight, self.RenderWidth, 4), dtype=np.uint8)
+        L = N.lib()
+        if rows is not None:
+            N.check(self._ctx, L.srb_present_rgba8_rows_async(self._ctx, N.ptr(out), int(rows[0]), int(rows[1])))
+            if wait:
+                self.PresentWait()
+        else:
+            fn = L.srb_present_rgba8 if wait else L.srb_present_rgba8_async
+            N.check(self._ctx, fn(self._ctx, N.ptr(out)))
+        return out
+
     def PresentWait(self) -> None:
         N.check(self._ctx, N.lib().srb_present_wait(self._ctx))
 

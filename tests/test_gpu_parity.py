@@ -167,6 +167,38 @@ def test_present_rgb_matches_colorbuffer():
         win.Close()
 
 
+def test_present_rgba8_is_the_quantised_colorbuffer(oracle):
+    """srb_present_rgba8[_rows][_async]: clamp(c,0,1)*255 rounded to nearest, per channel --
+    equal to the host-side quantisation of ColorBuffer, and within the parity gate of the oracle's image."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import submit_scene
+    sc = S.scene_model("Gun", 642, 361)                  # odd size: scalar tail path
+    oc, _, _ = oracle.render_scene(sc, threads=4)
+    win = srb.MainWindow(642, 361)
+    try:
+        submit_scene(win, sc)
+        cb = win.ColorBuffer
+        want = np.rint(np.clip(cb, 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+        got = win.PresentRgba8()
+        assert got.dtype == np.uint8 and np.array_equal(got, want)
+        assert np.array_equal(win.ColorBufferRgba8(), want)
+        o8 = np.rint(np.clip(oc, 0.0, 1.0) * np.float32(255.0)).astype(np.int32)
+        assert (np.abs(got.astype(np.int32) - o8).max(axis=-1) <= 1).mean() >= 0.999
+        rows = np.zeros_like(want)
+        win.PresentRgba8(rows, wait=False, rows=(0, 100))
+        win.PresentRgba8(rows, wait=True, rows=(100, 361))
+        assert np.array_equal(rows, want)
+        outs = [np.zeros_like(want) for _ in range(2)]
+        for k in range(4):
+            win.ReplayFrame()
+            win.PresentRgba8(outs[k & 1], wait=False)
+        win.PresentWait()
+        assert np.array_equal(outs[0], want) and np.array_equal(outs[1], want)
+    finally:
+        win.Close()
+
+
 def test_pipelined_frames_do_not_disturb_each_other():
     """Frames are pipelined (geometry of frame N+1 beside the tile kernel of frame N, two buffer sets): a burst
     of frames without any synchronisation in between -- replays of one scene, then two different scenes
