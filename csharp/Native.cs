@@ -27,6 +27,17 @@ namespace SoftwareRenderer
     }
 
     [StructLayout(LayoutKind.Sequential)]
+    public unsafe struct SrbRayHit              // srb200.h: SrbRayHit (48 bytes)
+    {
+        public int Hit;                         // return value of Physics.Raycast
+        public float Distance;                  // hitDistance
+        public Vector3 Point;                   // hitPoint
+        public Vector3 Normal;                  // hitNormal
+        public int Triangle;
+        public fixed int Pad[3];
+    }
+
+    [StructLayout(LayoutKind.Sequential)]
     public struct SrbStats
     {
         public long DrawsSubmitted, DrawsVisible, TrianglesSubmitted, TrianglesSetup, TilePairs, ClippedTriangles;
@@ -72,6 +83,7 @@ namespace SoftwareRenderer
         [DllImport(Lib)] public static extern int srb_present_rgba8(IntPtr ctx, byte* rgba8Out);
         [DllImport(Lib)] public static extern int srb_present_rgba8_async(IntPtr ctx, byte* rgba8Out);
         [DllImport(Lib)] public static extern int srb_present_rgba8_rows_async(IntPtr ctx, byte* rgba8Out, int y0, int y1);
+        [DllImport(Lib)] public static extern int srb_raycast(IntPtr ctx, int mesh, float* model, float* rays, int n, int faceMask, SrbRayHit* hits);
         [DllImport(Lib)] public static extern int srb_present_wait(IntPtr ctx);
         [DllImport(Lib)] public static extern int srb_present_fence(IntPtr ctx);
         [DllImport(Lib)] public static extern int srb_read_color_rows(IntPtr ctx, float* rgbaOut, int y0, int y1);

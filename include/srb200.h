@@ -193,6 +193,25 @@ void* srb_stream(SrbContext* ctx);             /* cudaStream_t the pipeline runs
 int srb_frustum_test(SrbContext* ctx, const float* spheres /* n*4 */, const float* models /* n*16 */,
                      const float view[16], const float proj[16], int n, int32_t* out_visible);
 
+/* ---- Physics.Raycast (Physics.cs:19-179), batched on the device ----
+ * n rays (6 floats each: origin xyz, direction xyz -- normalised by the call, Physics.cs:70) against one
+ * resident mesh under `model`; closest hit per ray by the reference's Moller-Trumbore test (:137-178).
+ * face_mask: RaycastFaceMask bits (Physics.cs:9-14).  A non-invertible model gives no hits (:30-36).
+ * Where the reference's parallel reduction leaves ties in distance to thread timing, the lowest triangle
+ * index wins here. */
+#define SRB_RAY_IGNORE_BACKFACES  1
+#define SRB_RAY_IGNORE_FRONTFACES 2
+typedef struct SrbRayHit {
+    int32_t hit;            /* return value of Physics.Raycast */
+    float   distance;       /* hitDistance (float.MaxValue when no hit) */
+    float   point[3];       /* hitPoint */
+    float   normal[3];      /* hitNormal */
+    int32_t triangle;       /* winning triangle index, -1 when no hit (not in the reference's signature) */
+    int32_t _pad[3];
+} SrbRayHit;
+int srb_raycast(SrbContext* ctx, SrbMesh mesh, const float model[16], const float* rays /* n*6 */, int n,
+                int face_mask, SrbRayHit* out /* n */);
+
 int srb_get_stats(SrbContext* ctx, SrbStats* out);
 /* Per-stage device times of the last completed frame (CUDA events on the pipeline stream).
  * Enable with srb_set_profiling(ctx, 1); stages: 0 frustum, 1 vertex, 2 setup+count, 3 scan,

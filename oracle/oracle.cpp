@@ -655,6 +655,114 @@ int orc_clip_near(const float clip_in[12], float near_clip, int numerics_fma, fl
     return n;
 }
 
+// ---------------------------------------------------------------------------
+// Physics.Raycast (Physics.cs:19-179)
+// ---------------------------------------------------------------------------
+// Matrix4x4.Invert, .NET BCL scalar algorithm (cofactor expansion along the first column; fails when
+// |det| < float.Epsilon).  Row-major M11..M44.
+static bool invert4(const float* M, float* R) {
+    float a = M[0], b = M[1], c = M[2], d = M[3], e = M[4], f = M[5], g = M[6], h = M[7];
+    float i = M[8], j = M[9], k = M[10], l = M[11], m = M[12], n = M[13], o = M[14], p = M[15];
+    float kp_lo = k * p - l * o, jp_ln = j * p - l * n, jo_kn = j * o - k * n;
+    float ip_lm = i * p - l * m, io_km = i * o - k * m, in_jm = i * n - j * m;
+    float a11 = +(f * kp_lo - g * jp_ln + h * jo_kn);
+    float a12 = -(e * kp_lo - g * ip_lm + h * io_km);
+    float a13 = +(e * jp_ln - f * ip_lm + h * in_jm);
+    float a14 = -(e * jo_kn - f * io_km + g * in_jm);
+    float det = a * a11 + b * a12 + c * a13 + d * a14;
+    if (fabsf(det) < 1.401298464e-45f) return false;
+    float invDet = 1.0f / det;
+    R[0] = a11 * invDet; R[4] = a12 * invDet; R[8] = a13 * invDet; R[12] = a14 * invDet;
+    R[1] = -(b * kp_lo - c * jp_ln + d * jo_kn) * invDet;
+    R[5] = +(a * kp_lo - c * ip_lm + d * io_km) * invDet;
+    R[9] = -(a * jp_ln - b * ip_lm + d * in_jm) * invDet;
+    R[13] = +(a * jo_kn - b * io_km + c * in_jm) * invDet;
+    float gp_ho = g * p - h * o, fp_hn = f * p - h * n, fo_gn = f * o - g * n;
+    float ep_hm = e * p - h * m, eo_gm = e * o - g * m, en_fm = e * n - f * m;
+    R[2] = +(b * gp_ho - c * fp_hn + d * fo_gn) * invDet;
+    R[6] = -(a * gp_ho - c * ep_hm + d * eo_gm) * invDet;
+    R[10] = +(a * fp_hn - b * ep_hm + d * en_fm) * invDet;
+    R[14] = -(a * fo_gn - b * eo_gm + c * en_fm) * invDet;
+    float gl_hk = g * l - h * k, fl_hj = f * l - h * j, fk_gj = f * k - g * j;
+    float el_hi = e * l - h * i, ek_gi = e * k - g * i, ej_fi = e * j - f * i;
+    R[3] = -(b * gl_hk - c * fl_hj + d * fk_gj) * invDet;
+    R[7] = +(a * gl_hk - c * el_hi + d * ek_gi) * invDet;
+    R[11] = -(a * fl_hj - b * el_hi + d * ej_fi) * invDet;
+    R[15] = +(a * fk_gj - b * ek_gi + c * ej_fi) * invDet;
+    return true;
+}
+
+static inline V3 cross3(V3 a, V3 b) {
+    return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+
+// RayIntersectsTriangle (Physics.cs:137-178).
+static bool ray_tri(V3 ro, V3 rd, V3 v0, V3 v1, V3 v2, int faceMask, float& distance, V3& bary) {
+    const float Epsilon = 1e-8f;
+    V3 edge1 = {v1.x - v0.x, v1.y - v0.y, v1.z - v0.z};
+    V3 edge2 = {v2.x - v0.x, v2.y - v0.y, v2.z - v0.z};
+    V3 pvec = cross3(rd, edge2);
+    float det = dot3(edge1, pvec);
+    if ((faceMask & 1) && det < Epsilon) return false;              // :156
+    if ((faceMask & 2) && det > -Epsilon) return false;             // :157
+    if (fabsf(det) < Epsilon) return false;                         // :158
+    float invDet = 1.0f / det;
+    V3 tvec = {ro.x - v0.x, ro.y - v0.y, ro.z - v0.z};
+    float u = dot3(tvec, pvec) * invDet;
+    if (u < 0 || u > 1) return false;
+    V3 qvec = cross3(tvec, edge1);
+    float v = dot3(rd, qvec) * invDet;
+    if (v < 0 || u + v > 1) return false;
+    distance = dot3(edge2, qvec) * invDet;
+    if (distance < 0) return false;
+    bary = {1.0f - u - v, u, v};
+    return true;
+}
+
+int orc_raycast(const float origin[3], const float direction[3], const float* vertices, int n_vertices,
+                const uint16_t* indices, int n_indices, const float model[16], int face_mask, int numerics_fma,
+                float* out_distance, float out_point[3], float out_normal[3], int* out_tri) {
+    bool fma = numerics_fma != 0;
+    *out_distance = 3.402823466e+38f;                                // float.MaxValue (:31, :66)
+    out_point[0] = out_point[1] = out_point[2] = 0.0f;
+    out_normal[0] = out_normal[1] = out_normal[2] = 0.0f;
+    if (out_tri) *out_tri = -1;
+    float inv[16];
+    if (!invert4(model, inv)) return 0;                              // :30-36
+    float nmat[16];                                                  // Matrix4x4.Transpose(invModel) (:38)
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) nmat[4 * r + c] = inv[4 * c + r];
+    std::vector<V3> wp(n_vertices), wn(n_vertices);
+    for (int i = 0; i < n_vertices; ++i) {                           // :43-49
+        const float* v = vertices + (size_t)i * 12;
+        V4 p = transform4({v[0], v[1], v[2], 1.0f}, model, fma);     // Vector3.Transform(position, model)
+        wp[i] = {p.x, p.y, p.z};
+        V4 n = transform4({v[5], v[6], v[7], 0.0f}, nmat, fma);      // Vector4.Transform((normal,0), normalMatrix)
+        wn[i] = normalize3({n.x, n.y, n.z});
+    }
+    V3 ro = {origin[0], origin[1], origin[2]};
+    V3 rd = normalize3({direction[0], direction[1], direction[2]});  // :70
+    float best = 3.402823466e+38f;
+    int bestTri = -1;
+    V3 bestBary = {0, 0, 0};
+    for (int t = 0; t < n_indices / 3; ++t) {
+        int i0 = indices[3 * t], i1 = indices[3 * t + 1], i2 = indices[3 * t + 2];
+        float dist; V3 bary;
+        if (!ray_tri(ro, rd, wp[i0], wp[i1], wp[i2], face_mask, dist, bary)) continue;
+        if (dist < best) { best = dist; bestTri = t; bestBary = bary; }   // :104-107, strict: first (lowest index) wins ties
+    }
+    if (bestTri < 0) return 0;
+    int i0 = indices[3 * bestTri], i1 = indices[3 * bestTri + 1], i2 = indices[3 * bestTri + 2];
+    V3 n = {(wn[i0].x * bestBary.x + wn[i1].x * bestBary.y) + wn[i2].x * bestBary.z,       // :101
+            (wn[i0].y * bestBary.x + wn[i1].y * bestBary.y) + wn[i2].y * bestBary.z,
+            (wn[i0].z * bestBary.x + wn[i1].z * bestBary.y) + wn[i2].z * bestBary.z};
+    n = normalize3(n);
+    *out_distance = best;
+    out_point[0] = ro.x + rd.x * best; out_point[1] = ro.y + rd.y * best; out_point[2] = ro.z + rd.z * best;   // :102
+    out_normal[0] = n.x; out_normal[1] = n.y; out_normal[2] = n.z;
+    if (out_tri) *out_tri = bestTri;
+    return 1;
+}
+
 // FrustumCuller.IsSphereInFrustum (FrustumCuller.cs:153-224, 19-35).
 int orc_sphere_in_frustum(const float sphere[4], const float M[16], const float V[16],
                           const float P[16], int numerics_fma) {

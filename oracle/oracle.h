@@ -95,6 +95,17 @@ void orc_vertex_shader(const float vtx[12], const float model[16], const float v
  * returns number of output triangles (0..2), out_clip = n*3*4 floats. */
 int orc_clip_near(const float clip_in[12], float near_clip, int numerics_fma, float out_clip[24]);
 
+/* Physics.Raycast (Physics.cs:19-179): one ray against one mesh under `model`; closest hit by
+ * Moller-Trumbore in world space.  face_mask: 1 IgnoreBackfaces, 2 IgnoreFrontfaces (Physics.cs:9-14).
+ * The reference reduces per-thread partial results in completion order; ties in distance are broken here
+ * by the lowest triangle index (the sequential order, one legal execution).
+ * Matrix4x4.Invert / Transpose come from the .NET 9 BCL (not in the reference tree, unpinned): restated from
+ * the BCL's published scalar cofactor algorithm; they only feed hit_normal.
+ * Returns 1 on a hit.  out_tri receives the winning triangle index (not in the reference's signature). */
+int orc_raycast(const float origin[3], const float direction[3], const float* vertices, int n_vertices,
+                const uint16_t* indices, int n_indices, const float model[16], int face_mask, int numerics_fma,
+                float* out_distance, float out_point[3], float out_normal[3], int* out_tri);
+
 /* Debug statistics of the last orc_render_* call chain since orc_clear_depth. */
 typedef struct OrcStats {
     int64_t triangles_in;       /* submitted */

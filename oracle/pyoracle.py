@@ -168,6 +168,21 @@ def render_scene(scene, threads: int = 0, tile_rows=None, clear=(True, True), wi
     return color, depth, st
 
 
+def raycast(origin, direction, vertices, indices, model, face_mask=1, fma=1):
+    """Physics.Raycast on the CPU oracle -> (hit, distance, point[3], normal[3], triangle)."""
+    L = lib()
+    o, d, m = _f32(origin, 3), _f32(direction, 3), _f32(model, 16)
+    v = np.ascontiguousarray(vertices).view(np.float32).reshape(-1, 12)
+    ix = np.ascontiguousarray(indices, dtype=np.uint16)
+    dist, tri = C.c_float(), C.c_int()
+    pt, nr = np.zeros(3, np.float32), np.zeros(3, np.float32)
+    L.orc_raycast.restype = C.c_int
+    hit = L.orc_raycast(C.c_void_p(o.ctypes.data), C.c_void_p(d.ctypes.data), C.c_void_p(v.ctypes.data), v.shape[0],
+                        C.c_void_p(ix.ctypes.data), ix.size, C.c_void_p(m.ctypes.data), int(face_mask), int(fma),
+                        C.byref(dist), C.c_void_p(pt.ctypes.data), C.c_void_p(nr.ctypes.data), C.byref(tri))
+    return bool(hit), dist.value, pt, nr, tri.value
+
+
 def texture_sample(pixels: np.ndarray, u: float, v: float, filter: int = 0) -> np.ndarray:
     px = np.ascontiguousarray(pixels, dtype=np.uint8)
     out = np.zeros(4, dtype=np.float32)

@@ -86,10 +86,19 @@ EXPORTS = [
     "srb_present_rgba8", "srb_present_rgba8_async", "srb_present_rgba8_rows_async", "srb_present_wait", "srb_present_fence",
     "srb_read_color_rows", "srb_get_pixel", "srb_set_pixel",
     "srb_get_depth", "srb_set_depth", "srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream",
-    "srb_frustum_test", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
+    "srb_frustum_test", "srb_raycast", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
 ]
 
 _lib = None
+
+
+class SrbRayHit(C.Structure):
+    _fields_ = [("hit", C.c_int32), ("distance", C.c_float), ("point", C.c_float * 3), ("normal", C.c_float * 3),
+                ("triangle", C.c_int32), ("_pad", C.c_int32 * 3)]
+
+
+RAY_HIT_DTYPE = np.dtype([("hit", "<i4"), ("distance", "<f4"), ("point", "<f4", (3,)), ("normal", "<f4", (3,)),
+                          ("triangle", "<i4"), ("_pad", "<i4", (3,))])
 
 
 class SrbError(RuntimeError):
@@ -143,6 +152,7 @@ def lib() -> C.CDLL:
     L.srb_present_rgba8_async.argtypes = [vp, vp]
     L.srb_present_rgba8_rows_async.argtypes = [vp, vp, C.c_int, C.c_int]
     L.srb_present_wait.argtypes = [vp]
+    L.srb_raycast.argtypes = [vp, C.c_int32, vp, vp, C.c_int, C.c_int, vp]
     L.srb_present_fence.argtypes = [vp]
     L.srb_read_color_rows.argtypes = [vp, vp, i32, i32]
     L.srb_get_pixel.argtypes = [vp, i32, i32, f32p]

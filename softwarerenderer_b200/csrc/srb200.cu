@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "srb_raster.cuh"
+#include "srb_physics.cuh"
 
 using namespace srb;
 
@@ -58,6 +59,7 @@ struct SrbContext {
     // frame k (copy stream) overlaps the rendering of frame k+1 (pipeline stream)
     cudaStream_t copyStream = nullptr;
     DevBuf<float> dPresent[2];
+    DevBuf<float4> dRayScratch;       // srb_raycast: directions, hits, keys, rays
     cudaEvent_t presentReady[2] = {}, presentCopied[2] = {};
     bool presentBusy[2] = {false, false};
     int presentSlot = 0;
@@ -385,6 +387,7 @@ int srb_destroy(SrbContext* c) {
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
     c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dClip.release();
+    c->dRayScratch.release();
     c->dRefs.release(); c->dBigQ.release(); c->dTileCount.release(); c->dBinScratch.release();
     for (auto& b : c->fb) {
         b.dWn.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
@@ -994,6 +997,78 @@ int srb_frustum_test(SrbContext* c, const float* spheres, const float* models, c
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d);
     if (e != cudaSuccess) return fail(c, SRB_ERR_CUDA, std::string("srb_frustum_test: ") + cudaGetErrorString(e));
+    return SRB_OK;
+}
+
+// Matrix4x4.Invert of the .NET BCL (scalar algorithm: cofactors of the first column, fails when |det| < float.Epsilon),
+// restated from its published form; row-major M11..M44.  Only the hit normal depends on it.
+static bool invert4(const float* M, float* R) {
+    const float a = M[0], b = M[1], c = M[2], d = M[3], e = M[4], f = M[5], g = M[6], h = M[7];
+    const float i = M[8], j = M[9], k = M[10], l = M[11], m = M[12], n = M[13], o = M[14], p = M[15];
+    const float kp_lo = k * p - l * o, jp_ln = j * p - l * n, jo_kn = j * o - k * n;
+    const float ip_lm = i * p - l * m, io_km = i * o - k * m, in_jm = i * n - j * m;
+    const float a11 = +(f * kp_lo - g * jp_ln + h * jo_kn), a12 = -(e * kp_lo - g * ip_lm + h * io_km);
+    const float a13 = +(e * jp_ln - f * ip_lm + h * in_jm), a14 = -(e * jo_kn - f * io_km + g * in_jm);
+    const float det = a * a11 + b * a12 + c * a13 + d * a14;
+    if (std::fabs(det) < 1.401298464e-45f) return false;
+    const float invDet = 1.0f / det;
+    R[0] = a11 * invDet; R[4] = a12 * invDet; R[8] = a13 * invDet; R[12] = a14 * invDet;
+    R[1] = -(b * kp_lo - c * jp_ln + d * jo_kn) * invDet; R[5] = +(a * kp_lo - c * ip_lm + d * io_km) * invDet;
+    R[9] = -(a * jp_ln - b * ip_lm + d * in_jm) * invDet; R[13] = +(a * jo_kn - b * io_km + c * in_jm) * invDet;
+    const float gp_ho = g * p - h * o, fp_hn = f * p - h * n, fo_gn = f * o - g * n;
+    const float ep_hm = e * p - h * m, eo_gm = e * o - g * m, en_fm = e * n - f * m;
+    R[2] = +(b * gp_ho - c * fp_hn + d * fo_gn) * invDet; R[6] = -(a * gp_ho - c * ep_hm + d * eo_gm) * invDet;
+    R[10] = +(a * fp_hn - b * ep_hm + d * en_fm) * invDet; R[14] = -(a * fo_gn - b * eo_gm + c * en_fm) * invDet;
+    const float gl_hk = g * l - h * k, fl_hj = f * l - h * j, fk_gj = f * k - g * j;
+    const float el_hi = e * l - h * i, ek_gi = e * k - g * i, ej_fi = e * j - f * i;
+    R[3] = -(b * gl_hk - c * fl_hj + d * fk_gj) * invDet; R[7] = +(a * gl_hk - c * el_hi + d * ek_gi) * invDet;
+    R[11] = -(a * fl_hj - b * el_hi + d * ej_fi) * invDet; R[15] = +(a * fk_gj - b * ek_gi + c * ej_fi) * invDet;
+    return true;
+}
+
+/* Physics.Raycast (Physics.cs:19-179), batched: n rays against one resident mesh. */
+int srb_raycast(SrbContext* c, SrbMesh mesh, const float model[16], const float* rays, int n, int face_mask, SrbRayHit* out) {
+    static_assert(sizeof(SrbRayHit) == sizeof(RayHit), "SrbRayHit layout");
+    if (!c || !model || !rays || !out || n < 0) return SRB_ERR_ARG;
+    if (mesh <= 0 || (size_t)mesh > c->meshes.size() || !c->meshes[mesh - 1].alive) return fail(c, SRB_ERR_HANDLE, "unknown mesh handle");
+    if (face_mask < 0 || face_mask > 3) return fail(c, SRB_ERR_ARG, "face_mask must be a combination of 1 (IgnoreBackfaces) and 2 (IgnoreFrontfaces)");
+    if (n == 0) return SRB_OK;
+    CK(c, cudaSetDevice(c->device));
+    const MeshRes& m = c->meshes[mesh - 1];
+    Mat4 M, NM;
+    std::memcpy(M.m, model, 64);
+    float inv[16];
+    if (!invert4(model, inv)) {                                  // :30-36: no hit, distance float.MaxValue, zero vectors
+        for (int r = 0; r < n; ++r) {
+            std::memset(&out[r], 0, sizeof(SrbRayHit));
+            out[r].distance = 3.402823466e+38f; out[r].triangle = -1;
+        }
+        return SRB_OK;
+    }
+    for (int r = 0; r < 4; ++r) for (int k = 0; k < 4; ++k) NM.m[4 * r + k] = inv[4 * k + r];     // Matrix4x4.Transpose (:38)
+    // scratch: rays (6 floats), normalised directions (float4), keys (u64), hits
+    const size_t bytes = (size_t)n * (24 + 16 + 8 + sizeof(RayHit)) + 64;
+    CK(c, c->dRayScratch.reserve((bytes + 15) / 16));
+    char* base = (char*)c->dRayScratch.p;
+    float4* dDirs = (float4*)base;
+    RayHit* dHits = (RayHit*)(base + (size_t)n * 16);
+    unsigned long long* dKeys = (unsigned long long*)(base + (size_t)n * (16 + sizeof(RayHit)));
+    float* dRays = (float*)(base + (size_t)n * (16 + sizeof(RayHit) + 8));
+    cudaStream_t s = c->stream;
+    CK(c, cudaMemcpyAsync(dRays, rays, (size_t)n * 24, cudaMemcpyHostToDevice, s));
+    ray_prepare_kernel<<<(n + 255) / 256, 256, 0, s>>>(dRays, n, dDirs, dKeys);
+    const int nTri = m.nI / 3;
+    if (nTri > 0) {
+        dim3 grid((nTri + 255) / 256, (n + kRayChunk - 1) / kRayChunk);
+        if (grid.y > 65535) return fail(c, SRB_ERR_ARG, "too many rays in one call (max 65535 * 64)");
+        if (c->uniforms.numerics_fma) raycast_kernel<true><<<grid, 256, 0, s>>>(m.vtx, m.idx, nTri, M, dRays, dDirs, n, face_mask, dKeys);
+        else raycast_kernel<false><<<grid, 256, 0, s>>>(m.vtx, m.idx, nTri, M, dRays, dDirs, n, face_mask, dKeys);
+    }
+    if (c->uniforms.numerics_fma) ray_resolve_kernel<true><<<(n + 127) / 128, 128, 0, s>>>(m.vtx, m.idx, M, NM, dRays, dDirs, n, face_mask, dKeys, dHits);
+    else ray_resolve_kernel<false><<<(n + 127) / 128, 128, 0, s>>>(m.vtx, m.idx, M, NM, dRays, dDirs, n, face_mask, dKeys, dHits);
+    CK(c, cudaGetLastError());
+    CK(c, cudaMemcpyAsync(out, dHits, (size_t)n * sizeof(RayHit), cudaMemcpyDeviceToHost, s));
+    CK(c, cudaStreamSynchronize(s));
     return SRB_OK;
 }
 
