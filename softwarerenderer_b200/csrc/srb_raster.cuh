@@ -410,6 +410,10 @@ template <int MODE>
 __global__ void __launch_bounds__(kVisThreads, SRB_VIS_MINBLOCKS)
 vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     __shared__ VisSmem sm;
+    // (Measured and rejected: a persistent grid of smCount x 8 CTAs taking launch-order entries from a device-side
+    // queue, each CTA fetching its next tile's order entry and first bin entries and prefetching their records
+    // while the current tile is shaded -- raster 113 -> 124 us, and resident CTAs that never retire keep the
+    // pipelined geometry kernels of the next frame off the SMs: city4k 5,470 -> 4,850 frames/s.)
     // One load gives the tile and its bin range.  (Measured and rejected: clearing the frame on a second
     // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
     const uint4 o = __ldg(A.order + blockIdx.x);

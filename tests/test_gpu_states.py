@@ -131,3 +131,46 @@ def test_wireframe_is_refused_by_the_forced_visibility_pipeline():
             S.submit_scene(win, sc)
     finally:
         win.Close()
+
+
+def test_racing_host_threads_with_submission_indices_give_the_ordered_frame(oracle):
+    """Renderer calls RenderMesh from Parallel.ForEach threads (Renderer.cs:444, 479): srb_draw is thread-safe and
+    the explicit submission index, not the arrival order, decides the order of blending."""
+    import ctypes as C
+    import threading
+
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import _native as N
+    from softwarerenderer_b200.scene import submit_scene
+    sc = _translucent_scene(31, 2, 1, 0, n=96, separate=True)
+    oc, od, _ = oracle.render_scene(sc, threads=4)
+    win = srb.MainWindow(sc.width, sc.height)
+    try:
+        submit_scene(win, sc)                        # uploads meshes, sets uniforms; reference image of the ordered path
+        want_c, want_d = win.ColorBuffer, win.DepthBuffer
+        compare(want_c, want_d, oc, od)
+        L, ctx = N.lib(), win._ctx
+        handles = [win.mesh_handle(d.mesh.Vertices, d.mesh.Indices) for d in sc.draws]
+        mats = [[np.ascontiguousarray(np.asarray(m, np.float32).reshape(16)) for m in (d.model, d.view, d.proj)] for d in sc.draws]
+        cc = (C.c_float * 4)(*[float(x) for x in sc.clear_color])
+        for trial in range(3):
+            N.check(ctx, L.srb_begin_frame(ctx, cc, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
+            order = np.random.RandomState(trial).permutation(len(sc.draws))
+            errs = []
+
+            def worker(chunk):
+                for i in chunk:
+                    d = sc.draws[i]
+                    rc = L.srb_draw(ctx, handles[i], N.ptr(mats[i][0]), N.ptr(mats[i][1]), N.ptr(mats[i][2]), 0,
+                                    int(d.cull), int(d.depth), int(d.blend), int(i))
+                    if rc != 0:
+                        errs.append(rc)
+
+            ts = [threading.Thread(target=worker, args=(order[k::8],)) for k in range(8)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+            assert not errs
+            N.check(ctx, L.srb_end_frame(ctx))
+            assert np.array_equal(win.ColorBuffer, want_c) and np.array_equal(win.DepthBuffer, want_d)
+    finally:
+        win.Close()
