@@ -386,6 +386,20 @@ def run_gpu(args):
         if fused and rank != 0:
             win.SetColorTarget(box[0])
 
+    # ---- single-frame latency (median and p5/p95 over >= 200 frames): one frame at a time,
+    # synchronised, device time of begin..end of the pipeline from the library's own CUDA events (no overlap
+    # between frames here, unlike the throughput loop above) ----
+    lat = []
+    for i in range(203):
+        N.check(ctx, L.srb_replay_frame(ctx))
+        s_ = win.Stats()                         # synchronises; gpu_ms = CUDA events around the whole frame
+        if i >= 3:
+            lat.append(float(s_.gpu_ms))
+    lat = np.array(lat)
+    frame_latency = {"median_ms": float(np.median(lat)), "p5_ms": float(np.percentile(lat, 5)),
+                     "p95_ms": float(np.percentile(lat, 95)), "frames": int(lat.size),
+                     "note": "one synchronised frame at a time (no frame pipelining); this rank's band only"}
+
     # ---- per-stage device times (CUDA events on the pipeline stream), one synced frame at a time ----
     N.check(ctx, L.srb_set_profiling(ctx, 1))
     Kp = min(K, 50)
@@ -464,6 +478,7 @@ def run_gpu(args):
             "e2e_parallel_present": e2e_parallel,     # N>1: promoted to `e2e` below; the gather-to-GPU-0 loop is kept beside it
             "gpu_launches": int(st.kernel_launches) * K,          # timed region of `value`; each e2e step adds the flatten kernel
             "clocks": clocks,
+            "frame_latency": frame_latency,
             "stage_ms": stage_ms,
             "stage_ms_ranks": stage_ms_ranks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -479,6 +494,14 @@ def run_gpu(args):
             del line["e2e_parallel_present"]
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(scene)
+            fr = line["cpu_baseline"].pop("fragments", None)
+            if fr:
+                # informational: what an immediate-mode rasterizer moves for the same frame --
+                # 4 B per depth-tested fragment + 36 B per written fragment -- against the tiled path's bytes
+                imm = 4 * fr["tested"] + 36 * fr["shaded"]
+                line["roofline_frame"]["immediate_mode_equivalent_bytes"] = int(imm)
+                line["roofline_frame"]["fragments_tested"] = int(fr["tested"])
+                line["roofline_frame"]["fragments_shaded_in_submission_order"] = int(fr["shaded"])
     win.Close()
     if world > 1:
         dist.barrier()
@@ -507,10 +530,13 @@ def cpu_baseline(scene, budget_s=25.0):
         times.append(time.perf_counter() - t0)
         if time.perf_counter() - t_all > budget_s and len(times) >= 2:
             break
+    st = O.OrcStats()
+    L.orc_get_stats(win, C.byref(st))            # counters restart at every orc_clear_depth: the last frame's
     L.orc_destroy(win)
     meas = times[1:] if len(times) > 1 else times
     med = float(np.median(meas))
-    return {"value": 1.0 / med, "unit": "frames/s", "cores": cores, "kind": "port",
+    return {"fragments": {"tested": int(st.fragments_tested), "shaded": int(st.fragments_shaded)},
+            "value": 1.0 / med, "unit": "frames/s", "cores": cores, "kind": "port",
             "sample": f"{len(meas)} full frame(s) after 1 warm-up, median; C++ restatement of the C# path "
                       "(tile-row-parallel, bit-identical to the literal oracle); the C# reference cannot run here"}
 
