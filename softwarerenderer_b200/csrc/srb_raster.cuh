@@ -237,7 +237,11 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
             // a pre-check 119 us, this 117 us.  Rejected: a hand-written CAS loop reusing the loaded value,
             // 123 -> 260 us -- the compiler's ATOMS.CAST.SPIN sequence is far better.)
             const unsigned long long key = make_key<MODE>(depth, seq);
+#ifdef SRB_EXP_NO_ATOMIC                         /* diagnostic builds only (tools/tile_breakdown.sh): wrong images */
+            krow[xx] = depth == depth ? key : 0ull;
+#else
             atomicMax(krow + xx, depth == depth ? key : 0ull);
+#endif
         }
         w0 = add(w0, a12); w1 = add(w1, a20); w2 = add(w2, a01);
     }
@@ -348,7 +352,11 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         // of the same triangle, which keeps a warp's row walks coherent.  (Measured and rejected: one
         // contiguous run of items per thread, reusing constants and the y accumulation -- 123 -> 190 us.) ----
         // (Measured, no gain: splitting each row over 2 or 4 threads when a chunk has few items.)
+#ifdef SRB_EXP_NO_WALK                           /* diagnostic builds only */
+        for (int i = tid; i < 0; i += kVisThreads) {
+#else
         for (int i = tid; i < total; i += kVisThreads) {
+#endif
             const int itv = sm.items[i];
             const int j = itv & 0xff, dy = itv >> 8;
             float w0 = S[0][j], w1 = S[1][j], w2 = S[2][j];
