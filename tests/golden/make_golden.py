@@ -52,6 +52,27 @@ def hash_cases():
     """name -> Scene (BASELINE config 1 at full size: hashes only)."""
     out = {f"gun_1280x720_cam{k}": S.scene_model("Gun", 1280, 720, view=S.gun_camera(k)) for k in range(9)}
     out["city24_1280x720"] = S.scene_city(1280, 720, n_instances=24)
+    # DebugMode.Wireframe (three DrawLine calls per triangle, Rasterizer.cs:419-425, 232-340)
+    for name, sc in (("gun_1280x720_cam0_wireframe", S.scene_model("Gun", 1280, 720)),
+                     ("city12_640x360_wireframe", S.scene_city(640, 360, n_instances=12))):
+        sc.debug_mode = 1
+        out[name] = sc
+    return out
+
+
+def raycast_cases():
+    """Physics.Raycast (Physics.cs:19-179): fixed rays against the first meshes of the Gun under a fixed model matrix."""
+    from softwarerenderer_b200 import numerics as nm
+    rng = np.random.default_rng(0x5EED0007)
+    M = (nm.create_scale(1.25) @ nm.create_rotation_y(0.6)).astype(np.float32)
+    M[3, :3] = (1.0, -0.5, 2.0)
+    out = []
+    for mi, m in enumerate(S.load_model("Gun").Meshes[:3]):
+        c, r = np.array(m.SphereBounds.Center, dtype=np.float64), m.SphereBounds.Radius
+        cw = (np.r_[c, 1.0] @ M.astype(np.float64))[:3]
+        o = (cw + rng.normal(size=(24, 3)) * 4 * r).astype(np.float32)
+        d = (cw + rng.uniform(-0.7, 0.7, (24, 3)) * r * 1.25 - o).astype(np.float32)
+        out.append((mi, M, o, d))
     return out
 
 
@@ -68,6 +89,20 @@ def main():
         print(name, hashes[name]["covered"])
     with open(os.path.join(HERE, "hashes.json"), "w") as f:
         json.dump(hashes, f, indent=1, sort_keys=True)
+    gun = S.load_model("Gun")
+    rays = []
+    for mi, M, o, d in raycast_cases():
+        m = gun.Meshes[mi]
+        for k in range(o.shape[0]):
+            for mask in (0, 1):
+                hit, dist, pt, nr, tri = O.raycast(o[k], d[k], m.Vertices, m.Indices, M, face_mask=mask)
+                rays.append({"mesh": mi, "ray": k, "mask": mask, "hit": bool(hit), "triangle": int(tri),
+                             "distance_bits": int(np.float32(dist).view(np.uint32)),
+                             "point_bits": [int(x) for x in np.asarray(pt, np.float32).view(np.uint32)],
+                             "normal": [float(x) for x in nr]})
+    with open(os.path.join(HERE, "raycast.json"), "w") as f:
+        json.dump(rays, f, indent=0)
+    print("raycast", len(rays), sum(r["hit"] for r in rays), "hits")
 
 
 if __name__ == "__main__":

@@ -46,6 +46,47 @@ def test_oracle_reproduces_config1_hashes(oracle, scenes, name):
     assert G.sha(G.to_u8(c)) == HASHES[name]["rgba8"]
 
 
+RAYS = json.load(open(os.path.join(HERE, "raycast.json")))
+
+
+def _ray_inputs():
+    from softwarerenderer_b200 import scene as S
+    gun = S.load_model("Gun")
+    return {mi: (gun.Meshes[mi], M, o, d) for mi, M, o, d in G.raycast_cases()}
+
+
+def test_oracle_reproduces_golden_raycasts(oracle):
+    """Physics.Raycast fixtures: hit flag, triangle, distance and point bit for bit; normal within 1e-6."""
+    inp = _ray_inputs()
+    assert sum(r["hit"] for r in RAYS) > 30
+    for r in RAYS:
+        m, M, o, d = inp[r["mesh"]]
+        hit, dist, pt, nr, tri = oracle.raycast(o[r["ray"]], d[r["ray"]], m.Vertices, m.Indices, M, face_mask=r["mask"])
+        assert hit == r["hit"] and tri == r["triangle"]
+        assert int(np.float32(dist).view(np.uint32)) == r["distance_bits"]
+        assert [int(x) for x in pt.view(np.uint32)] == r["point_bits"]
+        assert np.allclose(nr, r["normal"], atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_cuda_matches_golden_raycasts():
+    import softwarerenderer_b200 as srb
+    inp = _ray_inputs()
+    win = srb.MainWindow(64, 64)
+    try:
+        for mi, (m, M, o, d) in inp.items():
+            for mask in (0, 1):
+                got = srb.Physics.RaycastBatch(win, o, d, m.Vertices, m.Indices, M, srb.RaycastFaceMask(mask))
+                for r in (x for x in RAYS if x["mesh"] == mi and x["mask"] == mask):
+                    g = got[r["ray"]]
+                    assert bool(g["hit"]) == r["hit"] and int(g["triangle"]) == r["triangle"]
+                    assert int(g["distance"].view(np.uint32)) == r["distance_bits"]
+                    assert [int(x) for x in g["point"].view(np.uint32)] == r["point_bits"]
+                    assert np.allclose(g["normal"], r["normal"], atol=1e-6)
+    finally:
+        win.Close()
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("pipeline", [1, 2])
 @pytest.mark.parametrize("name", IMAGE_CASES)
