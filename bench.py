@@ -152,8 +152,8 @@ def run_reference(args):
 
 
 class _DevArray:
-    def __init__(self, ptr, shape):
-        self.__cuda_array_interface__ = {"shape": shape, "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+    def __init__(self, ptr, shape, typestr="<f4"):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (int(ptr), False), "version": 2}
 
 
 STAGES = ["frustum", "vertex", "setup_count", "scan", "fill", "sort", "tile_raster"]
@@ -200,9 +200,17 @@ def run_gpu(args):
         cuts = balanced_cuts(w_rows, world, remote_extra=extra)
     r0, r1 = cuts[rank], cuts[rank + 1]
     fused = world > 1 and args.gather == "fused"
+    rgba8_gather = fused and args.gather_format == "rgba8"
     if world > 1:
         win.SetBand(r0, r1)
-        if fused:
+        if fused and rgba8_gather:
+            # rank 0 exports an RGBA8 frame; every rank's tile kernel stores its band's 8-bit colour into it
+            # (rank 0 locally, the others as 4-byte peer stores over NVLink); float4 colour stays on each rank
+            box = [win.ExportGatherRgba8() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=0)
+            if rank != 0:
+                win.SetGatherRgba8Target(box[0])
+        elif fused:
             # rank 0 exports its colour buffer; band ranks store their final colour straight into it
             box = [win.ExportColorHandle() if rank == 0 else None]
             dist.broadcast_object_list(box, src=0)
@@ -273,7 +281,10 @@ def run_gpu(args):
         N.check(ctx, L.srb_end_frame(ctx))
         gather()
         if rank == 0:
-            N.check(ctx, L.srb_present_rgba8_async(ctx, C.c_void_p(host_rgba8[e2e_count[0] & 1].data_ptr())))
+            if rgba8_gather:        # the assembled 8-bit frame is already in rank 0's gather frame: copy it out
+                N.check(ctx, L.srb_present_gathered_rgba8_async(ctx, C.c_void_p(host_rgba8[e2e_count[0] & 1].data_ptr())))
+            else:
+                N.check(ctx, L.srb_present_rgba8_async(ctx, C.c_void_p(host_rgba8[e2e_count[0] & 1].data_ptr())))
             e2e_count[0] += 1
         if fused:
             dist.all_reduce(token)
@@ -322,19 +333,33 @@ def run_gpu(args):
     sampler = ClockSampler(local) if rank == 0 else None
     ms, wall, clocks = timed(step_resident, K, Wm, sampler)
     fps = K / (ms / 1000.0)
+    gather_verified = None
+    if rgba8_gather:
+        # the frame assembled on rank 0 must be every rank's own band, quantised
+        full8 = torch.from_numpy(win.GatheredRgba8()).to(dev) if rank == 0 else torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
+        dist.broadcast(full8, src=0)
+        mine = np.rint(np.clip(win.ColorBuffer[y0:y1], 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+        oks = [None] * world
+        dist.all_gather_object(oks, bool(np.array_equal(full8[y0:y1].cpu().numpy(), mine)))
+        gather_verified = all(oks)
+        del full8
     # e2e: host buffers in, host frame out, every step (wall clock: it includes host work by design)
     Ke = max(5, min(K, args.e2e_steps))
-    ms_e, wall_e, _ = timed(step_e2e, Ke, 3)
-    fps_e = Ke / max(wall_e, ms_e / 1000.0)          # timed() ends with a device-wide synchronize: the last copies are inside
-    N.check(ctx, L.srb_present_wait(ctx))
-    ms_c, wall_c, _ = timed(step_e2e_colorbuffer, Ke, 3)
-    fps_c = Ke / max(wall_c, ms_c / 1000.0)
+    if rgba8_gather:      # rank 0 holds only its own band as float4: the float forms of the via-GPU-0 loop do not apply
+        ms_e = wall_e = ms_c = wall_c = float("nan")
+        fps_e = fps_c = None
+    else:
+        ms_e, wall_e, _ = timed(step_e2e, Ke, 3)
+        fps_e = Ke / max(wall_e, ms_e / 1000.0)          # timed() ends with a device-wide synchronize: the last copies are inside
+        N.check(ctx, L.srb_present_wait(ctx))
+        ms_c, wall_c, _ = timed(step_e2e_colorbuffer, Ke, 3)
+        fps_c = Ke / max(wall_c, ms_c / 1000.0)
     K8 = max(Ke, min(K, 4 * args.e2e_steps))
     ms_8, wall_8, _ = timed(step_e2e_rgba8, K8, 3)
     fps_8 = K8 / max(wall_8, ms_8 / 1000.0)
     N.check(ctx, L.srb_present_wait(ctx))
     rgba8_ok = None
-    if rank == 0:
+    if rank == 0 and not rgba8_gather:
         cb = win.ColorBuffer
         rgba8_ok = bool(np.array_equal(host_rgba8[(e2e_count[0] - 1) & 1].numpy(),
                                        np.rint(np.clip(cb, 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)))
@@ -344,7 +369,7 @@ def run_gpu(args):
     # A 4-byte all-reduce behind a device-side fence on the previous copies is the "frame delivered" barrier.
     e2e_parallel = None
     if world > 1:
-        if fused and rank != 0:
+        if fused and rank != 0 and not rgba8_gather:
             win.SetColorTarget(None)            # final colour back into the local buffer
         nbytes = 2 * H * W * 12
         shm_path = "/dev/shm/srb200_frame_%s" % os.environ.get("MASTER_PORT", "0")
@@ -383,7 +408,7 @@ def run_gpu(args):
         dist.barrier()
         if rank == 0:
             os.unlink(shm_path)
-        if fused and rank != 0:
+        if fused and rank != 0 and not rgba8_gather:
             win.SetColorTarget(box[0])
 
     # ---- single-frame latency (median and p5/p95 over >= 200 frames): one frame at a time,
@@ -459,14 +484,17 @@ def run_gpu(args):
                        "tile_pairs": int(st.tile_pairs), "pipeline": "visibility" if st.pipeline_used == 2 else "ordered",
                        "parallelism": f"bands{world}" if world > 1 else "single",
                        "bands": {"cuts_tile_rows": [int(x) for x in cuts], "policy": args.bands,
-                                 "gather": ("peer stores from the tile kernel into rank 0's buffer over NVLink + 4-byte "
-                                            "NCCL all-reduce as frame barrier") if fused else "NCCL grouped send/recv of float4 bands"}
+                                 "gather": (("RGBA8 (4 B/pixel) " if rgba8_gather else "float4 (16 B/pixel) ") +
+                                            "peer stores from the tile kernel into rank 0's frame over NVLink + 4-byte "
+                                            "NCCL all-reduce as frame barrier") if fused else "NCCL grouped send/recv of float4 bands",
+                                 "gather_format": args.gather_format if fused else "float4", "gather_verified": gather_verified}
                        if world > 1 else None,
                        "l2": "no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
                              if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush"},
             "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES + 8 * n_geom_blocks),
-                    "d2h_bytes_per_step": int(W * H * 12), "steps": Ke, "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke,
-                    "mpixels_per_sec": W * H * fps_e / 1e6,
+                    "d2h_bytes_per_step": int(W * H * 12), "steps": Ke,
+                    "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke if fps_e else None,
+                    "mpixels_per_sec": W * H * fps_e / 1e6 if fps_e else None,
                     "result": "packed RGB float frame, the array MainWindow.OnRender uploads (MainWindow.cs:232-246), "
                               "srb_present_rgb_async into two alternating pinned host frames; D2H of frame k overlaps frame k+1",
                     "colorbuffer_float4_sync": {"value": fps_c, "unit": "frames/s", "d2h_bytes_per_step": int(W * H * 16),
@@ -502,6 +530,11 @@ def run_gpu(args):
                 line["roofline_frame"]["immediate_mode_equivalent_bytes"] = int(imm)
                 line["roofline_frame"]["fragments_tested"] = int(fr["tested"])
                 line["roofline_frame"]["fragments_shaded_in_submission_order"] = int(fr["shaded"])
+    if world > 1:
+        if fused and rank != 0:                  # unmap rank 0's frame before rank 0 frees it
+            (win.SetGatherRgba8Target if rgba8_gather else win.SetColorTarget)(None)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
     win.Close()
     if world > 1:
         dist.barrier()
@@ -552,6 +585,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"], help="N>1: how bands reach rank 0")
+    ap.add_argument("--gather-format", default="float4", choices=["float4", "rgba8"],
+                    help="N>1, fused gather: what the band ranks store into rank 0's frame (float4 ColorBuffer, or the "
+                         "frame at display precision: a quarter of the NVLink traffic)")
     ap.add_argument("--remote-cost", type=float, default=12.0,
                     help="N>1, fused gather: extra cost of a tile whose pixels are stored to rank 0 over NVLink, in bin pairs")
     ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"], help="N>1: band cut policy")

@@ -126,6 +126,18 @@ int srb_set_pipeline(SrbContext* ctx, int pipeline);
 #define SRB_IPC_HANDLE_BYTES 64
 int srb_export_color_handle(SrbContext* ctx, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]);
 int srb_set_color_target(SrbContext* ctx, const uint8_t handle[SRB_IPC_HANDLE_BYTES]);
+/* The same gather at display precision (payload float4 or RGBA8): rank 0 exports an RGBA8 frame
+ * (W*H*4 bytes, allocated by the call); from then on its own tile kernel stores clamp(c,0,1)*255 (round to
+ * nearest) of its band there, beside the float4 ColorBuffer.  A band rank that passes the handle as its target
+ * stores its band's bytes straight into rank 0's frame over NVLink (4 B per pixel instead of 16) and keeps its
+ * float4 colour local.  handle == NULL turns it off.  srb_read_gathered_rgba8 copies the assembled frame to
+ * the host (after the caller's frame barrier across ranks). */
+int srb_gather_rgba8_export(SrbContext* ctx, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]);
+int srb_gather_rgba8_target(SrbContext* ctx, const uint8_t handle[SRB_IPC_HANDLE_BYTES]);
+int srb_read_gathered_rgba8(SrbContext* ctx, uint8_t* rgba8_out);
+void* srb_device_gathered_rgba8_ptr(SrbContext* ctx);
+/* Queue the copy of the assembled frame to (pinned) host memory; same slots and rules as srb_present_rgba8_async. */
+int srb_present_gathered_rgba8_async(SrbContext* ctx, uint8_t* rgba8_out);
 /* Work per 16-px tile row of the last completed frame: (triangle, tile) pairs binned into the
  * row (out[0..n), n <= tile rows).  Input of cost-balanced band cuts. */
 int srb_get_tile_row_pairs(SrbContext* ctx, uint32_t* out, int n);

@@ -78,7 +78,8 @@ assert DRAW_CMD_DTYPE.itemsize == 248, DRAW_CMD_DTYPE.itemsize
 # Every symbol include/srb200.h declares (checked by tests/test_abi.py).
 EXPORTS = [
     "srb_create", "srb_destroy", "srb_resize", "srb_get_size", "srb_last_error", "srb_set_band",
-    "srb_set_pipeline", "srb_export_color_handle", "srb_set_color_target", "srb_get_tile_row_pairs",
+    "srb_set_pipeline", "srb_export_color_handle", "srb_set_color_target", "srb_gather_rgba8_export", "srb_gather_rgba8_target",
+    "srb_read_gathered_rgba8", "srb_device_gathered_rgba8_ptr", "srb_present_gathered_rgba8_async", "srb_get_tile_row_pairs",
     "srb_texture_create", "srb_texture_destroy", "srb_texture_sample",
     "srb_mesh_create", "srb_mesh_destroy", "srb_set_uniforms", "srb_begin_frame", "srb_draw",
     "srb_submit_draws", "srb_end_frame", "srb_replay_frame", "srb_sync", "srb_read_color",
@@ -159,7 +160,11 @@ def lib() -> C.CDLL:
     L.srb_set_pixel.argtypes = [vp, i32, i32, f32p]
     L.srb_get_depth.argtypes = [vp, i32, i32, f32p]
     L.srb_set_depth.argtypes = [vp, i32, i32, C.c_float]
-    for name in ("srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream"):
+    L.srb_gather_rgba8_export.argtypes = [vp, vp]
+    L.srb_gather_rgba8_target.argtypes = [vp, vp]
+    L.srb_read_gathered_rgba8.argtypes = [vp, vp]
+    L.srb_present_gathered_rgba8_async.argtypes = [vp, vp]
+    for name in ("srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream", "srb_device_gathered_rgba8_ptr"):
         getattr(L, name).argtypes = [vp]
         getattr(L, name).restype = vp
     L.srb_frustum_test.argtypes = [vp, vp, vp, vp, vp, i32, vp]

@@ -55,6 +55,8 @@ struct SrbContext {
     float4* color = nullptr;
     float* depth = nullptr;
     float4* colorTarget = nullptr;    // peer buffer opened from an IPC handle (band gather), or null
+    uint32_t* color8 = nullptr;       // RGBA8 gather frame owned by this context (rank 0 of an RGBA8 band gather)
+    uint32_t* color8Target = nullptr; // a peer's RGBA8 gather frame (band ranks)
     // present path: packed RGB float copies of finished frames, double buffered so that the D2H copy of
     // frame k (copy stream) overlaps the rendering of frame k+1 (pipeline stream)
     cudaStream_t copyStream = nullptr;
@@ -116,6 +118,9 @@ namespace {
 void close_color_target(SrbContext* c) {
     if (c->colorTarget) { cudaIpcCloseMemHandle(c->colorTarget); c->colorTarget = nullptr; }
 }
+void close_color8_target(SrbContext* c) {
+    if (c->color8Target) { cudaIpcCloseMemHandle(c->color8Target); c->color8Target = nullptr; }
+}
 
 int fail(SrbContext* c, int code, const std::string& msg) {
     if (c) c->err = msg; else g_createError = msg;
@@ -142,7 +147,8 @@ void default_uniforms(SrbUniforms& u) {
 int alloc_framebuffer(SrbContext* c, int w, int h) {
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
-    c->color = nullptr; c->depth = nullptr;
+    if (c->color8) cudaFree(c->color8);      // a resize drops the RGBA8 gather frame: export it again
+    c->color = nullptr; c->depth = nullptr; c->color8 = nullptr;
     CK(c, cudaMalloc((void**)&c->color, (size_t)w * h * sizeof(float4)));
     CK(c, cudaMalloc((void**)&c->depth, (size_t)w * h * sizeof(float)));
     CK(c, cudaMemsetAsync(c->color, 0, (size_t)w * h * sizeof(float4), c->stream));
@@ -242,6 +248,7 @@ int launch_frame(SrbContext* c) {
     A.clipAttrs = B.dClipAttrs.p; A.tileStart = B.dTileStart.p; A.tileEnd = B.dTileCursor.p;
     A.bins = B.dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = B.dCnt;
     A.colorOut = c->colorTarget ? c->colorTarget : c->color;
+    A.color8Out = c->color8Target ? c->color8Target : c->color8;
 #ifdef SRB_TILE_TIMING
     if (c->dBinScratch.reserve((size_t)nTiles * 8) != cudaSuccess) return fail(c, SRB_ERR_CUDA, "dbg alloc");
     A.dbg = (ulonglong4*)c->dBinScratch.p;
@@ -384,6 +391,8 @@ int srb_destroy(SrbContext* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     close_color_target(c);
+    close_color8_target(c);
+    if (c->color8) cudaFree(c->color8);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
     c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dClip.release();
@@ -470,6 +479,50 @@ int srb_set_color_target(SrbContext* c, const uint8_t handle[SRB_IPC_HANDLE_BYTE
     c->colorTarget = (float4*)p;
     return SRB_OK;
 }
+
+/* RGBA8 band gather (payload float4 or RGBA8 selectable). */
+int srb_gather_rgba8_export(SrbContext* c, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]) {
+    if (!c || !handle_out) return SRB_ERR_ARG;
+    if (c->inFrame) return fail(c, SRB_ERR_STATE, "gather frame change inside a frame");
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    if (!c->color8) {
+        CK(c, cudaMalloc((void**)&c->color8, (size_t)c->W * c->H * sizeof(uint32_t)));
+        CK(c, cudaMemset(c->color8, 0, (size_t)c->W * c->H * sizeof(uint32_t)));
+    }
+    cudaIpcMemHandle_t h;
+    CK(c, cudaIpcGetMemHandle(&h, c->color8));
+    std::memcpy(handle_out, &h, sizeof(h));
+    return SRB_OK;
+}
+
+int srb_gather_rgba8_target(SrbContext* c, const uint8_t handle[SRB_IPC_HANDLE_BYTES]) {
+    if (!c) return SRB_ERR_ARG;
+    if (c->inFrame) return fail(c, SRB_ERR_STATE, "gather target change inside a frame");
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    close_color8_target(c);
+    if (!handle) return SRB_OK;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    CK(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->color8Target = (uint32_t*)p;
+    return SRB_OK;
+}
+
+int srb_read_gathered_rgba8(SrbContext* c, uint8_t* out) {
+    if (!c || !out) return SRB_ERR_ARG;
+    if (!c->color8) return fail(c, SRB_ERR_STATE, "no RGBA8 gather frame on this context (srb_gather_rgba8_export first)");
+    int rc = srb_sync(c);
+    if (rc != SRB_OK) return rc;
+    CK(c, cudaMemcpy(out, c->color8, (size_t)c->W * c->H * 4, cudaMemcpyDeviceToHost));
+    return SRB_OK;
+}
+
+void* srb_device_gathered_rgba8_ptr(SrbContext* c) { return c ? (void*)c->color8 : nullptr; }
 
 int srb_get_tile_row_pairs(SrbContext* c, uint32_t* out, int n) {
     if (!c || !out || n < 0) return SRB_ERR_ARG;
@@ -901,8 +954,11 @@ int srb_read_color_rgba8(SrbContext* c, uint8_t* out) {
 
 /* Present path (MainWindow.cs:226-246).  Flatten on the device, copy on a second stream: the call returns
  * once the copy is queued, and the next frame may be submitted and rendered while it runs. */
-static int present_rows_async(SrbContext* c, void* out, int y0, int y1, bool rgba8) {
+// gathered: the source is this context's RGBA8 gather frame (already 8-bit, assembled by all band ranks): staged
+// with a device copy instead of a pack kernel, so that the next frame may overwrite the gather frame at once.
+static int present_rows_async(SrbContext* c, void* out, int y0, int y1, bool rgba8, bool gathered = false) {
     if (!c || !out) return SRB_ERR_ARG;
+    if (gathered && !c->color8) return fail(c, SRB_ERR_STATE, "no RGBA8 gather frame on this context (srb_gather_rgba8_export first)");
     if (y0 < 0 || y1 < y0 || y1 > c->H) return fail(c, SRB_ERR_ARG, "row range out of bounds");
     int rc = srb_sync(c);                                  // frame finished and capacity overflows settled
     if (rc != SRB_OK) return rc;
@@ -920,7 +976,9 @@ static int present_rows_async(SrbContext* c, void* out, int y0, int y1, bool rgb
         c->presentBusy[s] = false;
     }
     CK(c, c->dPresent[s].reserve((rgba8 ? n : n * 3) + 16));
-    if (rgba8)
+    if (gathered)
+        CK(c, cudaMemcpyAsync(c->dPresent[s].p, c->color8 + first, n * 4, cudaMemcpyDeviceToDevice, c->stream));
+    else if (rgba8)
         present_rgba8_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color + first, (uint32_t*)c->dPresent[s].p, n);
     else
         present_rgb_kernel<<<(unsigned)((n / 4 + 1 + 255) / 256), 256, 0, c->stream>>>(c->color + first, c->dPresent[s].p, n);
@@ -941,6 +999,9 @@ int srb_present_rgb_rows_async(SrbContext* c, float* out, int y0, int y1) { retu
 int srb_present_rgba8_rows_async(SrbContext* c, uint8_t* out, int y0, int y1) { return present_rows_async(c, out, y0, y1, true); }
 int srb_present_rgba8_async(SrbContext* c, uint8_t* out) {
     return c ? present_rows_async(c, out, 0, c->H, true) : SRB_ERR_ARG;
+}
+int srb_present_gathered_rgba8_async(SrbContext* c, uint8_t* out) {
+    return c ? present_rows_async(c, out, 0, c->H, true, true) : SRB_ERR_ARG;
 }
 int srb_present_rgba8(SrbContext* c, uint8_t* out) {
     int rc = srb_present_rgba8_async(c, out);

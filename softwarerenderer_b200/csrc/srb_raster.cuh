@@ -182,6 +182,7 @@ ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     if (inb) {
         A.colorOut[pidx] = col;
         A.depth[pidx] = dep;
+        if (A.color8Out) A.color8Out[pidx] = pack_unorm8(col);
     }
 }
 
@@ -290,6 +291,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
                 const size_t pidx = (size_t)y * fp.W + x;
                 __stcs(A.colorOut + pidx, clearCol);
                 __stcs(A.depth + pidx, kClearDepth);
+                if (A.color8Out) __stcs(A.color8Out + pidx, pack_unorm8(clearCol));
             }
         }
         return;
@@ -408,6 +410,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         const size_t pidx = (size_t)y * fp.W + x;
         __stcs(A.colorOut + pidx, outc);
         __stcs(A.depth + pidx, outd);
+        if (A.color8Out) __stcs(A.color8Out + pidx, pack_unorm8(outc));
     }
 }
 
@@ -465,10 +468,6 @@ __global__ void pack_rgba8_kernel(const float4* __restrict__ color, uchar4* __re
 // The same step at display precision: the reference draws its RGBA32F texture into the window's 8-bit
 // framebuffer (MainWindow.cs:251-253), i.e. clamp to [0,1] and round to the nearest of 255 steps -- the format
 // of the parity gate.  Four pixels per thread: 4 x 128-bit loads, one 128-bit store.
-__device__ __forceinline__ uint32_t pack_unorm8(const float4 c) {
-    auto q = [](float v) { return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.0f), 1.0f) * 255.0f); };   // NaN -> 0
-    return q(c.x) | (q(c.y) << 8) | (q(c.z) << 16) | (q(c.w) << 24);
-}
 __global__ void present_rgba8_kernel(const float4* __restrict__ color, uint32_t* __restrict__ out, size_t n) {
     const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t i = q * 4;

@@ -18,11 +18,19 @@ struct RasterArgs {
     float4* color;                // this context's colour buffer (read when a frame does not clear)
     float4* colorOut;             // where final colour is stored: == color, or a peer GPU's buffer (band gather)
     float* depth;
+    uint32_t* color8Out;          // optional second destination of final colour at display precision (R,G,B,A bytes):
+                                  // the RGBA8 band gather -- rank 0's own frame or a peer GPU's (null: off)
 #ifdef SRB_TILE_TIMING
     ulonglong4* dbg;              // per-CTA {start ns, end ns, tile<<32 | bin length, smid} (diagnostic builds only)
 #endif
     const Counters* cnt;          // kernels bail out when a capacity overflowed (frame is re-run)
 };
+
+// Display precision: clamp to [0,1], x255, round to nearest (what the reference's blit leaves in the 8-bit window).
+__device__ __forceinline__ uint32_t pack_unorm8(const float4 c) {
+    auto q = [](float v) { return (uint32_t)__float2int_rn(fminf(fmaxf(v, 0.0f), 1.0f) * 255.0f); };   // NaN -> 0
+    return q(c.x) | (q(c.y) << 8) | (q(c.z) << 16) | (q(c.w) << 24);
+}
 
 // Texture.Sample (Texture.cs:42-63): nearest, repeat.
 __device__ __forceinline__ float4 tex_nearest(const uchar4* tex, int tw, int th, float uu, float vv) {

@@ -107,6 +107,26 @@ class MainWindow:
             buf = (C.c_uint8 * 64).from_buffer_copy(handle)
             N.check(self._ctx, N.lib().srb_set_color_target(self._ctx, buf))
 
+    # -- the same gather at display precision: 4 B per pixel over NVLink --------------
+    def ExportGatherRgba8(self) -> bytes:
+        """Rank 0: create the RGBA8 gather frame; this window's tile kernel fills its own band of it."""
+        buf = (C.c_uint8 * 64)()
+        N.check(self._ctx, N.lib().srb_gather_rgba8_export(self._ctx, buf))
+        return bytes(buf)
+
+    def SetGatherRgba8Target(self, handle: Optional[bytes]) -> None:
+        """Band rank: store the band's 8-bit colour into the frame behind `handle` (float4 colour stays local)."""
+        if handle is None:
+            N.check(self._ctx, N.lib().srb_gather_rgba8_target(self._ctx, None))
+        else:
+            buf = (C.c_uint8 * 64).from_buffer_copy(handle)
+            N.check(self._ctx, N.lib().srb_gather_rgba8_target(self._ctx, buf))
+
+    def GatheredRgba8(self) -> np.ndarray:
+        out = np.empty((self.RenderHeight, self.RenderWidth, 4), dtype=np.uint8)
+        N.check(self._ctx, N.lib().srb_read_gathered_rgba8(self._ctx, N.ptr(out)))
+        return out
+
     def TileRowPairs(self) -> np.ndarray:
         """(triangle, tile) pairs binned into each 16-px tile row by the last frame."""
         n = (self.RenderHeight + 15) // 16

@@ -18,7 +18,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, out_path):
+def _worker(rank, world, port, out_path, rgba8=False):
     import torch.distributed as dist
 
     import softwarerenderer_b200 as srb
@@ -32,18 +32,21 @@ def _worker(rank, world, port, out_path):
         S.submit_scene(win, sc)                                   # full frame once: per-row work for the cuts
         cuts = balanced_cuts(win.TileRowPairs().astype(np.float64) + 0.85 * 80, world)
         win.SetBand(cuts[rank], cuts[rank + 1])
-        box = [win.ExportColorHandle() if rank == 0 else None]
+        box = [(win.ExportGatherRgba8() if rgba8 else win.ExportColorHandle()) if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
         if rank != 0:
-            win.SetColorTarget(box[0])
+            (win.SetGatherRgba8Target if rgba8 else win.SetColorTarget)(box[0])
         dist.barrier()
         S.submit_scene(win, sc)
         win.Sync()
         dist.barrier()                                            # every band has landed in rank 0's buffer
         if rank == 0:
-            np.savez(out_path, color=win.ColorBuffer, cuts=np.array(cuts))
+            np.savez(out_path, color=win.GatheredRgba8() if rgba8 else win.ColorBuffer, cuts=np.array(cuts))
+        if rgba8:                                                     # float4 colour stays on the rank that rendered it
+            y0, y1 = cuts[rank] * 16, min(cuts[rank + 1] * 16, sc.height)
+            np.save(out_path + f".band{rank}.npy", win.ColorBuffer[y0:y1])
         dist.barrier()
-        win.SetColorTarget(None)
+        (win.SetGatherRgba8Target if rgba8 else win.SetColorTarget)(None)
         win.Close()
     finally:
         dist.destroy_process_group()
@@ -61,4 +64,27 @@ def test_fused_band_gather_reproduces_the_full_frame(tmp_path, oracle):
     cuts = z["cuts"].tolist()
     assert cuts[0] == 0 and cuts[-1] == 45 and 0 < cuts[1] < 45
     d8 = np.abs(to_u8(z["color"]) - to_u8(oc)).max(axis=-1)
+    assert (d8 <= 1).mean() >= 0.999 and d8.max() <= 1
+
+
+def test_rgba8_band_gather_assembles_the_quantised_frame(tmp_path, oracle):
+    """The same gather at display precision (srb_gather_rgba8_export / _target): 4-byte peer stores; rank 0's gather
+    frame must be the whole frame, equal to each rank's own float4 band quantised, and within the gate of the oracle."""
+    import torch.multiprocessing as mp
+
+    from softwarerenderer_b200 import scene as S
+    from tests.util import to_u8
+    out = str(tmp_path / "fused8.npz")
+    mp.spawn(_worker, args=(2, _free_port(), out, True), nprocs=2, join=True)
+    z = np.load(out)
+    cuts = z["cuts"].tolist()
+    frame = z["color"]
+    assert frame.dtype == np.uint8 and frame.shape == (720, 1280, 4)
+    for r in range(2):
+        band = np.load(out + f".band{r}.npy")
+        y0 = cuts[r] * 16
+        want = np.rint(np.clip(band, 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+        assert np.array_equal(frame[y0:y0 + band.shape[0]], want)
+    oc, _, _ = oracle.render_scene(S.scene_city(1280, 720, n_instances=24), threads=8)
+    d8 = np.abs(frame.astype(np.int32) - to_u8(oc)).max(axis=-1)
     assert (d8 <= 1).mean() >= 0.999 and d8.max() <= 1
