@@ -442,6 +442,32 @@ def run_gpu(args):
         stage_ms_ranks = [None] * world
         dist.all_gather_object(stage_ms_ranks, stage_ms)
 
+    # ---- N>1, float4 gather: the same resident loop once more with the RGBA8 gather (reported beside `value`,
+    # never in its place): band ranks switch from float4 peer stores to 4-byte ones into rank 0's RGBA8 frame ----
+    rgba8_extra = None
+    if fused and not rgba8_gather and not args.no_rgba8_extra:
+        box8 = [win.ExportGatherRgba8() if rank == 0 else None]
+        dist.broadcast_object_list(box8, src=0)
+        if rank != 0:
+            win.SetColorTarget(None)
+            win.SetGatherRgba8Target(box8[0])
+        dist.barrier()
+        Kx = min(K, 300)
+        ms_x, _, _ = timed(step_resident, Kx, 3)
+        full8 = torch.from_numpy(win.GatheredRgba8()).to(dev) if rank == 0 else torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
+        dist.broadcast(full8, src=0)
+        mine = np.rint(np.clip(win.ColorBuffer[y0:y1], 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+        oks8 = [None] * world
+        dist.all_gather_object(oks8, bool(np.array_equal(full8[y0:y1].cpu().numpy(), mine)))
+        del full8
+        rgba8_extra = {"value": Kx / (ms_x / 1000.0), "unit": "frames/s", "steps": Kx, "verified": all(oks8),
+                       "note": "same loop, bands gathered at display precision (--gather-format rgba8): 4 B per pixel "
+                               "into one RGBA8 frame on GPU 0, float4 bands stay on the rendering GPU"}
+        if rank != 0:                               # back to the float4 gather
+            win.SetGatherRgba8Target(None)
+            win.SetColorTarget(box[0])
+        dist.barrier()
+
     # ---- roofline bookkeeping ----
     depth = win.DepthBuffer
     p_cov = int((depth[y0:y1] != np.float32(-3.4028235e38)).sum())
@@ -506,6 +532,7 @@ def run_gpu(args):
             "e2e_parallel_present": e2e_parallel,     # N>1: promoted to `e2e` below; the gather-to-GPU-0 loop is kept beside it
             "gpu_launches": int(st.kernel_launches) * K,          # timed region of `value`; each e2e step adds the flatten kernel
             "clocks": clocks,
+            "value_rgba8_gather": rgba8_extra,
             "frame_latency": frame_latency,
             "stage_ms": stage_ms,
             "stage_ms_ranks": stage_ms_ranks,
@@ -588,6 +615,7 @@ def main():
     ap.add_argument("--gather-format", default="float4", choices=["float4", "rgba8"],
                     help="N>1, fused gather: what the band ranks store into rank 0's frame (float4 ColorBuffer, or the "
                          "frame at display precision: a quarter of the NVLink traffic)")
+    ap.add_argument("--no-rgba8-extra", action="store_true", help="N>1: skip the additional RGBA8-gather measurement")
     ap.add_argument("--remote-cost", type=float, default=12.0,
                     help="N>1, fused gather: extra cost of a tile whose pixels are stored to rank 0 over NVLink, in bin pairs")
     ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"], help="N>1: band cut policy")
