@@ -7,6 +7,7 @@
 // There is no CPU fallback: without a CUDA device srb_create fails.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -61,6 +62,11 @@ struct SrbContext {
     // frame k (copy stream) overlaps the rendering of frame k+1 (pipeline stream)
     cudaStream_t copyStream = nullptr;
     DevBuf<float> dPresent[2];
+    int bigCountCtas = std::getenv("SRB_BIGCOUNT_CTAS") ? std::atoi(std::getenv("SRB_BIGCOUNT_CTAS")) : 1;   // CTAs per SM of the large-triangle count pass
+    int fillCtas = std::getenv("SRB_FILL_CTAS") ? std::atoi(std::getenv("SRB_FILL_CTAS")) : 2;                 // CTAs per SM and role of the fill pass
+    // (Both passes wait on atomic round trips, not on issue slots: with 4 CTAs per SM they are a few us shorter alone
+    // -- fill 20 vs 26 us, count 45.5 vs 50 us for setup+count -- but hold four times the registers while the previous
+    // frame's tile kernel wants them; pipelined, city4k runs at 5,590 frames/s with 1 / 2 against 5,450 with 4 / 4.)
     DevBuf<float4> dRayScratch;       // srb_raycast: directions, hits, keys, rays
     cudaEvent_t presentReady[2] = {}, presentCopied[2] = {};
     bool presentBusy[2] = {false, false};
@@ -213,7 +219,7 @@ int launch_frame(SrbContext* c) {
         setup_kernel<<<c->nTBlocks, kGeomBlock, 0, gs>>>(
             c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
             c->dTileCount.p, B.dCnt);
-        bin_big_kernel<0><<<c->smCount * 4, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
+        bin_big_kernel<0><<<c->smCount * c->bigCountCtas, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
         launches += 2;
     }
     mark(3);
@@ -229,7 +235,7 @@ int launch_frame(SrbContext* c) {
         unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
         // One launch or two: decided from the last completed frame's counters (a heuristic only -- both
         // orders of filling give the same bins up to order, which no consumer depends on).
-        const unsigned wave = (unsigned)c->smCount * 4;
+        const unsigned wave = (unsigned)c->smCount * c->fillCtas;
         if (prevBig > 0 && prevRefs <= wave * 256u) {
             fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(c->dRefs.p, c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
                                                                B.dBins.p, wave);
