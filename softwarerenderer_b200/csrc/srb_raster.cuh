@@ -280,7 +280,11 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float4 clearCol = make_float4(fp.clearColor[0], fp.clearColor[1], fp.clearColor[2], fp.clearColor[3]);
 
+#ifdef SRB_EXP_ALL_EMPTY                         /* diagnostic builds only: every tile takes the clear-only path */
+    if (true) {
+#else
     if (bs == SRB_BE) {
+#endif
 #ifdef SRB_EXP_SKIP_EMPTY
         return;
 #endif
