@@ -429,6 +429,8 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     // queue, each CTA fetching its next tile's order entry and first bin entries and prefetching their records
     // while the current tile is shaded -- raster 113 -> 124 us, and resident CTAs that never retire keep the
     // pipelined geometry kernels of the next frame off the SMs: city4k 5,470 -> 4,850 frames/s.)
+    // (Measured and rejected as well: M tiles per CTA at a fixed stride through the launch order, look-ahead fetches
+    // included, M = 2..8: raster 115 -> 117..124 us.)
     // One load gives the tile and its bin range.  (Measured and rejected: clearing the frame on a second
     // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
     const uint4 o = __ldg(A.order + blockIdx.x);
