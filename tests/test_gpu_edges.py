@@ -1,0 +1,124 @@
+"""-m gpu: edge cases of the path against the oracle -- empty frames, targets smaller than a tile, degenerate,
+off-screen, NaN/Inf and w == 0 geometry, a draw with no triangles, everything frustum-culled, resize."""
+import numpy as np
+import pytest
+
+from tests.test_gpu_parity import _render_gpu
+from tests.util import CLEAR_DEPTH, compare, screen_tri_scene
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("size", [(1, 1), (7, 3), (16, 16), (17, 33), (250, 1)])
+@pytest.mark.parametrize("pipeline", [1, 2])
+def test_frame_without_draws_is_the_clear(size, pipeline):
+    from softwarerenderer_b200.scene import Scene
+    W, H = size
+    sc = Scene(W, H, [], clear_color=(0.25, 0.5, 0.75, 1.0))
+    c, d, st = _render_gpu(sc, pipeline)
+    assert c.shape == (H, W, 4) and (d == CLEAR_DEPTH).all()
+    assert np.array_equal(c, np.broadcast_to(np.array([0.25, 0.5, 0.75, 1.0], np.float32), c.shape))
+    assert st.triangles_submitted == 0
+
+
+@pytest.mark.parametrize("size", [(1, 1), (5, 9), (15, 15), (31, 17)])
+@pytest.mark.parametrize("pipeline", [1, 2])
+def test_targets_smaller_than_or_straddling_a_tile(oracle, size, pipeline):
+    W, H = size
+    tris = [[(-4, -4), (3 * W + 8, -4), (-4, 3 * H + 8)], [(0.25, 0.25), (W - 0.5, 0.5), (W * 0.5, H - 0.25)]]
+    sc = screen_tri_scene_any(W, H, tris)
+    oc, od, _ = oracle.render_scene(sc, threads=2)
+    gc, gd, _ = _render_gpu(sc, pipeline)
+    compare(gc, gd, oc, od, min_frac=0.0 if W * H < 100 else 0.999)
+    assert np.array_equal(gd, od)
+
+
+def screen_tri_scene_any(W, H, tris, **kw):
+    """screen_tri_scene for any W, H: vertices are given in pixels and mapped through the same float32 viewport
+    arithmetic both sides use, so exact invertibility does not matter -- oracle and GPU get identical inputs."""
+    return screen_tri_scene(W, H, tris, cull=0, colors=[(1.0, 0.5, 0.25, 1.0), (0.2, 0.9, 0.4, 1.0)][: len(tris)],
+                            ndc_z=[0.25, 0.5][: len(tris)], **kw)
+
+
+@pytest.mark.parametrize("pipeline", [1, 2])
+def test_degenerate_offscreen_and_non_finite_triangles(oracle, pipeline):
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200.scene import DrawItem, Mesh, Scene
+    from softwarerenderer_b200.shaders import Material, Shaders
+    W, H = 64, 48
+    nan, inf = float("nan"), float("inf")
+    pos = [
+        (-0.5, -0.5, 0.5), (0.5, -0.5, 0.5), (0.0, 0.5, 0.5),          # 0: ordinary
+        (0.1, 0.1, 0.5), (0.1, 0.1, 0.5), (0.1, 0.1, 0.5),             # 1: a point (area 0, :396)
+        (-0.9, -0.9, 0.5), (0.0, 0.0, 0.5), (0.9, 0.9, 0.5),           # 2: collinear (area 0)
+        (5.0, 5.0, 0.5), (6.0, 5.0, 0.5), (5.0, 6.0, 0.5),             # 3: entirely off-screen (empty bbox)
+        (nan, 0.0, 0.5), (0.5, 0.5, 0.5), (0.0, 0.5, 0.5),             # 4: NaN position (:378-380)
+        (inf, 0.0, 0.5), (0.5, 0.5, 0.5), (0.0, 0.5, 0.5),             # 5: Inf position
+        (-1e15, -1e15, 0.5), (1e15, -1e15, 0.5), (0.0, 1e15, 0.5),     # 6: huge but finite edge products: covers the whole target
+        (-1e30, -1e30, 0.4), (1e30, -1e30, 0.4), (0.0, 1e30, 0.4),     # 6b: edge products overflow -> NaN area, covers nothing
+        (-0.2, -0.2, 0.2), (0.2, -0.2, 0.2), (0.0, 0.2, 0.2),          # 7: small, nearer
+    ]
+    col = np.repeat(np.array([(1, 0, 0, 1), (0, 1, 0, 1), (0, 0, 1, 1), (1, 1, 0, 1), (0, 1, 1, 1), (1, 0, 1, 1),
+                              (0.5, 0.5, 0.5, 1), (0.3, 0.3, 0.3, 1), (1, 1, 1, 1)], dtype=np.float32), 3, axis=0)
+    v = Shaders.make_vertices(pos, color=col)
+    I = nm.identity()
+    mesh = Mesh(v, np.arange(len(pos), dtype=np.uint16), Material())
+    empty = Mesh(Shaders.make_vertices([(0, 0, 0)]), np.zeros(0, dtype=np.uint16), Material())     # a draw with no triangles
+    sc = Scene(W, H, [DrawItem(empty, I, I, I, cull=0), DrawItem(mesh, I, I, I, cull=0), DrawItem(empty, I, I, I, cull=0)],
+               clear_color=(0, 0, 0, 0), fog_start=10.0, fog_end=20.0)
+    oc, od, ost = oracle.render_scene(sc, threads=2)
+    gc, gd, st = _render_gpu(sc, pipeline)
+    compare(gc, gd, oc, od)
+    assert (od != CLEAR_DEPTH).all()                                   # the huge triangle covers everything
+    assert st.triangles_submitted == 9
+    assert abs(float(od[0, 0]) + 0.75) < 1e-6 and abs(float(od[H - 1, W - 1]) + 0.75) < 1e-6   # (0.5 + 1) / 2, negated: triangle 6, not 6b
+
+
+def test_w_zero_and_behind_the_camera(oracle):
+    """Corners with w <= 0 go through the near clip (:208-224); all three behind: dropped; w == 0 exactly (:393)."""
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200.scene import DrawItem, Mesh, Scene, default_projection
+    from softwarerenderer_b200.shaders import Material, Shaders
+    W, H = 160, 96
+    pos = [(-1, -1, -3), (1, -1, -3), (0, 1, 2),          # one corner behind the camera
+           (-1, -1, 2), (1, -1, 3), (0, 1, 4),            # all behind
+           (-2, -0.5, 0.0), (2, -0.5, 0.0), (0, 0.5, -4), # two corners at z == 0: w == 0 under the projection
+           (-1, 0.2, -2), (1, 0.2, -2), (0, 1.0, -2)]     # ordinary
+    v = Shaders.make_vertices(pos)
+    mesh = Mesh(v, np.arange(12, dtype=np.uint16), Material())
+    I = nm.identity()
+    sc = Scene(W, H, [DrawItem(mesh, I, I, default_projection(W, H), cull=0)])
+    oc, od, _ = oracle.render_scene(sc, threads=2)
+    for pipeline in (1, 2):
+        gc, gd, st = _render_gpu(sc, pipeline)
+        compare(gc, gd, oc, od)
+        assert st.clipped_triangles >= 1
+
+
+def test_everything_frustum_culled_leaves_the_clear(oracle):
+    from softwarerenderer_b200 import scene as S
+    sc = S.scene_city(320, 180, n_instances=6)
+    for d in sc.draws:                                    # move every instance far behind the camera
+        m = np.array(d.model, dtype=np.float32).reshape(4, 4).copy()
+        m[3, 2] += 5000.0
+        d.model = m
+    assert not any(oracle.frustum_flags(sc))
+    gc, gd, st = _render_gpu(sc, 0)
+    assert st.draws_visible == 0 and (gd == CLEAR_DEPTH).all()
+
+
+def test_resize_between_frames(oracle):
+    """MainWindow.HandleResize (MainWindow.cs:298-361): new buffers, same meshes and textures."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    win = srb.MainWindow(320, 180)
+    try:
+        for W, H in ((320, 180), (640, 361), (100, 40), (320, 180)):
+            win.Resize(W, H)
+            assert (win.RenderWidth, win.RenderHeight) == (W, H)
+            sc = S.scene_model("Gun", W, H)
+            S.submit_scene(win, sc)
+            oc, od, _ = oracle.render_scene(sc, threads=4)
+            compare(win.ColorBuffer, win.DepthBuffer, oc, od)
+    finally:
+        win.Close()
