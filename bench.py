@@ -592,11 +592,21 @@ def cpu_baseline(scene, budget_s=25.0):
             break
     st = O.OrcStats()
     L.orc_get_stats(win, C.byref(st))            # counters restart at every orc_clear_depth: the last frame's
+    # (i) of SURVEY.md 8(d): the literal single-thread walk (reference loop order), one frame, if the budget allows
+    single = None
+    if float(np.median(times)) * cores < 20.0:
+        t0 = time.perf_counter()
+        L.orc_clear_depth(win)
+        L.orc_clear_color(win, cc)
+        for k in range(n):
+            L.orc_render_mesh(win, C.byref(arr[k]), C.byref(u))
+        single = 1.0 / (time.perf_counter() - t0)
     L.orc_destroy(win)
     meas = times[1:] if len(times) > 1 else times
     med = float(np.median(meas))
     return {"fragments": {"tested": int(st.fragments_tested), "shaded": int(st.fragments_shaded)},
             "value": 1.0 / med, "unit": "frames/s", "cores": cores, "kind": "port",
+            "single_thread_literal_value": single,
             "sample": f"{len(meas)} full frame(s) after 1 warm-up, median; C++ restatement of the C# path "
                       "(tile-row-parallel, bit-identical to the literal oracle); the C# reference cannot run here"}
 
