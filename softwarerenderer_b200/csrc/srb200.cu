@@ -217,7 +217,7 @@ int launch_frame(SrbContext* c) {
     mark(2);
     if (c->nTBlocks > 0) {
         setup_kernel<<<c->nTBlocks, kGeomBlock, 0, gs>>>(
-            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
+            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
             c->dTileCount.p, B.dCnt);
         bin_big_kernel<0><<<c->smCount * c->bigCountCtas, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
         launches += 2;
@@ -250,7 +250,7 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaEventRecord(c->geomDone[s], gs));
     CK(c, cudaStreamWaitEvent(c->stream, c->geomDone[s], 0));
     RasterArgs A;
-    A.draws = c->dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p;
+    A.draws = c->dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
     A.clipAttrs = B.dClipAttrs.p; A.tileStart = B.dTileStart.p; A.tileEnd = B.dTileCursor.p;
     A.bins = B.dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = B.dCnt;
     A.colorOut = c->colorTarget ? c->colorTarget : c->color;

@@ -215,7 +215,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
                 const int parts = big_parts(out.tx[k], out.ty[k]);
                 if (bi + parts > fp.bigCap) { atomicOr(&cnt->overflow, 4u); bi += parts; continue; }
                 // the record this thread stored a moment ago: plain (coherent) loads, not the read-only path
-                const volatile float4* q = recs.R + 3 * (size_t)out.seq[k];
+                const volatile float4* q = recs.R + 3 * rec_slot(recs, out.seq[k]);
                 const float ax = q[0].x, ay = q[0].y, az = q[0].z, aw = q[0].w, bx = q[1].x, by = q[1].y;
                 const float cz = q[2].z, cw = q[2].w;
                 const int y0 = out.ty[k] & 0xffff, y1 = out.ty[k] >> 16, rows = big_rows(out.tx[k]);

@@ -60,19 +60,27 @@ struct TriRec {
 struct RecStore {
     float4* R;                // 3 float4 per slot
     float4* S;                // 2 float4 per slot
+    uint32_t fan1Base;        // first slot of the second fan triangles (= total triangle count of the frame)
 };
+// seq = 2*global_triangle + fan.  Fan 0 (every unclipped triangle) lives at slot global_triangle, so that a warp of
+// the setup kernel writes one contiguous run of records and the records a tile gathers sit densely in their lines;
+// the rare second triangle of a near-clipped fan lives at fan1Base + global_triangle.  (With slot = seq every other
+// slot was a hole: 48-byte records at a 96-byte pitch, i.e. two half-used sectors per record in both directions.)
+__device__ __forceinline__ size_t rec_slot(const RecStore& st, uint32_t seq) {
+    return (size_t)(seq >> 1) + ((seq & 1u) ? (size_t)st.fan1Base : 0);
+}
 __device__ __forceinline__ void store_rec(const RecStore& st, uint32_t seq, const TriRec& r) {
-    float4* q = st.R + 3 * (size_t)seq;
+    float4* q = st.R + 3 * rec_slot(st, seq);
     q[0] = make_float4(r.s0x, r.s0y, r.s1x, r.s1y);
     q[1] = make_float4(r.s2x, r.s2y, r.d0, r.d1);
     q[2] = make_float4(r.d2, r.invArea, __uint_as_float(r.bx), __uint_as_float(r.by));
-    float4* t = st.S + 2 * (size_t)seq;
+    float4* t = st.S + 2 * rec_slot(st, seq);
     t[0] = make_float4(r.cz0, r.cz1, r.cz2, r.cw0);
     t[1] = make_float4(r.cw1, r.cw2, __uint_as_float(r.meta), 0.0f);
 }
 // Coverage part only (cz/cw/meta left unset).
 __device__ __forceinline__ TriRec load_rec_raster(const RecStore& st, uint32_t seq) {
-    const float4* q = st.R + 3 * (size_t)seq;
+    const float4* q = st.R + 3 * rec_slot(st, seq);
     float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
     TriRec r;
     r.s0x = a.x; r.s0y = a.y; r.s1x = a.z; r.s1y = a.w;
@@ -82,7 +90,7 @@ __device__ __forceinline__ TriRec load_rec_raster(const RecStore& st, uint32_t s
 }
 __device__ __forceinline__ TriRec load_rec(const RecStore& st, uint32_t seq) {
     TriRec r = load_rec_raster(st, seq);
-    const float4* t = st.S + 2 * (size_t)seq;
+    const float4* t = st.S + 2 * rec_slot(st, seq);
     float4 a = __ldg(t), b = __ldg(t + 1);
     r.cz0 = a.x; r.cz1 = a.y; r.cz2 = a.z; r.cw0 = a.w;
     r.cw1 = b.x; r.cw2 = b.y; r.meta = __float_as_uint(b.z);
