@@ -262,11 +262,16 @@ int launch_frame(SrbContext* c) {
     if (bandTiles > 0) {
         if (c->useVis) {
             mark(6);                       // no sort stage on the visibility path
+            const bool out8 = A.color8Out != nullptr;
             switch (c->visMode) {
-                case 0: vis_tile_kernel<0><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
-                case 1: vis_tile_kernel<1><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
-                case 2: vis_tile_kernel<2><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
-                default: vis_tile_kernel<3><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 0: if (out8) vis_tile_kernel<0, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
+                        else vis_tile_kernel<0, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 1: if (out8) vis_tile_kernel<1, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
+                        else vis_tile_kernel<1, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 2: if (out8) vis_tile_kernel<2, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
+                        else vis_tile_kernel<2, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                default: if (out8) vis_tile_kernel<3, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
+                         else vis_tile_kernel<3, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
             }
             ++launches;
         } else {

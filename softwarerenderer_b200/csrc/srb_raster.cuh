@@ -261,7 +261,7 @@ struct VisSmem {
 
 // One 16x16 tile, whole CTA.  Ends with every thread past its last shared-memory access
 // only after the caller's __syncthreads() (heavy-list CTAs loop over several tiles).
-template <int MODE>
+template <int MODE, bool OUT8>
 #ifdef SRB_EXP_CAP_BIN
 #define SRB_BE be_
 #else
@@ -295,7 +295,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
                 const size_t pidx = (size_t)y * fp.W + x;
                 __stcs(A.colorOut + pidx, clearCol);
                 __stcs(A.depth + pidx, kClearDepth);
-                if (A.color8Out) __stcs(A.color8Out + pidx, pack_unorm8(clearCol));
+                if (OUT8) __stcs(A.color8Out + pidx, pack_unorm8(clearCol));
             }
         }
         return;
@@ -414,14 +414,16 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         const size_t pidx = (size_t)y * fp.W + x;
         __stcs(A.colorOut + pidx, outc);
         __stcs(A.depth + pidx, outd);
-        if (A.color8Out) __stcs(A.color8Out + pidx, pack_unorm8(outc));
+        if (OUT8) __stcs(A.color8Out + pidx, pack_unorm8(outc));
     }
 }
 
 #ifndef SRB_VIS_MINBLOCKS
 #define SRB_VIS_MINBLOCKS 8
 #endif
-template <int MODE>
+// OUT8: the frame is also stored at display precision into A.color8Out (RGBA8 band gather); a template parameter
+// because a run-time test of the pointer cost the default path 2 us.
+template <int MODE, bool OUT8>
 __global__ void __launch_bounds__(kVisThreads, SRB_VIS_MINBLOCKS)
 vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     __shared__ VisSmem sm;
@@ -441,7 +443,7 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
 #endif
-    vis_process_tile<MODE>((int)o.x, o.y, o.z, A, fp, U, sm);
+    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, A, fp, U, sm);
 #ifdef SRB_TILE_TIMING
     __syncthreads();
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
