@@ -63,10 +63,10 @@ struct SrbContext {
     cudaStream_t copyStream = nullptr;
     DevBuf<float> dPresent[2];
     int bigCountCtas = std::getenv("SRB_BIGCOUNT_CTAS") ? std::atoi(std::getenv("SRB_BIGCOUNT_CTAS")) : 1;   // CTAs per SM of the large-triangle count pass
-    int fillCtas = std::getenv("SRB_FILL_CTAS") ? std::atoi(std::getenv("SRB_FILL_CTAS")) : 2;                 // CTAs per SM and role of the fill pass
-    // (Both passes wait on atomic round trips, not on issue slots: with 4 CTAs per SM they are a few us shorter alone
-    // -- fill 20 vs 26 us, count 45.5 vs 50 us for setup+count -- but hold four times the registers while the previous
-    // frame's tile kernel wants them; pipelined, city4k runs at 5,590 frames/s with 1 / 2 against 5,450 with 4 / 4.)
+    int fillCtas = std::getenv("SRB_FILL_CTAS") ? std::atoi(std::getenv("SRB_FILL_CTAS")) : 4;                 // CTAs per SM and role of the fill pass
+    // (The count pass waits on atomic round trips, not on issue slots: with 4 CTAs per SM it is a few us shorter alone
+    // -- 45.5 vs 50 us for setup+count -- but holds four times the registers while the previous frame's tile kernel
+    // wants them; pipelined, city4k gains about 1 % with 1.)
     DevBuf<float4> dRayScratch;       // srb_raycast: directions, hits, keys, rays
     cudaEvent_t presentReady[2] = {}, presentCopied[2] = {};
     bool presentBusy[2] = {false, false};
@@ -233,10 +233,15 @@ int launch_frame(SrbContext* c) {
         // grid-stride over the accepted-triangle list (its length is only known on the device)
         size_t maxRefs = 2 * (size_t)fp.totalT;
         unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
-        // One launch or two: decided from the last completed frame's counters (a heuristic only -- both
-        // orders of filling give the same bins up to order, which no consumer depends on).
         const unsigned wave = (unsigned)c->smCount * c->fillCtas;
-        if (prevBig > 0 && prevRefs <= wave * 256u) {
+        // One launch or two.  The merged kernel saves a launch, which is what a small, launch-latency-bound frame
+        // wants (gun1080: 18,670 frames/s merged, 17,440 as two launches).  Its CTAs are twice as heavy, though (64+
+        // registers x 256 threads), and beside the previous frame's tile kernel a large frame does better with the two
+        // lean launches although they take 4 us longer alone (city4k: 5,690 against 5,590 frames/s).
+        // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
+        // bins up to order, which no consumer depends on).  SRB_FILL_MERGE: 0 never, 1 (default) small frames, 2 always.
+        static const int mergeMode = std::getenv("SRB_FILL_MERGE") ? std::atoi(std::getenv("SRB_FILL_MERGE")) : 1;
+        if (mergeMode != 0 && prevBig > 0 && (mergeMode == 2 || prevRefs <= 16384u)) {
             fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(c->dRefs.p, c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
                                                                B.dBins.p, wave);
         } else {
