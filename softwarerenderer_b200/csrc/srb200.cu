@@ -175,6 +175,10 @@ int launch_frame(SrbContext* c) {
     const SrbUniforms U = c->uniforms;
     const int nTiles = fp.tilesX * fp.tilesY;
     const int bandTiles = (fp.bandRow1 - fp.bandRow0) * fp.tilesX;
+    // A context that renders the whole frame is bound by its tile kernel, and the geometry of the next frame beside it
+    // should be lean (few, light CTAs) rather than quick; a band rank's tile kernel is shorter than its geometry chain,
+    // so there the chain's duration is the period and the quicker variants of the binning passes are used.
+    const bool fullFrame = fp.bandRow0 == 0 && fp.bandRow1 == fp.tilesY;
     int launches = 0;
     int stage = 0;
     const uint32_t prevRefs = c->fb[c->slot].hCnt->nRefs, prevBig = c->fb[c->slot].hCnt->nBig;   // last launched frame (heuristics only)
@@ -219,7 +223,7 @@ int launch_frame(SrbContext* c) {
         setup_kernel<<<c->nTBlocks, kGeomBlock, 0, gs>>>(
             c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
             c->dTileCount.p, B.dCnt);
-        bin_big_kernel<0><<<c->smCount * c->bigCountCtas, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
+        bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
         launches += 2;
     }
     mark(3);
@@ -241,7 +245,7 @@ int launch_frame(SrbContext* c) {
         // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
         // bins up to order, which no consumer depends on).  SRB_FILL_MERGE: 0 never, 1 (default) small frames, 2 always.
         static const int mergeMode = std::getenv("SRB_FILL_MERGE") ? std::atoi(std::getenv("SRB_FILL_MERGE")) : 1;
-        if (mergeMode != 0 && prevBig > 0 && (mergeMode == 2 || prevRefs <= 16384u)) {
+        if (mergeMode != 0 && prevBig > 0 && (mergeMode == 2 || prevRefs <= (fullFrame ? 16384u : wave * 256u))) {
             fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(c->dRefs.p, c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
                                                                B.dBins.p, wave);
         } else {
