@@ -231,7 +231,6 @@ def run_gpu(args):
                               sphereBounds=d.mesh.SphereBounds if d.frustum_cull else None)
     cmds = np.concatenate(win._draws)
     # draw records + the vertex/triangle block tables (8 B per 128-element block) are what end_frame uploads
-    n_geom_blocks = sum(-(-d.mesh.Vertices.shape[0] // 128) + -(-(d.mesh.Indices.size // 3) // 128) for d in scene.draws)
     win._draws = []
     win._clear_flags = 0
     clear = (C.c_float * 4)(*[float(x) for x in scene.clear_color])
@@ -517,7 +516,7 @@ def run_gpu(args):
                        if world > 1 else None,
                        "l2": "no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
                              if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush"},
-            "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES + 8 * n_geom_blocks),
+            "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES),
                     "d2h_bytes_per_step": int(W * H * 12), "steps": Ke,
                     "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke if fps_e else None,
                     "mpixels_per_sec": W * H * fps_e / 1e6 if fps_e else None,

@@ -86,7 +86,8 @@ struct SrbContext {
     bool useVis = false;
     int visMode = 0;
     DevBuf<DrawRec> dDraws;
-    DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels
+    DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels: (draw, first element) of every run of
+                                      // kGeomBlock vertices / triangles of a VISIBLE draw, compacted per frame by the frustum kernel
     int nVBlocks = 0, nTBlocks = 0;
     DevBuf<float4> dClip;
     DevBuf<TriRef> dRefs;
@@ -109,8 +110,7 @@ struct SrbContext {
     cudaEvent_t geomDone[2] = {}, rasterDone[2] = {}, inputsReady = nullptr;
     bool rasterRecorded[2] = {false, false}, inputsDirty = false;
     DrawRec* hDraws = nullptr;        // pinned staging
-    int2* hBlocks = nullptr;          // pinned staging: vertex blocks then triangle blocks
-    size_t hDrawsCap = 0, hBlocksCap = 0;
+    size_t hDrawsCap = 0;
     SrbStats stats;
     bool profiling = false;
     cudaEvent_t stageEv[SRB_N_STAGES + 1] = {};
@@ -182,6 +182,11 @@ int launch_frame(SrbContext* c) {
     int launches = 0;
     int stage = 0;
     const uint32_t prevRefs = c->fb[c->slot].hCnt->nRefs, prevBig = c->fb[c->slot].hCnt->nBig;   // last launched frame (heuristics only)
+    // Grids of the vertex and setup kernels: the live block counts of the last launched frame plus a margin (their
+    // stride loops cover whatever the frustum kernel of this frame really leaves alive); every block when unknown.
+    const uint32_t prevV = c->fb[c->slot].hCnt->nVLive, prevT = c->fb[c->slot].hCnt->nTLive;
+    const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, (int)(prevV + prevV / 8 + 16)) : c->nVBlocks);
+    const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, (int)(prevT + prevT / 8 + 16)) : c->nTBlocks);
     const int s = c->slot ^ 1;
     c->slot = s;
     SrbContext::FrameBufs& B = c->fb[s];
@@ -206,21 +211,21 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), gs));
     if (c->profiling) cudaEventRecord(c->stageEv[0], gs);
     if (fp.nDraws > 0) {
-        frustum_draws_kernel<<<(fp.nDraws + 127) / 128, 128, 0, gs>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
-                                                                                    fp.bandRow1, fp.tilesY);
+        frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
+                                                                                fp.bandRow1, fp.tilesY, c->dVBlocks.p, c->dTBlocks.p);
         ++launches;
     }
     mark(1);
     if (c->nVBlocks > 0) {
         if (U.numerics_fma)
-            vertex_kernel<true><<<c->nVBlocks, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, B.dWn.p);
+            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
         else
-            vertex_kernel<false><<<c->nVBlocks, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, c->dClip.p, B.dWn.p);
+            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
         ++launches;
     }
     mark(2);
     if (c->nTBlocks > 0) {
-        setup_kernel<<<c->nTBlocks, kGeomBlock, 0, gs>>>(
+        setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
             c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
             c->dTileCount.p, B.dCnt);
         bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
@@ -439,7 +444,6 @@ int srb_destroy(SrbContext* c) {
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
     if (c->hDraws) cudaFreeHost(c->hDraws);
-    if (c->hBlocks) cudaFreeHost(c->hBlocks);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     for (auto& e : c->stageEv) if (e) cudaEventDestroy(e);
@@ -775,16 +779,6 @@ int srb_end_frame(SrbContext* c) {
         nVB += ((size_t)m.nV + kGeomBlock - 1) / kGeomBlock;
         nTB += ((size_t)(m.nI / 3) + kGeomBlock - 1) / kGeomBlock;
     }
-    if (nVB + nTB + 1 > c->hBlocksCap) {
-        if (c->hBlocks) cudaFreeHost(c->hBlocks);
-        c->hBlocks = nullptr;
-        size_t cap = (nVB + nTB) + (nVB + nTB) / 2 + 64;
-        CK(c, cudaMallocHost((void**)&c->hBlocks, cap * sizeof(int2)));
-        c->hBlocksCap = cap;
-    }
-    int2* hV = c->hBlocks;
-    int2* hT = c->hBlocks + nVB;
-    size_t iv = 0, it = 0;
     int64_t totalV = 0, totalT = 0;
     bool eligible = (c->clearFlags & SRB_CLEAR_COLOR) && (c->clearFlags & SRB_CLEAR_DEPTH);
     int commonDepth = -1;
@@ -808,8 +802,6 @@ int srb_end_frame(SrbContext* c) {
         d.flags = q.flags; d.visible = 1; d._pad = 0;
         d.tblockSpheres = m.blockSpheres;
         for (int k = 0; k < 4; ++k) d.planes[k] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
-        for (int f = 0; f < m.nV; f += kGeomBlock) hV[iv++] = make_int2(i, f);
-        for (int f = 0; f < m.nI / 3; f += kGeomBlock) hT[it++] = make_int2(i, f);
         totalV += m.nV; totalT += m.nI / 3;
         // Visibility path eligibility: extreme-depth winner with
         // alpha provably 1, one depth function for the whole frame.
@@ -855,8 +847,6 @@ int srb_end_frame(SrbContext* c) {
     if (nDraws > 0) {
         CK(c, cudaMemcpyAsync(c->dDraws.p, c->hDraws, (size_t)nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, c->stream));
     }
-    if (nVB) CK(c, cudaMemcpyAsync(c->dVBlocks.p, hV, nVB * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
-    if (nTB) CK(c, cudaMemcpyAsync(c->dTBlocks.p, hT, nTB * sizeof(int2), cudaMemcpyHostToDevice, c->stream));
     c->nVBlocks = (int)nVB; c->nTBlocks = (int)nTB;
     FrameParams& fp = c->fp;
     fp.W = c->W; fp.H = c->H; fp.tilesX = c->tilesX; fp.tilesY = c->tilesY;

@@ -144,13 +144,16 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     const unsigned full = 0xffffffffu;
     __shared__ TileAgg agg;
     __shared__ uint32_t sNoCover;
-    const int2 blk = __ldg(tblocks + blockIdx.x);
+    // tblocks is the live table the frustum kernel of this frame compacted (visible draws only); stride loop and
+    // early first-entry load as in vertex_kernel.
+    int2 blk = tblocks[blockIdx.x];
+    const uint32_t nLive = cnt->nTLive;
+  for (uint32_t bi = blockIdx.x; bi < nLive; bi += gridDim.x, blk = tblocks[min(bi, nLive - 1)]) {
     const int di = blk.x;
     const DrawRec& d = draws[di];
-    if (!d.visible) return;                                   // uniform over the CTA
 #ifndef SRB_EXP_NO_BLOCKCULL
     if ((fp.bandRow0 > 0 || fp.bandRow1 < fp.tilesY) && block_outside(d, blk.y / kGeomBlock))
-        return;                                               // uniform too: the whole block is off band / off screen
+        continue;                                             // uniform over the CTA: the whole block is off band / off screen
 #endif
     agg_clear(agg);
     if (threadIdx.x == 0) sNoCover = 0u;
@@ -238,6 +241,8 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     __syncthreads();
     agg_flush<0>(agg, tileCount);
     if (threadIdx.x == 0 && sNoCover) atomicAdd(&cnt->nNoCover, sNoCover);
+    __syncthreads();                                          // the table and sNoCover are reused by the next block
+  }
 }
 
 // ---------------------------------------------------------------------------
