@@ -230,7 +230,7 @@ def run_gpu(args):
                               Shaders.StockFragmentShader(d.mesh.Texture), d.cull, d.depth, d.blend, submissionIndex=i,
                               sphereBounds=d.mesh.SphereBounds if d.frustum_cull else None)
     cmds = np.concatenate(win._draws)
-    # draw records + the vertex/triangle block tables (8 B per 128-element block) are what end_frame uploads
+    # the draw records are what end_frame uploads (the vertex/triangle block tables are built on the device)
     win._draws = []
     win._clear_flags = 0
     clear = (C.c_float * 4)(*[float(x) for x in scene.clear_color])

@@ -197,7 +197,7 @@ int launch_frame(SrbContext* c) {
         if (!c->profiling) return;
         for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], stage + 1 <= 5 ? gs : c->stream);
     };
-    if (c->inputsDirty) {             // draw table / block tables were uploaded on c->stream
+    if (c->inputsDirty) {             // the draw table was uploaded on c->stream
         CK(c, cudaEventRecord(c->inputsReady, c->stream));
         CK(c, cudaStreamWaitEvent(gs, c->inputsReady, 0));
         c->inputsDirty = false;
