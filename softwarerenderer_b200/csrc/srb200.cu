@@ -185,8 +185,11 @@ int launch_frame(SrbContext* c) {
     // Grids of the vertex and setup kernels: the live block counts of the last launched frame plus a margin (their
     // stride loops cover whatever the frustum kernel of this frame really leaves alive); every block when unknown.
     const uint32_t prevV = c->fb[c->slot].hCnt->nVLive, prevT = c->fb[c->slot].hCnt->nTLive;
-    const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, (int)(prevV + prevV / 8 + 16)) : c->nVBlocks);
-    const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, (int)(prevT + prevT / 8 + 16)) : c->nTBlocks);
+    // Never fewer than two full waves' worth of CTAs (when the scene has that many blocks): a frame with far more live
+    // blocks than the one before it (alternating passes, a camera cut) then still runs at full occupancy.
+    const int floorCtas = c->smCount * 16;
+    const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, std::max<int>(floorCtas, (int)(prevV + prevV / 8 + 16))) : c->nVBlocks);
+    const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, std::max<int>(floorCtas, (int)(prevT + prevT / 8 + 16))) : c->nTBlocks);
     const int s = c->slot ^ 1;
     c->slot = s;
     SrbContext::FrameBufs& B = c->fb[s];
