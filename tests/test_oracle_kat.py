@@ -523,3 +523,91 @@ def test_wireframe_tile_parallel_variant_is_bit_identical(oracle):
     c1, d1, _ = oracle.render_scene(sc, threads=3)
     assert np.array_equal(d0, d1) and np.array_equal(c0, c1)
     assert 0.005 < (d0 != CLEAR_DEPTH).mean() < 0.5
+
+
+# --------------------------------------------------------------------------
+# RenderMesh / DrawTriangle rejections (Rasterizer.cs:208-215, 378-380) and the interpolated WorldNormal
+# (InterpolateData, Rasterizer.cs:680-688)
+# --------------------------------------------------------------------------
+def _one_tri_scene(W, H, pos, proj, normal=None, color=None, cull=0):
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200.scene import DrawItem, Mesh, Scene
+    from softwarerenderer_b200.shaders import Material, Shaders
+    I = nm.identity()
+    v = Shaders.make_vertices(pos, normal=normal, color=color)
+    mesh = Mesh(v, np.array([0, 1, 2], np.uint16), Material())
+    return Scene(W, H, [DrawItem(mesh, I, I, proj, cull=cull)], clear_color=(0.0, 0.0, 0.0, 0.0), fog_start=1e6, fog_end=2e6)
+
+
+def test_triangle_entirely_behind_the_eye_is_rejected(oracle):
+    """All three clip w <= 0 -> the triangle is skipped before clipping (Rasterizer.cs:208-215).  With the reference's
+    perspective matrix w = -z_view, so a triangle at z = +2 (behind a camera looking down -Z) has w = -2 at every corner."""
+    from softwarerenderer_b200.scene import default_projection
+    W, H = 64, 48
+    sc = _one_tri_scene(W, H, [(-1, -1, 2.0), (1, -1, 2.0), (0, 1, 2.0)], default_projection(W, H))
+    c, d, st = _render(oracle, sc)
+    assert st.triangles_drawn == 0
+    assert not (d != CLEAR_DEPTH).any() and not c.any()
+    # the same triangle mirrored to z = -2 is in front of the eye and is drawn
+    sc = _one_tri_scene(W, H, [(-1, -1, -2.0), (1, -1, -2.0), (0, 1, -2.0)], default_projection(W, H))
+    _, d, st = _render(oracle, sc)
+    assert st.triangles_drawn == 1 and (d != CLEAR_DEPTH).any()
+
+
+@pytest.mark.parametrize("bad", [float("nan"), float("inf"), float("-inf")])
+def test_non_finite_ndc_rejects_the_triangle(oracle, bad):
+    """DrawTriangle returns when any NDC component is NaN or infinite (Rasterizer.cs:378-380)."""
+    from softwarerenderer_b200 import numerics as nm
+    W, H = 32, 32
+    sc = _one_tri_scene(W, H, [(-0.5, -0.5, 0.5), (0.5, -0.5, 0.5), (bad, 0.5, 0.5)], nm.identity())
+    c, d, st = _render(oracle, sc)
+    assert st.triangles_drawn == 0
+    assert not (d != CLEAR_DEPTH).any() and not c.any()
+
+
+def test_interpolated_world_normal_is_renormalised(oracle):
+    """InterpolateData normalises a Vector3 entry after the weighted sum when its squared length exceeds 1e-6
+    (Rasterizer.cs:680-688).  Affine triangle (w = 1): weights are the barycentrics.  Pixel (4,4) of the triangle
+    (0,0),(16,0),(0,16) has weights 0.5 / 0.25 / 0.25; normals (0,0,1),(0,0,1),(0,0,-1) sum to (0,0,0.5), which
+    becomes (0,0,1): diffuse 1.0, not 0.5."""
+    W = H = 32
+    col = (0.8, 0.6, 0.4, 1.0)
+
+    def scene(normals):
+        t = [(0, 0), (16, 0), (0, 16)]
+        pos = [(2.0 * x / W - 1.0, 1.0 - 2.0 * y / H, 0.5) for x, y in t]
+        from softwarerenderer_b200 import numerics as nm
+        sc = _one_tri_scene(W, H, pos, nm.identity(), normal=normals, color=[col] * 3)
+        sc.light_dir = np.array((0, 0, -1), np.float32)
+        return sc
+
+    c, d, _ = _render(oracle, scene([(0, 0, 1), (0, 0, 1), (0, 0, -1)]))
+    assert d[4, 4] != CLEAR_DEPTH
+    assert np.allclose(c[4, 4, :3], np.array(col[:3]) * (0.1 + 0.9 * 1.0), atol=1e-6)
+    # ... and where the sum points away from the light (weights 0.125/0.125/0.75 at (2,12)) the floor applies
+    assert np.allclose(c[12, 2, :3], np.array(col[:3]) * (0.1 + 0.9 * 0.25), atol=1e-6)
+
+
+def test_vanishing_world_normal_is_left_unnormalised(oracle):
+    """Below the 1e-6 squared-length threshold the vector is NOT normalised (Rasterizer.cs:680-688): at pixel (8,4)
+    the weights are 0.25 / 0.5 / 0.25 and normals (0,0,1),(0,0,-1),(0,0,1) cancel; the fragment gets the lighting
+    floor max(0.25, ~0) and no NaN."""
+    W = H = 32
+    col = (0.8, 0.6, 0.4, 1.0)
+    t = [(0, 0), (16, 0), (0, 16)]
+    pos = [(2.0 * x / W - 1.0, 1.0 - 2.0 * y / H, 0.5) for x, y in t]
+    from softwarerenderer_b200 import numerics as nm
+    sc = _one_tri_scene(W, H, pos, nm.identity(), normal=[(0, 0, 1), (0, 0, -1), (0, 0, 1)], color=[col] * 3)
+    sc.light_dir = np.array((0, 0, -1), np.float32)
+    c, d, _ = _render(oracle, sc)
+    assert d[4, 8] != CLEAR_DEPTH and np.isfinite(c).all()
+    assert np.allclose(c[4, 8, :3], np.array(col[:3]) * (0.1 + 0.9 * 0.25), atol=1e-6)
+
+
+def test_partial_last_tile_row_and_column_are_rasterised(oracle):
+    """Tile loops clamp to the bounding box, not to whole tiles (Rasterizer.cs:449-476): a target whose size is not a
+    multiple of TileSize = 16 (1080 rows leave 8) is covered to its last row and column."""
+    W, H = 40, 24                                     # 2.5 x 1.5 tiles
+    sc = screen_tri_scene(W, H, [[(-50, -50), (200, -50), (-50, 200)]], cull=0)
+    _, d, _ = _render(oracle, sc)
+    assert (d != CLEAR_DEPTH).all()
