@@ -122,3 +122,36 @@ def test_resize_between_frames(oracle):
             compare(win.ColorBuffer, win.DepthBuffer, oc, od)
     finally:
         win.Close()
+
+
+@pytest.mark.parametrize("pipeline", [1, 2])
+@pytest.mark.parametrize("normals", [[(0, 0, 1), (0, 0, 1), (0, 0, -1)], [(0, 0, 1), (0, 0, -1), (0, 0, 1)],
+                                     [(1, 0, 0), (-1, 0, 0), (0, 1e-4, 0)]])
+def test_cancelling_vertex_normals(oracle, pipeline, normals):
+    """InterpolateData's Vector3 branch (Rasterizer.cs:680-688): the interpolated WorldNormal is renormalised only
+    above a squared length of 1e-6; where the corner normals cancel the fragment keeps the short vector (lighting
+    floor, no NaN).  Same scenes as the known-answer tests in test_oracle_kat.py."""
+    from tests.test_oracle_kat import _one_tri_scene
+    from softwarerenderer_b200 import numerics as nm
+    W = H = 32
+    t = [(0, 0), (16, 0), (0, 16)]
+    pos = [(2.0 * x / W - 1.0, 1.0 - 2.0 * y / H, 0.5) for x, y in t]
+    sc = _one_tri_scene(W, H, pos, nm.identity(), normal=normals, color=[(0.8, 0.6, 0.4, 1.0)] * 3)
+    sc.light_dir = np.array((0, 0, -1), np.float32)
+    oc, od, _ = oracle.render_scene(sc, threads=2)
+    gc, gd, _ = _render_gpu(sc, pipeline)
+    assert np.isfinite(gc).all()
+    assert np.array_equal(gd, od)
+    compare(gc, gd, oc, od)
+
+
+@pytest.mark.parametrize("pipeline", [1, 2])
+def test_triangle_behind_the_eye_draws_nothing(oracle, pipeline):
+    """All three clip w <= 0 (Rasterizer.cs:208-215)."""
+    from tests.test_oracle_kat import _one_tri_scene
+    from softwarerenderer_b200.scene import default_projection
+    W, H = 64, 48
+    sc = _one_tri_scene(W, H, [(-1, -1, 2.0), (1, -1, 2.0), (0, 1, 2.0)], default_projection(W, H))
+    gc, gd, st = _render_gpu(sc, pipeline)
+    oc, od, _ = oracle.render_scene(sc, threads=2)
+    assert (gd == CLEAR_DEPTH).all() and np.array_equal(gd, od) and np.array_equal(gc, oc)
