@@ -148,12 +148,26 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     // early first-entry load as in vertex_kernel.
     int2 blk = tblocks[blockIdx.x];
     const uint32_t nLive = cnt->nTLive;
+#ifdef SRB_EXP_SETUP_PREFETCH
+    // Experiment (not measured yet, off by default): the next block's table entry is requested at the top of the
+    // current block and its three indices before the count pass, so that a CTA's second and later blocks start
+    // with two of the five dependent round trips already done.
+    int2 nblk;
+    int pi0 = -1, pi1 = 0, pi2 = 0;                           // prefetched indices of this thread's triangle (pi0 < 0: none)
+  for (uint32_t bi = blockIdx.x; bi < nLive; bi += gridDim.x, blk = nblk) {
+    nblk = tblocks[min(bi + gridDim.x, nLive - 1)];
+#else
   for (uint32_t bi = blockIdx.x; bi < nLive; bi += gridDim.x, blk = tblocks[min(bi, nLive - 1)]) {
+#endif
     const int di = blk.x;
     const DrawRec& d = draws[di];
 #ifndef SRB_EXP_NO_BLOCKCULL
     if ((fp.bandRow0 > 0 || fp.bandRow1 < fp.tilesY) && block_outside(d, blk.y / kGeomBlock))
+#ifdef SRB_EXP_SETUP_PREFETCH
+        { pi0 = -1; continue; }
+#else
         continue;                                             // uniform over the CTA: the whole block is off band / off screen
+#endif
 #endif
     agg_clear(agg);
     if (threadIdx.x == 0) sNoCover = 0u;
@@ -166,7 +180,13 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     out.seq[0] = out.seq[1] = 0; out.tx[0] = out.tx[1] = 0; out.ty[0] = out.ty[1] = 0;
     if (t < d.n_triangles) {
         const int g = d.tbase + t;
+#ifdef SRB_EXP_SETUP_PREFETCH
+        int i3[3];
+        if (pi0 >= 0) { i3[0] = pi0; i3[1] = pi1; i3[2] = pi2; }
+        else { i3[0] = (int)__ldg(d.idx + 3 * t); i3[1] = (int)__ldg(d.idx + 3 * t + 1); i3[2] = (int)__ldg(d.idx + 3 * t + 2); }
+#else
         int i3[3] = {(int)__ldg(d.idx + 3 * t), (int)__ldg(d.idx + 3 * t + 1), (int)__ldg(d.idx + 3 * t + 2)};
+#endif
         float4 c0 = clipIn[d.vbase + i3[0]], c1 = clipIn[d.vbase + i3[1]], c2 = clipIn[d.vbase + i3[2]];
         bool b0 = c0.w <= 0.0f, b1 = c1.w <= 0.0f, b2 = c2.w <= 0.0f;     // :208-210
         if (b0 && b1 && b2) {
@@ -232,6 +252,16 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
             }
         }
     }
+#ifdef SRB_EXP_SETUP_PREFETCH
+    pi0 = -1;
+    if (bi + gridDim.x < nLive) {
+        const DrawRec& nd = draws[nblk.x];
+        const int nt_ = nblk.y + (int)threadIdx.x;
+        if (nt_ < nd.n_triangles) {
+            pi0 = (int)__ldg(nd.idx + 3 * nt_); pi1 = (int)__ldg(nd.idx + 3 * nt_ + 1); pi2 = (int)__ldg(nd.idx + 3 * nt_ + 2);
+        }
+    }
+#endif
     // Count pass: small triangles through the aggregation table (large ones: bin_big_kernel<0>).
     for (int k = 0; k < out.n; ++k) {
         const int nt = tile_range_count(out.tx[k], out.ty[k]);
