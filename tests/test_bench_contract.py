@@ -52,3 +52,27 @@ def test_product_arm_refuses_to_run_without_a_device():
     assert r.returncode != 0
     assert "no CUDA device" in (r.stderr + r.stdout)
     assert not [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+
+
+def test_committed_bench_line_carries_every_contract_key():
+    """The newest committed N=1 line under profiles/ (written by `python bench.py` on a B200) has every key the
+    bench contract names; guards against a bench.py edit that silently drops one."""
+    import glob
+    paths = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_bench_city4k.json")))
+    assert paths
+    d = json.loads(open(paths[-1]).read().strip().splitlines()[-1])
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
+        assert k in d, k
+    assert d["n_gpus"] == 1 and d["warmup"] >= 3 and d["config"]["workload"] == "city4k"
+    assert abs(d["value"] * d["ms_per_step"] / 1000.0 - 1.0) < 1e-6
+    r = d["roofline"]
+    assert r["bound"] in ("hbm", "tensor") and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    assert r["traffic"] is None or r["traffic"] > 0
+    e = d["e2e"]
+    assert e["value"] > 0 and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0 and e["value"] < d["value"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] in ("port", "reference") and cb["cores"] >= 1 and cb["value"] > 0 and cb["sample"]
+    c = d["clocks"]
+    assert not set(c["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    assert d["gpu_launches"] >= d["steps"]
