@@ -5,11 +5,15 @@
   python bench.py --impl reference ...      # the CPU path (oracle port) on the host cores
 
 A step = one frame of the workload.  `value` = frames/s with the draw list and
-all meshes/textures resident in HBM (srb_replay_frame); `e2e` = the same frame
-through the public API with host buffers: begin_frame + submit_draws (host
-matrices -> pinned -> H2D) + end_frame + read_color (D2H, float4) every step.
-N>1: sort-first bands on 16-row tile boundaries, one rank per GPU, NCCL
-send/recv gather of the bands into rank 0's framebuffer inside the timed region.
+all meshes/textures resident in HBM (srb_replay_frame, frames pipelined); `e2e`
+= the same frame through the public API with host buffers, every step:
+srb_begin_frame + srb_submit_draws (host draw records -> pinned -> H2D) +
+srb_end_frame + srb_present_rgb_async (the packed RGB float frame
+MainWindow.OnRender uploads, D2H on the copy stream while the next frame
+renders).  N>1: sort-first bands on 16-row tile boundaries, one rank per GPU;
+the bands reach rank 0's frame as peer stores over NVLink from inside the tile
+kernel (`--gather nccl`: grouped NCCL send/recv instead); for `e2e` every rank
+delivers its own rows to one shared pinned host frame over its own PCIe link.
 """
 import argparse
 import ctypes as C
@@ -85,6 +89,16 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def base_config(workload, scene):
+    """The workload description both arms print (identical dictionaries: the driver compares them); everything
+    that only the GPU arm knows goes under `config_detail`."""
+    W, H = scene.width, scene.height
+    l2 = ("no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
+          if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush")
+    return {"workload": workload, "scene": WORKLOADS[workload]["desc"], "width": W, "height": H,
+            "triangles": scene.triangle_count, "draws": len(scene.draws), "l2": l2}
+
+
 def algorithmic_bytes(scene, visible, p_cov):
     """compulsory bytes per frame."""
     geo, texs = 0, {}
@@ -122,26 +136,27 @@ def run_reference(args):
 
     budget = float(os.environ.get("SRB_REF_BUDGET_S", "150"))
     t_start = time.perf_counter()
-    for _ in range(min(args.warmup, 1)):
+    # Warm-up frames as asked (the driver compares both arms' counts), within a quarter of the time budget.
+    warm = 0
+    while warm < args.warmup and (warm == 0 or time.perf_counter() - t_start < budget / 4):
         frame()
+        warm += 1
     t0 = time.perf_counter()
-    one = t0 - t_start if args.warmup else None
     steps = 0
     while steps < args.steps:
         frame()
         steps += 1
-        if time.perf_counter() - t_start > budget:
+        if time.perf_counter() - t_start > budget and steps >= 1:
             break
     dt = time.perf_counter() - t0
     fps = steps / dt
     W, H = scene.width, scene.height
     line = {
         "impl": "reference", "metric": "frames_per_sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
-        "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": 1000.0 * dt / steps,
+        "steps": steps, "warmup": warm, "ms_per_step": 1000.0 * dt / steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "mpixels_per_sec": W * H * fps / 1e6,
-        "config": {"workload": args.workload, "scene": WORKLOADS[args.workload]["desc"], "width": W, "height": H,
-                   "triangles": scene.triangle_count, "draws": len(scene.draws)},
+        "config": base_config(args.workload, scene),
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
                          "sample": f"{steps} full frame(s) of the workload (requested {args.steps}; bounded to ~{budget:.0f}s); "
                                    "C++ restatement of the C# path, tile-row-parallel; the C# reference cannot run here (no .NET)"},
@@ -157,7 +172,7 @@ class _DevArray:
 
 
 STAGES = ["frustum", "vertex", "setup_count", "scan", "fill", "sort", "tile_raster"]
-DRAW_REC_BYTES = 352
+DRAW_REC_BYTES = 368
 
 
 def run_gpu(args):
@@ -503,19 +518,17 @@ def run_gpu(args):
             "ms_per_step": frame_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "mpixels_per_sec": W * H * fps / 1e6,
-            "config": {"workload": args.workload, "scene": WORKLOADS[args.workload]["desc"], "width": W, "height": H,
-                       "triangles": scene.triangle_count, "draws": len(scene.draws),
-                       "draws_visible": int(sum(visible)), "triangles_setup": int(st.triangles_setup),
-                       "tile_pairs": int(st.tile_pairs), "pipeline": "visibility" if st.pipeline_used == 2 else "ordered",
-                       "parallelism": f"bands{world}" if world > 1 else "single",
-                       "bands": {"cuts_tile_rows": [int(x) for x in cuts], "policy": args.bands,
-                                 "gather": (("RGBA8 (4 B/pixel) " if rgba8_gather else "float4 (16 B/pixel) ") +
-                                            "peer stores from the tile kernel into rank 0's frame over NVLink + 4-byte "
-                                            "NCCL all-reduce as frame barrier") if fused else "NCCL grouped send/recv of float4 bands",
-                                 "gather_format": args.gather_format if fused else "float4", "gather_verified": gather_verified}
-                       if world > 1 else None,
-                       "l2": "no explicit flush: per-frame working set (framebuffer %.0f MB + geometry/records) exceeds the 126 MB L2" % (20 * W * H / 1e6)
-                             if 20 * W * H > 126e6 else "working set fits L2 (launch-latency-bound config); no flush"},
+            "config": base_config(args.workload, scene),
+            "config_detail": {"draws_visible": int(sum(visible)), "triangles_setup": int(st.triangles_setup),
+                              "triangles_direct": int(st.triangles_direct), "triangles_no_coverage": int(st.triangles_no_coverage),
+                              "tile_pairs": int(st.tile_pairs), "pipeline": "visibility" if st.pipeline_used == 2 else "ordered",
+                              "parallelism": f"bands{world}" if world > 1 else "single",
+                              "bands": {"cuts_tile_rows": [int(x) for x in cuts], "policy": args.bands,
+                                        "gather": (("RGBA8 (4 B/pixel) " if rgba8_gather else "float4 (16 B/pixel) ") +
+                                                   "peer stores from the tile kernel into rank 0's frame over NVLink + 4-byte "
+                                                   "NCCL all-reduce as frame barrier") if fused else "NCCL grouped send/recv of float4 bands",
+                                        "gather_format": args.gather_format if fused else "float4", "gather_verified": gather_verified}
+                              if world > 1 else None},
             "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES),
                     "d2h_bytes_per_step": int(W * H * 12), "steps": Ke,
                     "ms_per_step": 1000.0 * max(wall_e, ms_e / 1000.0) / Ke if fps_e else None,

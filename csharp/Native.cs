@@ -43,7 +43,7 @@ namespace SoftwareRenderer
         public long DrawsSubmitted, DrawsVisible, TrianglesSubmitted, TrianglesSetup, TilePairs, ClippedTriangles;
         public int PipelineUsed, KernelLaunches;
         public float GpuMs;
-        public int TrianglesNoCoverage;
+        public int TrianglesNoCoverage, TrianglesDirect, Pad;
     }
 
     public static unsafe class Srb

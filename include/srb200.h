@@ -99,7 +99,7 @@ typedef struct SrbStats {
     int64_t draws_submitted;
     int64_t draws_visible;        /* after the device frustum test */
     int64_t triangles_submitted;
-    int64_t triangles_setup;      /* survived behind/NaN/area/cull/bbox(/band) and may cover a pixel */
+    int64_t triangles_setup;      /* survived behind/NaN/area/cull/bbox(/band) and may cover a pixel (binned + direct) */
     int64_t tile_pairs;           /* (triangle, tile) bin entries */
     int64_t clipped_triangles;    /* went through the near-plane clipper */
     int32_t pipeline_used;        /* SRB_PIPELINE_ORDERED or SRB_PIPELINE_VISIBILITY */
@@ -107,6 +107,9 @@ typedef struct SrbStats {
     float   gpu_ms;               /* device time of the last end_frame (CUDA events) */
     int32_t triangles_no_coverage;/* accepted by the reference's setup, but at most 4x4 px and proven to pass its
                                      coverage test nowhere: not binned (triangles_setup + this = the reference's count) */
+    int32_t triangles_direct;     /* of triangles_setup: at most 4x4 px, unclipped, rasterized by the setup kernel itself
+                                     into the per-pixel winner keys (visibility pipeline; no record, no bin entry) */
+    int32_t _pad;
 } SrbStats;
 
 /* ---- context / framebuffer: MainWindow buffers (MainWindow.cs:23-31, 298-361) ---- */

@@ -52,6 +52,8 @@ class SrbStats(C.Structure):
         ("kernel_launches", C.c_int32),
         ("gpu_ms", C.c_float),
         ("triangles_no_coverage", C.c_int32),
+        ("triangles_direct", C.c_int32),
+        ("_pad", C.c_int32),
     ]
 
 

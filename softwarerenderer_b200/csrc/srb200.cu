@@ -62,8 +62,8 @@ struct SrbContext {
     // frame k (copy stream) overlaps the rendering of frame k+1 (pipeline stream)
     cudaStream_t copyStream = nullptr;
     DevBuf<float> dPresent[2];
-    int bigCountCtas = std::getenv("SRB_BIGCOUNT_CTAS") ? std::atoi(std::getenv("SRB_BIGCOUNT_CTAS")) : 1;   // CTAs per SM of the large-triangle count pass
-    int fillCtas = std::getenv("SRB_FILL_CTAS") ? std::atoi(std::getenv("SRB_FILL_CTAS")) : 4;                 // CTAs per SM and role of the fill pass
+    static constexpr int bigCountCtas = 1;   // CTAs per SM of the large-triangle count pass (measured: 1 / 2 / 4)
+    static constexpr int fillCtas = 4;       // CTAs per SM and role of the fill pass
     // (The count pass waits on atomic round trips, not on issue slots: with 4 CTAs per SM it is a few us shorter alone
     // -- 45.5 vs 50 us for setup+count -- but holds four times the registers while the previous frame's tile kernel
     // wants them; pipelined, city4k gains about 1 % with 1.)
@@ -89,7 +89,7 @@ struct SrbContext {
     DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels: (draw, first element) of every run of
                                       // kGeomBlock vertices / triangles of a VISIBLE draw, compacted per frame by the frustum kernel
     int nVBlocks = 0, nTBlocks = 0;
-    DevBuf<float4> dClip;
+    DevBuf<int32_t> dTri2Draw;        // draw of every 64th global triangle (frustum kernel -> resolve of direct winners)
     DevBuf<TriRef> dRefs;
     DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
     DevBuf<uint32_t> dTileCount, dBinScratch;
@@ -98,6 +98,8 @@ struct SrbContext {
     // exists twice; frames alternate between the two sets.
     struct FrameBufs {
         DevBuf<float4> dWn;               // world normals (vertex stage -> shading)
+        DevBuf<float4> dClip;             // clip positions (vertex stage -> setup; resolve of direct winners)
+        DevBuf<unsigned long long> dGKeys;    // winner keys of the direct path, 256 per tile; all zero between frames
         DevBuf<float4> dRecsR, dRecsS;    // split setup records (RecStore)
         DevBuf<ClipAttr> dClipAttrs;
         DevBuf<uint32_t> dTileStart, dTileCursor, dBins;
@@ -211,32 +213,36 @@ int launch_frame(SrbContext* c) {
     c->lastGeomStream = gs;
     CK(c, cudaEventRecord(c->ev0, gs));
     CK(c, cudaMemsetAsync(B.dCnt, 0, sizeof(Counters), gs));
-    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), gs));
+    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, 2 * (size_t)nTiles * sizeof(uint32_t), gs));      // counts + dirty flags
+    uint32_t* const tileDirty = c->dTileCount.p + nTiles;
+    fp.directSmall = c->useVis ? 1 : 0;
+    fp.visMode = c->visMode;
     if (c->profiling) cudaEventRecord(c->stageEv[0], gs);
     if (fp.nDraws > 0) {
         frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
-                                                                                fp.bandRow1, fp.tilesY, c->dVBlocks.p, c->dTBlocks.p);
+                                                                                fp.bandRow1, fp.tilesY, c->dVBlocks.p, c->dTBlocks.p,
+                                                                                c->dTri2Draw.p);
         ++launches;
     }
     mark(1);
     if (c->nVBlocks > 0) {
         if (U.numerics_fma)
-            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
+            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
         else
-            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
+            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
         ++launches;
     }
     mark(2);
     if (c->nTBlocks > 0) {
         setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
-            c->dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
-            c->dTileCount.p, B.dCnt);
+            c->dDraws.p, c->dTBlocks.p, fp, U, B.dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
+            c->dTileCount.p, B.dCnt, B.dGKeys.p, tileDirty);
         bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
         launches += 2;
     }
     mark(3);
     if (bandTiles > 0) {
-        scan_tiles_kernel<<<kScanCtas, 1024, 0, gs>>>(c->dTileCount.p, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p,
+        scan_tiles_kernel<<<kScanCtas, 1024, 0, gs>>>(c->dTileCount.p, tileDirty, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p,
                                                      fp.bandRow0 * fp.tilesX, bandTiles, B.dCnt, fp.pairCap);
         ++launches;
     }
@@ -251,9 +257,8 @@ int launch_frame(SrbContext* c) {
         // registers x 256 threads), and beside the previous frame's tile kernel a large frame does better with the two
         // lean launches although they take 4 us longer alone (city4k: 5,690 against 5,590 frames/s).
         // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
-        // bins up to order, which no consumer depends on).  SRB_FILL_MERGE: 0 never, 1 (default) small frames, 2 always.
-        static const int mergeMode = std::getenv("SRB_FILL_MERGE") ? std::atoi(std::getenv("SRB_FILL_MERGE")) : 1;
-        if (mergeMode != 0 && prevBig > 0 && (mergeMode == 2 || prevRefs <= (fullFrame ? 16384u : wave * 256u))) {
+        // bins up to order, which no consumer depends on).
+        if (prevBig > 0 && prevRefs <= (fullFrame ? 16384u : wave * 256u)) {
             fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(c->dRefs.p, c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
                                                                B.dBins.p, wave);
         } else {
@@ -268,6 +273,7 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaStreamWaitEvent(c->stream, c->geomDone[s], 0));
     RasterArgs A;
     A.draws = c->dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
+    A.clip = B.dClip.p; A.tri2draw = c->dTri2Draw.p; A.gkeys = B.dGKeys.p;
     A.clipAttrs = B.dClipAttrs.p; A.tileStart = B.dTileStart.p; A.tileEnd = B.dTileCursor.p;
     A.bins = B.dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = B.dCnt;
     A.colorOut = c->colorTarget ? c->colorTarget : c->color;
@@ -318,8 +324,11 @@ int complete_frame(SrbContext* c) {
     for (int attempt = 0; attempt < 8; ++attempt) {
         const Counters& k = *c->fb[c->slot].hCnt;
         if (!k.overflow) break;
-        if (c->fp.loadColor || c->fp.loadDepth)
-            return fail(c, SRB_ERR_STATE, "bin overflow on a frame that preserves the framebuffer; cannot re-run");
+        // Every overflow flag is raised by the setup or scan kernel, and every raster kernel returns at once when
+        // one is set: the framebuffer is untouched, so the frame can be run again -- also one that does not clear.
+        // What the aborted frame did leave behind are direct-path keys in its set's global key buffer.
+        if (c->useVis && c->fb[c->slot].dGKeys.p)
+            CK(c, cudaMemsetAsync(c->fb[c->slot].dGKeys.p, 0, (size_t)c->tilesX * c->tilesY * kTile * kTile * sizeof(unsigned long long), c->stream));
         if (k.overflow & 1u) {
             size_t want = (size_t)k.nPairs + k.nPairs / 8 + 1024;
             for (auto& b : c->fb) CK(c, b.dBins.reserve(want));
@@ -343,7 +352,8 @@ int complete_frame(SrbContext* c) {
     c->framePending = false;
     const Counters& k = *c->fb[c->slot].hCnt;
     c->stats.draws_visible = k.nVisibleDraws;
-    c->stats.triangles_setup = k.nRefs;
+    c->stats.triangles_setup = (int64_t)k.nRefs + k.nDirect;
+    c->stats.triangles_direct = k.nDirect;
     c->stats.triangles_no_coverage = (int32_t)k.nNoCover;
     c->stats.tile_pairs = k.nPairs;
     c->stats.clipped_triangles = k.nClippedTris;
@@ -423,11 +433,11 @@ int srb_destroy(SrbContext* c) {
     if (c->color8) cudaFree(c->color8);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
-    c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dClip.release();
+    c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dTri2Draw.release();
     c->dRayScratch.release();
     c->dRefs.release(); c->dBigQ.release(); c->dTileCount.release(); c->dBinScratch.release();
     for (auto& b : c->fb) {
-        b.dWn.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
+        b.dWn.release(); b.dClip.release(); b.dGKeys.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
         b.dTileCursor.release(); b.dBins.release(); b.dOrder.release();
         if (b.dCnt) cudaFree(b.dCnt);
         if (b.hCnt) cudaFreeHost(b.hCnt);
@@ -813,7 +823,7 @@ int srb_end_frame(SrbContext* c) {
         if (q.blend != SRB_BLEND_ALPHA && q.blend != SRB_BLEND_NONE) eligible = false;
         if (!m.opaque || !texOpaque) eligible = false;
     }
-    if (totalV > 0x3fffffff || totalT > 0x3fffffff) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
+    if (totalV > 0x3ffffff0 || totalT > 0x3ffffff0) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
     if (c->colorTarget && !(c->clearFlags & SRB_CLEAR_COLOR))
         return fail(c, SRB_ERR_STATE, "a remote colour target needs frames that clear colour");
     if (c->uniforms.debug_mode == SRB_DEBUG_WIREFRAME) eligible = false;   // DrawLine: depth 1/d, W != 0 writes -- ordered replay only
@@ -833,9 +843,14 @@ int srb_end_frame(SrbContext* c) {
     CK(c, c->dVBlocks.reserve(nVB + 1));
     CK(c, c->dTBlocks.reserve(nTB + 1));
     for (auto& b : c->fb) CK(c, b.dOrder.reserve(nTiles));
-    CK(c, c->dClip.reserve((size_t)totalV + 1));
+    CK(c, c->dTri2Draw.reserve(((size_t)totalT >> kTri2DrawShift) + 2));
     for (auto& b : c->fb) {
         CK(c, b.dWn.reserve((size_t)totalV + 1));
+        CK(c, b.dClip.reserve((size_t)totalV + 1));
+        if (c->useVis && b.dGKeys.cap < (size_t)nTiles * kTile * kTile) {
+            CK(c, b.dGKeys.reserve((size_t)nTiles * kTile * kTile));
+            CK(c, cudaMemsetAsync(b.dGKeys.p, 0, b.dGKeys.cap * sizeof(unsigned long long), c->stream));
+        }
         CK(c, b.dRecsR.reserve(3 * (2 * (size_t)totalT + 2)));
         CK(c, b.dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
         CK(c, b.dClipAttrs.reserve(4096));
@@ -845,7 +860,7 @@ int srb_end_frame(SrbContext* c) {
     }
     CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
     CK(c, c->dBigQ.reserve(1u << 16));
-    CK(c, c->dTileCount.reserve(nTiles));
+    CK(c, c->dTileCount.reserve(2 * (size_t)nTiles));
     CK(c, c->dBinScratch.reserve(std::max(c->fb[0].dBins.cap, c->fb[1].dBins.cap)));
     if (nDraws > 0) {
         CK(c, cudaMemcpyAsync(c->dDraws.p, c->hDraws, (size_t)nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, c->stream));

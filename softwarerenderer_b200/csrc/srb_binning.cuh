@@ -140,53 +140,35 @@ __global__ void __launch_bounds__(kGeomBlock, 8)
 setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks, FrameParams fp,
              SrbUniforms U, const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
              RecStore recs, ClipAttr* __restrict__ clipAttrs, TriRef* __restrict__ refs, BigEntry* __restrict__ bigQ,
-             uint32_t* __restrict__ tileCount, Counters* cnt) {
+             uint32_t* __restrict__ tileCount, Counters* cnt, unsigned long long* __restrict__ gkeys,
+             uint32_t* __restrict__ tileDirty) {
     const unsigned full = 0xffffffffu;
     __shared__ TileAgg agg;
-    __shared__ uint32_t sNoCover;
+    __shared__ uint32_t sNoCover, sDirect;
     // tblocks is the live table the frustum kernel of this frame compacted (visible draws only); stride loop and
     // early first-entry load as in vertex_kernel.
     int2 blk = tblocks[blockIdx.x];
     const uint32_t nLive = cnt->nTLive;
-#ifdef SRB_EXP_SETUP_PREFETCH
-    // Experiment (not measured yet, off by default): the next block's table entry is requested at the top of the
-    // current block and its three indices before the count pass, so that a CTA's second and later blocks start
-    // with two of the five dependent round trips already done.
-    int2 nblk;
-    int pi0 = -1, pi1 = 0, pi2 = 0;                           // prefetched indices of this thread's triangle (pi0 < 0: none)
-  for (uint32_t bi = blockIdx.x; bi < nLive; bi += gridDim.x, blk = nblk) {
-    nblk = tblocks[min(bi + gridDim.x, nLive - 1)];
-#else
   for (uint32_t bi = blockIdx.x; bi < nLive; bi += gridDim.x, blk = tblocks[min(bi, nLive - 1)]) {
-#endif
     const int di = blk.x;
     const DrawRec& d = draws[di];
 #ifndef SRB_EXP_NO_BLOCKCULL
     if ((fp.bandRow0 > 0 || fp.bandRow1 < fp.tilesY) && block_outside(d, blk.y / kGeomBlock))
-#ifdef SRB_EXP_SETUP_PREFETCH
-        { pi0 = -1; continue; }
-#else
         continue;                                             // uniform over the CTA: the whole block is off band / off screen
 #endif
-#endif
     agg_clear(agg);
-    if (threadIdx.x == 0) sNoCover = 0u;
+    if (threadIdx.x == 0) { sNoCover = 0u; sDirect = 0u; }
     __syncthreads();
     const int t = blk.y + threadIdx.x;
     SetupOut out;
     out.n = 0;
     out.nNoCover = 0;
+    out.nDirect = 0;
     out.bigMask = 0u;
     out.seq[0] = out.seq[1] = 0; out.tx[0] = out.tx[1] = 0; out.ty[0] = out.ty[1] = 0;
     if (t < d.n_triangles) {
         const int g = d.tbase + t;
-#ifdef SRB_EXP_SETUP_PREFETCH
-        int i3[3];
-        if (pi0 >= 0) { i3[0] = pi0; i3[1] = pi1; i3[2] = pi2; }
-        else { i3[0] = (int)__ldg(d.idx + 3 * t); i3[1] = (int)__ldg(d.idx + 3 * t + 1); i3[2] = (int)__ldg(d.idx + 3 * t + 2); }
-#else
         int i3[3] = {(int)__ldg(d.idx + 3 * t), (int)__ldg(d.idx + 3 * t + 1), (int)__ldg(d.idx + 3 * t + 2)};
-#endif
         float4 c0 = clipIn[d.vbase + i3[0]], c1 = clipIn[d.vbase + i3[1]], c2 = clipIn[d.vbase + i3[2]];
         bool b0 = c0.w <= 0.0f, b1 = c1.w <= 0.0f, b2 = c2.w <= 0.0f;     // :208-210
         if (b0 && b1 && b2) {
@@ -199,7 +181,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
             int minX, maxX, minY, maxY;
             if (setup_tri(c, fp.W, fp.H, d.cull, r, minX, maxX, minY, maxY)) {
                 r.meta = (uint32_t)di;
-                accept_tri(r, 2u * (uint32_t)g, minX, maxX, minY, maxY, fp, recs, out);
+                accept_tri(r, 2u * (uint32_t)g, minX, maxX, minY, maxY, fp, recs, out, gkeys, tileDirty, true);
             }
         }
     }
@@ -214,22 +196,24 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     for (int k = 0; k < out.n; ++k)
         if (out.bigMask >> k & 1u) nb += big_parts(out.tx[k], out.ty[k]);
     const int n = out.n;
-    uint32_t incl = (uint32_t)n | ((uint32_t)nb << 16);
+    // list entries in the low word, queue entries in the high word -- the layout of the counter pair itself, so that
+    // no count can carry into the other (a triangle of a 65535-px target can take thousands of queue entries)
+    const unsigned long long mine = (unsigned long long)(uint32_t)n | ((unsigned long long)(uint32_t)nb << 32);
+    unsigned long long incl = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(full, incl, o);
+        const unsigned long long v = __shfl_up_sync(full, incl, o);
         if (lane >= o) incl += v;
     }
     if (out.nNoCover) atomicAdd(&sNoCover, (uint32_t)out.nNoCover);      // statistics; flushed once per CTA below
-    const uint32_t tot = __shfl_sync(full, incl, 31);
+    if (out.nDirect) atomicAdd(&sDirect, (uint32_t)out.nDirect);
+    const unsigned long long tot = __shfl_sync(full, incl, 31);
     if (tot) {                                                // uniform over the warp
         unsigned long long base = 0ull;
-        if (lane == 31)
-            base = atomicAdd(reinterpret_cast<unsigned long long*>(&cnt->nRefs),
-                             (unsigned long long)(tot & 0xffffu) | ((unsigned long long)(tot >> 16) << 32));
+        if (lane == 31) base = atomicAdd(reinterpret_cast<unsigned long long*>(&cnt->nRefs), tot);
         base = __shfl_sync(full, base, 31);
-        const uint32_t excl = incl - ((uint32_t)n | ((uint32_t)nb << 16));
-        uint32_t ri = (uint32_t)base + (excl & 0xffffu), bi = (uint32_t)(base >> 32) + (excl >> 16);
+        const unsigned long long excl = incl - mine;
+        uint32_t ri = (uint32_t)base + (uint32_t)excl, bi = (uint32_t)(base >> 32) + (uint32_t)(excl >> 32);
         for (int k = 0; k < n; ++k, ++ri) {
             TriRef rf;
             rf.seq = out.seq[k]; rf.tx = out.tx[k]; rf.ty = out.ty[k]; rf._pad = 0;
@@ -252,16 +236,6 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
             }
         }
     }
-#ifdef SRB_EXP_SETUP_PREFETCH
-    pi0 = -1;
-    if (bi + gridDim.x < nLive) {
-        const DrawRec& nd = draws[nblk.x];
-        const int nt_ = nblk.y + (int)threadIdx.x;
-        if (nt_ < nd.n_triangles) {
-            pi0 = (int)__ldg(nd.idx + 3 * nt_); pi1 = (int)__ldg(nd.idx + 3 * nt_ + 1); pi2 = (int)__ldg(nd.idx + 3 * nt_ + 2);
-        }
-    }
-#endif
     // Count pass: small triangles through the aggregation table (large ones: bin_big_kernel<0>).
     for (int k = 0; k < out.n; ++k) {
         const int nt = tile_range_count(out.tx[k], out.ty[k]);
@@ -271,6 +245,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     __syncthreads();
     agg_flush<0>(agg, tileCount);
     if (threadIdx.x == 0 && sNoCover) atomicAdd(&cnt->nNoCover, sNoCover);
+    if (threadIdx.x == 0 && sDirect) atomicAdd(&cnt->nDirect, sDirect);
     __syncthreads();                                          // the table and sNoCover are reused by the next block
   }
 }
@@ -301,9 +276,9 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 constexpr int kScanCtas = 8;
 
 __global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
-scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
-                  uint32_t* __restrict__ tileCursor, uint4* __restrict__ order, int tile0, int nTiles,
-                  Counters* cnt, uint32_t pairCap) {
+scan_tiles_kernel(const uint32_t* __restrict__ tileCount, const uint32_t* __restrict__ tileDirty,
+                  uint32_t* __restrict__ tileStart, uint32_t* __restrict__ tileCursor, uint4* __restrict__ order,
+                  int tile0, int nTiles, Counters* cnt, uint32_t pairCap) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     __shared__ uint32_t wsum[3][32];
@@ -390,7 +365,8 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
                 if (hv) pos = oh + __popc(mh & lt);
                 else if (md) pos = th + om + __popc(mm & lt);
                 else pos = th + tm + orest + __popc(mv & ~mh & ~mm & lt);
-                order[pos] = make_uint4((uint32_t)i, excl, excl + c[k], 0u);      // tile, bin start, bin end
+                // tile, bin start, bin end, "the setup kernel rasterized small triangles straight into this tile's keys"
+                order[pos] = make_uint4((uint32_t)i, excl, excl + c[k], __ldg(tileDirty + i));
             }
             run += __shfl_sync(full, incl, 31);
             oh += __popc(mh); om += __popc(mm); orest += __popc(mv & ~mh & ~mm);

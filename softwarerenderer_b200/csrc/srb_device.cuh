@@ -37,10 +37,13 @@ struct DrawRec {
     int32_t visible;          // written by the frustum kernel
     int32_t _pad;
     const float4* tblockSpheres;  // object-space bounding sphere of every run of kGeomBlock triangles (mesh upload)
-    float4 planes[4];         // written by the frustum kernel: object-space half-spaces left/right/top/bottom of the
-                              // screen (top/bottom: of this context's band), nx,ny,nz,d normalised; inside: n.p + d >= 0
+    float4 planes[5];         // written by the frustum kernel: object-space half-spaces left/right/top/bottom of the
+                              // screen (top/bottom: of this context's band), nx,ny,nz,d normalised; inside: n.p + d >= 0.
+                              // planes[4] is the half-space clip w > 0: the four screen planes describe where a vertex
+                              // lands on screen only for w > 0 (for w < 0 the NDC position flips sides), so a block is
+                              // culled only when its sphere also lies entirely inside this one.
 };
-static_assert(sizeof(DrawRec) == 352, "DrawRec layout");
+static_assert(sizeof(DrawRec) == 368, "DrawRec layout");
 
 // ---- triangle setup record, slot = 2*global_triangle + fan ----
 // s = screen coords of outputs {v2,v1,v0} (Rasterizer.cs:367,383-386),
@@ -193,6 +196,38 @@ __device__ __forceinline__ uint32_t f2ord(float f) {
 __device__ __forceinline__ float ord2f(uint32_t o) {
     uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
     return __uint_as_float(u);
+}
+
+// ---- per-pixel winner keys of the visibility path ----
+// MODE: 0 LessEqual (max depth, later wins ties), 1 Less (max, earlier wins),
+//       2 GreaterEqual (min, later wins), 3 Greater (min, earlier wins).
+// Low word: 2*seq + direct, ordered like seq.  `direct` marks a triangle that was rasterized by the setup kernel
+// straight into the global key buffer and has no setup record (the resolve step rebuilds it from the mesh).
+// A valid key is never 0: 0 is the "nothing here" value of the global key buffer in every mode.
+__device__ __forceinline__ unsigned long long make_key_rt(int mode, float depth, uint32_t seq, uint32_t direct) {
+    uint32_t hi = f2ord(depth);
+    if (mode >= 2) hi = ~hi;
+    const uint32_t ord = 2u * seq + direct;
+    const uint32_t lo = (mode & 1) ? (0xfffffffeu - ord) : (ord + 1u);
+    return ((unsigned long long)hi << 32) | lo;
+}
+__device__ __forceinline__ unsigned long long clear_key_rt(int mode) {
+    uint32_t hi = f2ord(kClearDepth);
+    if (mode >= 2) hi = ~hi;
+    const uint32_t lo = (mode & 1) ? 0xffffffffu : 0u;
+    return ((unsigned long long)hi << 32) | lo;
+}
+template <int MODE>
+__device__ __forceinline__ unsigned long long make_key(float depth, uint32_t seq, uint32_t direct = 0u) {
+    return make_key_rt(MODE, depth, seq, direct);
+}
+template <int MODE>
+__device__ __forceinline__ unsigned long long clear_key() { return clear_key_rt(MODE); }
+// seq and the direct flag of a winner key.
+template <int MODE>
+__device__ __forceinline__ uint32_t key_ord(unsigned long long key) {
+    const uint32_t lo = (uint32_t)key;
+    return (MODE & 1) ? (0xfffffffeu - lo) : (lo - 1u);
 }
 
 // GetDepthTestFunction (Rasterizer.cs:542-559), flipped compares included.

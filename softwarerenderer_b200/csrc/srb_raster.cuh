@@ -191,21 +191,6 @@ ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
 // MODE: 0 LessEqual (max depth, later wins ties), 1 Less (max, earlier wins),
 //       2 GreaterEqual (min, later wins), 3 Greater (min, earlier wins).
 // ---------------------------------------------------------------------------
-template <int MODE>
-__device__ __forceinline__ unsigned long long make_key(float depth, uint32_t seq) {
-    uint32_t hi = f2ord(depth);
-    if (MODE >= 2) hi = ~hi;
-    uint32_t lo = (MODE & 1) ? (0xfffffffeu - seq) : (seq + 1u);
-    return ((unsigned long long)hi << 32) | lo;
-}
-template <int MODE>
-__device__ __forceinline__ unsigned long long clear_key() {
-    uint32_t hi = f2ord(kClearDepth);
-    if (MODE >= 2) hi = ~hi;
-    uint32_t lo = (MODE & 1) ? 0xffffffffu : 0u;
-    return ((unsigned long long)hi << 32) | lo;
-}
-
 #ifndef SRB_VIS_THREADS
 #define SRB_VIS_THREADS 128
 #endif
@@ -248,6 +233,66 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
     }
 }
 
+// Setup record of a directly rasterized triangle (fan 0 of an unclipped triangle), rebuilt from the mesh for the
+// resolve step: the draw from the tri2draw table, then the same setup_tri the setup kernel ran on the same clip
+// positions -- the same bits.  The triangle was accepted there, so cull state and rejections need no second look.
+__device__ __forceinline__ TriRec rebuild_rec(const RasterArgs& A, const FrameParams& fp, const uint32_t seq) {
+    const int g = (int)(seq >> 1);
+    int di = __ldg(A.tri2draw + (g >> kTri2DrawShift));
+    while (g >= A.draws[di].tbase + A.draws[di].n_triangles) ++di;       // short: draws of fewer than 64 triangles in between
+    const DrawRec& d = A.draws[di];
+    const int t = g - d.tbase;
+    const int i0 = (int)__ldg(d.idx + 3 * t), i1 = (int)__ldg(d.idx + 3 * t + 1), i2 = (int)__ldg(d.idx + 3 * t + 2);
+    const float4 c[3] = {A.clip[d.vbase + i2], A.clip[d.vbase + i1], A.clip[d.vbase + i0]};     // :367 order {v2,v1,v0}
+    TriRec r;
+    int minX, maxX, minY, maxY;
+    setup_tri(c, fp.W, fp.H, SRB_CULL_NONE, r, minX, maxX, minY, maxY);
+    r.meta = (uint32_t)di;
+    return r;
+}
+
+template <int MODE, bool OUT8, bool DIRECT>
+__device__ __forceinline__ void vis_resolve(const unsigned long long* keys, const unsigned long long ckey, const bool dirty,
+                                            const int tx0, const int ty0, const float4 clearCol, const RasterArgs& A,
+                                            const FrameParams& fp, const SrbUniforms& U) {
+    for (int p = threadIdx.x; p < kTile * kTile; p += kVisThreads) {
+        const int px = p & 15, py = p >> 4;
+        const int x = tx0 + px, y = ty0 + py;
+        if (x >= fp.W || y >= fp.H) continue;
+        const unsigned long long key = keys[py * kKeyPitch + px];
+        float4 outc = clearCol;
+        float outd = kClearDepth;
+#ifdef SRB_EXP_SKIP_SHADE
+        if (false) {
+#else
+        if (key != ckey) {
+#endif
+            uint32_t hi = (uint32_t)(key >> 32);
+            const uint32_t ord = key_ord<MODE>(key), seq = ord >> 1;
+            if (((ord & 1u) != 0u) != DIRECT) continue;                 // the other pass's pixel (never taken in a clean tile)
+            if (MODE >= 2) hi = ~hi;
+            const TriRec r = DIRECT ? rebuild_rec(A, fp, seq) : load_rec(A.recs, seq);
+            const TriEq e = tri_eq(r);
+            const int startX = max(e.minX, tx0), startY = max(e.minY, ty0);
+            float w0, w1, w2, w0f, w1f, w2f;
+            edge_chain(r, e, startX, startY, x, y, w0, w1, w2);
+            frag_depth(r.d0, r.d1, r.d2, e.invArea, w0, w1, w2, w0f, w1f, w2f);
+            int di;
+            float4 c = shade_fragment(A, fp, U, r, seq, w0f, w1f, w2f, di);
+            // Eligibility guarantees alpha > 0 and alpha == 1 up to rounding, so
+            // the blend destination is immaterial at 8 bits; use the clear colour.
+            outc = blend_px(c, clearCol, A.draws[di].blend);
+            outd = ord2f(hi);
+        } else if (DIRECT) {
+            continue;                                                   // clear pixels were written by the first pass
+        }
+        const size_t pidx = (size_t)y * fp.W + x;
+        __stcs(A.colorOut + pidx, outc);
+        __stcs(A.depth + pidx, outd);
+        if (OUT8) __stcs(A.color8Out + pidx, pack_unorm8(outc));
+    }
+}
+
 struct VisSmem {
     unsigned long long keys[kTile * kKeyPitch]; // rows padded: lanes walk DIFFERENT rows at the same x, and an
                                                 // unpadded 128-byte row pitch would put them all on the same two banks
@@ -268,8 +313,8 @@ template <int MODE, bool OUT8>
 #define SRB_BE be
 #endif
 __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t bs, const uint32_t SRB_BE,
-                                                 const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U,
-                                                 VisSmem& sm) {
+                                                 const bool dirty, const RasterArgs& A, const FrameParams& fp,
+                                                 const SrbUniforms& U, VisSmem& sm) {
     unsigned long long* keys = sm.keys;
     float (*S)[kVisThreads] = sm.S;
     int* warpRows = sm.warpRows;
@@ -283,7 +328,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
 #ifdef SRB_EXP_ALL_EMPTY                         /* diagnostic builds only: every tile takes the clear-only path */
     if (true) {
 #else
-    if (bs == SRB_BE) {
+    if (bs == SRB_BE && !dirty) {
 #endif
 #ifdef SRB_EXP_SKIP_EMPTY
         return;
@@ -305,7 +350,19 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     const uint32_t be = min(be_, bs + (uint32_t)SRB_EXP_CAP_BIN);
 #endif
     const unsigned long long ckey = clear_key<MODE>();
-    for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
+    if (dirty) {
+        // The setup kernel rasterized small triangles straight into this tile's slice of the global key buffer
+        // (direct_raster): start from those keys and hand the slice back empty for the frame after next.
+        unsigned long long* gk = A.gkeys + (size_t)tile * (kTile * kTile);
+        for (int i = tid; i < kTile * kTile; i += kVisThreads) {
+            const unsigned long long k = gk[i];
+            gk[i] = 0ull;
+            keys[(i >> 4) * kKeyPitch + (i & 15)] = max(k, ckey);
+        }
+    } else {
+        for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
+    }
+    if (bs == SRB_BE) __syncthreads();              // no chunk loop below: its barriers are what orders the key init otherwise
 
     for (uint32_t cb = bs; cb < be; cb += kVisThreads) {
         // ---- one triangle per thread: derive its raster constants for this tile ----
@@ -382,40 +439,11 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
 #ifdef SRB_TILE_TIMING
     if (tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(sm.phase[1]));
 #endif
-    // ---- resolve: shade each pixel's winner once, write colour + depth ----
-    for (int p = tid; p < kTile * kTile; p += kVisThreads) {
-        const int px = p & 15, py = p >> 4;
-        const int x = tx0 + px, y = ty0 + py;
-        if (x >= fp.W || y >= fp.H) continue;
-        const unsigned long long key = keys[py * kKeyPitch + px];
-        float4 outc = clearCol;
-        float outd = kClearDepth;
-#ifdef SRB_EXP_SKIP_SHADE
-        if (false) {
-#else
-        if (key != ckey) {
-#endif
-            uint32_t lo = (uint32_t)key, hi = (uint32_t)(key >> 32);
-            const uint32_t seq = (MODE & 1) ? (0xfffffffeu - lo) : (lo - 1u);
-            if (MODE >= 2) hi = ~hi;
-            const TriRec r = load_rec(A.recs, seq);
-            const TriEq e = tri_eq(r);
-            const int startX = max(e.minX, tx0), startY = max(e.minY, ty0);
-            float w0, w1, w2, w0f, w1f, w2f;
-            edge_chain(r, e, startX, startY, x, y, w0, w1, w2);
-            frag_depth(r.d0, r.d1, r.d2, e.invArea, w0, w1, w2, w0f, w1f, w2f);
-            int di;
-            float4 c = shade_fragment(A, fp, U, r, seq, w0f, w1f, w2f, di);
-            // Eligibility guarantees alpha > 0 and alpha == 1 up to rounding, so
-            // the blend destination is immaterial at 8 bits; use the clear colour.
-            outc = blend_px(c, clearCol, A.draws[di].blend);
-            outd = ord2f(hi);
-        }
-        const size_t pidx = (size_t)y * fp.W + x;
-        __stcs(A.colorOut + pidx, outc);
-        __stcs(A.depth + pidx, outd);
-        if (OUT8) __stcs(A.color8Out + pidx, pack_unorm8(outc));
-    }
+    // ---- resolve: shade each pixel's winner once, write colour + depth.  Winners of the direct path (no setup
+    // record: rebuilt from the mesh) are left to a second pass that only dirty tiles run, so that the rebuild's
+    // registers do not weigh on the common loop. ----
+    vis_resolve<MODE, OUT8, false>(keys, ckey, dirty, tx0, ty0, clearCol, A, fp, U);
+    if (dirty) vis_resolve<MODE, OUT8, true>(keys, ckey, dirty, tx0, ty0, clearCol, A, fp, U);
 }
 
 #ifndef SRB_VIS_MINBLOCKS
@@ -443,7 +471,7 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
 #endif
-    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, A, fp, U, sm);
+    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, o.w != 0u, A, fp, U, sm);
 #ifdef SRB_TILE_TIMING
     __syncthreads();
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));

@@ -8,6 +8,9 @@ namespace srb {
 // Everything the tile kernels need to reach per-frame data.
 struct RasterArgs {
     const DrawRec* draws;
+    const float4* clip;           // clip positions from vertex_kernel (the resolve step rebuilds direct winners from them)
+    const int32_t* tri2draw;      // draw of every 2^kTri2DrawShift-th global triangle (frustum kernel)
+    unsigned long long* gkeys;    // global winner keys of the direct path, 256 per tile, 0 = nothing (read and reset per tile)
     const float4* wn;             // world normals from vertex_kernel
     RecStore recs;
     const ClipAttr* clipAttrs;
@@ -38,10 +41,12 @@ __device__ __forceinline__ float4 tex_nearest(const uchar4* tex, int tw, int th,
     float v = sub(vv, (float)sat_int(vv));
     u = add(u, (u < 0.0f) ? 1.0f : 0.0f);
     v = add(v, (v < 0.0f) ? 1.0f : 0.0f);
-    int x = sat_int(mul(u, (float)tw)) % tw;
-    int y = sat_int(mul(v, (float)th)) % th;
-    if (x < 0) x += tw;
-    if (y < 0) y += th;
+    int x = sat_int(mul(u, (float)tw));
+    int y = sat_int(mul(v, (float)th));
+    // u in [0, 1] puts x in [0, tw], where "% tw" only folds x == tw to 0; the integer division runs only for
+    // the values outside (huge or non-finite coordinates)
+    if ((unsigned)x >= (unsigned)tw) { x = x == tw ? 0 : x % tw; if (x < 0) x += tw; }
+    if ((unsigned)y >= (unsigned)th) { y = y == th ? 0 : y % th; if (y < 0) y += th; }
     uchar4 p = __ldg(tex + (size_t)y * tw + x);
     const float inv255 = 1.0f / 255.0f;
     return make_float4(mul((float)p.x, inv255), mul((float)p.y, inv255), mul((float)p.z, inv255), mul((float)p.w, inv255));

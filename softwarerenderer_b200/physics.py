@@ -33,6 +33,7 @@ class Physics:
         rays = np.ascontiguousarray(np.concatenate([o, d], axis=1))
         m = np.ascontiguousarray(np.asarray(model, dtype=np.float32).reshape(16))
         out = np.zeros(rays.shape[0], dtype=N.RAY_HIT_DTYPE)
+        window.ApplyUniforms()                  # numerics_fma selects the form of Vector3.Transform (Physics.cs:56-58)
         N.check(window._ctx, N.lib().srb_raycast(window._ctx, window.mesh_handle(vertices, indices), N.ptr(m), N.ptr(rays),
                                                  rays.shape[0], int(faceMask), N.ptr(out)))
         return out

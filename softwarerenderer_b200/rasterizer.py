@@ -106,8 +106,11 @@ class FrustumCuller:
         sph = np.array([(*b.Center, b.Radius) for b in bounds], dtype=np.float32).reshape(n, 4)
         mod = np.ascontiguousarray(np.asarray(models, dtype=np.float32).reshape(n, 16))
         out = np.zeros(n, dtype=np.int32)
-        N.check(window._ctx, N.lib().srb_frustum_test(window._ctx, N.ptr(sph), N.ptr(mod), N.ptr(_mat(viewMatrix)),
-                                                      N.ptr(_mat(projectionMatrix)), n, N.ptr(out)))
+        # the converted matrices are bound to locals: N.ptr() keeps no reference, and a temporary would be freed
+        # (and its block reused by the next conversion) before the C call reads it
+        v, p = _mat(viewMatrix), _mat(projectionMatrix)
+        window.ApplyUniforms()                      # numerics_fma selects the form of Vector4.Transform
+        N.check(window._ctx, N.lib().srb_frustum_test(window._ctx, N.ptr(sph), N.ptr(mod), N.ptr(v), N.ptr(p), n, N.ptr(out)))
         return out
 
     @staticmethod

@@ -8,7 +8,9 @@ deferred: RenderFrame() submits them and launches the CUDA pipeline.
 from __future__ import annotations
 
 import ctypes as C
-import zlib
+import hashlib
+import weakref
+from collections import OrderedDict
 from typing import Optional
 
 import numpy as np
@@ -48,6 +50,14 @@ class Uniforms:
         return u
 
 
+class MeshHandle:
+    """A mesh resident on one window's device (MainWindow.CreateMesh)."""
+    __slots__ = ("window_uid", "handle")
+
+    def __init__(self, window_uid: int, handle: int):
+        self.window_uid, self.handle = window_uid, handle
+
+
 class MainWindow:
     _next_uid = 0
 
@@ -68,8 +78,9 @@ class MainWindow:
         self._clear_flags = 0
         self._clear_color = np.zeros(4, dtype=np.float32)
         self._draws = []               # recorded SrbDrawCmd rows
-        self._mesh_cache = {}
-        self._keepalive = []
+        self._mesh_by_content = OrderedDict()    # blake2b of the arrays -> device mesh handle, LRU order
+        self._mesh_by_identity = {}              # (id(vertices), id(indices)) -> (weakrefs, layout, content key)
+        self.MeshCacheCapacity = 8192            # resident meshes kept before the least recently used is destroyed
 
     # -- lifetime -----------------------------------------------------------
     def Close(self) -> None:
@@ -149,12 +160,38 @@ class MainWindow:
             self.RenderFrame()
         self._clear_flags |= N.SRB_CLEAR_DEPTH
 
-    # -- mesh upload cache (the reference re-passes ToArray() copies every call) --
-    def mesh_handle(self, vertices: np.ndarray, indices: np.ndarray) -> int:
+    # -- mesh upload cache (the reference re-passes ToArray() copies every call, Renderer.cs:452-453) --
+    # Keyed by array identity: an array object seen before costs a dictionary lookup and two
+    # weak-reference checks per RenderMesh call.  An array seen for the first time is hashed once (blake2b, so that
+    # equal copies share one device mesh and a collision cannot silently swap geometry); the least recently used
+    # device meshes are destroyed beyond MeshCacheCapacity.  Arrays are assumed immutable while cached, as the
+    # reference's List<VertexInput> are after load; InvalidateMesh() drops the entry of one that was edited in place.
+    @staticmethod
+    def _layout(a: np.ndarray):
+        return (a.__array_interface__["data"][0], a.nbytes, a.dtype.str, a.strides)
+
+    def mesh_handle(self, vertices, indices) -> int:
+        if isinstance(vertices, MeshHandle):                     # explicit resident handle: no hashing at all
+            if vertices.window_uid != self._uid:
+                raise ValueError("mesh handle belongs to another window")
+            return vertices.handle
+        ident = (id(vertices), id(indices))
+        hit = self._mesh_by_identity.get(ident)
+        if hit is not None:
+            wv, wi, lay, ckey = hit
+            if wv() is vertices and wi() is indices and lay == (self._layout(vertices), self._layout(indices)):
+                h = self._mesh_by_content.get(ckey)
+                if h is not None:
+                    self._mesh_by_content.move_to_end(ckey)
+                    return h
+            del self._mesh_by_identity[ident]
         v = np.ascontiguousarray(vertices)
         i = np.ascontiguousarray(indices, dtype=np.uint16)
-        key = (v.nbytes, i.nbytes, zlib.crc32(v.view(np.uint8).reshape(-1)), zlib.crc32(i.view(np.uint8).reshape(-1)))
-        h = self._mesh_cache.get(key)
+        dig = hashlib.blake2b(digest_size=20)
+        dig.update(v.view(np.uint8).reshape(-1))
+        dig.update(i.view(np.uint8).reshape(-1))
+        ckey = (v.nbytes, i.nbytes, dig.digest())
+        h = self._mesh_by_content.get(ckey)
         if h is None:
             flat = v.view(np.float32).reshape(-1)
             if flat.size % 12:
@@ -163,8 +200,33 @@ class MainWindow:
             N.check(self._ctx, N.lib().srb_mesh_create(self._ctx, N.ptr(flat), flat.size // 12, N.ptr(i), i.size,
                                                        C.byref(out)))
             h = out.value
-            self._mesh_cache[key] = h
+            self._mesh_by_content[ckey] = h
+            while len(self._mesh_by_content) > max(1, int(self.MeshCacheCapacity)):
+                if self._draws:                                  # recorded draws may name the victim: keep it
+                    break
+                _, victim = self._mesh_by_content.popitem(last=False)
+                N.check(self._ctx, N.lib().srb_mesh_destroy(self._ctx, victim))
+        else:
+            self._mesh_by_content.move_to_end(ckey)
+        if isinstance(vertices, np.ndarray) and isinstance(indices, np.ndarray):
+            try:
+                if len(self._mesh_by_identity) > 4 * max(1, int(self.MeshCacheCapacity)):
+                    self._mesh_by_identity = {k: e for k, e in self._mesh_by_identity.items()
+                                              if e[0]() is not None and e[1]() is not None}
+                self._mesh_by_identity[ident] = (weakref.ref(vertices), weakref.ref(indices),
+                                                 (self._layout(vertices), self._layout(indices)), ckey)
+            except TypeError:
+                pass
         return h
+
+    def CreateMesh(self, vertices, indices) -> "MeshHandle":
+        """Upload once, keep the handle: RenderMesh / Physics.Raycast accept it in place of the vertex array
+        (indices=None), and a resident mesh then costs no lookup at all."""
+        return MeshHandle(self._uid, self.mesh_handle(vertices, indices))
+
+    def InvalidateMesh(self, vertices, indices) -> None:
+        """Forget the identity entry of arrays that were modified in place."""
+        self._mesh_by_identity.pop((id(vertices), id(indices)), None)
 
     def record_draw(self, row: np.ndarray) -> None:
         self._draws.append(row)
@@ -188,6 +250,13 @@ class MainWindow:
         N.check(self._ctx, L.srb_end_frame(self._ctx))
         self._draws = []
         self._clear_flags = 0
+
+    def ApplyUniforms(self, near_clip: Optional[float] = None) -> None:
+        """Push the captured shader state (and the numerics_fma switch) to the device without submitting a frame:
+        srb_raycast and srb_frustum_test read it."""
+        from .rasterizer import Rasterizer
+        u = self.Uniforms.to_struct(Rasterizer.NearClip if near_clip is None else near_clip, int(Rasterizer.RenderDebugMode))
+        N.check(self._ctx, N.lib().srb_set_uniforms(self._ctx, C.byref(u)))
 
     def ReplayFrame(self) -> None:
         N.check(self._ctx, N.lib().srb_replay_frame(self._ctx))

@@ -74,8 +74,10 @@ def test_degenerate_offscreen_and_non_finite_triangles(oracle, pipeline):
     assert abs(float(od[0, 0]) + 0.75) < 1e-6 and abs(float(od[H - 1, W - 1]) + 0.75) < 1e-6   # (0.5 + 1) / 2, negated: triangle 6, not 6b
 
 
-def test_w_zero_and_behind_the_camera(oracle):
-    """Corners with w <= 0 go through the near clip (:208-224); all three behind: dropped; w == 0 exactly (:393)."""
+@pytest.mark.parametrize("fma", [0, 1])
+def test_w_zero_and_behind_the_camera(oracle, fma):
+    """Corners with w <= 0 go through the near clip (:208-224); all three behind: dropped; w == 0 exactly (:393).
+    Both forms of Shaders.Lerp / Vector4.Transform (numerics_fma)."""
     from softwarerenderer_b200 import numerics as nm
     from softwarerenderer_b200.scene import DrawItem, Mesh, Scene, default_projection
     from softwarerenderer_b200.shaders import Material, Shaders
@@ -88,6 +90,7 @@ def test_w_zero_and_behind_the_camera(oracle):
     mesh = Mesh(v, np.arange(12, dtype=np.uint16), Material())
     I = nm.identity()
     sc = Scene(W, H, [DrawItem(mesh, I, I, default_projection(W, H), cull=0)])
+    sc.numerics_fma = fma
     oc, od, _ = oracle.render_scene(sc, threads=2)
     for pipeline in (1, 2):
         gc, gd, st = _render_gpu(sc, pipeline)
@@ -155,3 +158,80 @@ def test_triangle_behind_the_eye_draws_nothing(oracle, pipeline):
     gc, gd, st = _render_gpu(sc, pipeline)
     oc, od, _ = oracle.render_scene(sc, threads=2)
     assert (gd == CLEAR_DEPTH).all() and np.array_equal(gd, od) and np.array_equal(gc, oc)
+
+
+def test_frame_that_keeps_the_framebuffer_grows_its_buffers(oracle):
+    """More near-clipped triangles than the clip side buffer's first capacity (4096), in a frame that does NOT
+    clear: every raster kernel returns at once when a capacity overflowed, so the framebuffer is untouched and the
+    frame is simply run again with larger buffers."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200.scene import DrawItem, Mesh, Scene, default_projection, submit_scene
+    from softwarerenderer_b200.shaders import Material, Shaders
+    W, H = 320, 200
+    rng = np.random.RandomState(3)
+    n = 6000
+    pos = []
+    for k in range(n):                                    # one corner behind the camera, two in front: always clipped
+        cx, cy = rng.uniform(-3, 3), rng.uniform(-2, 2)
+        pos += [(cx - 0.2, cy - 0.2, -3.0), (cx + 0.2, cy - 0.2, -3.0), (cx, cy + 0.2, 2.0)]
+    v = Shaders.make_vertices(pos, color=np.tile(rng.uniform(0.2, 1.0, (n, 1, 4)), (1, 3, 1)).reshape(-1, 4))
+    v["Color"][:, 3] = 0.5                                # translucent: ordered pipeline, blending with what is there
+    mesh = Mesh(v, np.arange(3 * n, dtype=np.uint16), Material())
+    I = nm.identity()
+    from softwarerenderer_b200 import scene as S
+    first = S.scene_model("Gun", W, H)
+    second = Scene(W, H, [DrawItem(mesh, I, I, default_projection(W, H), cull=0)])
+    win = srb.MainWindow(W, H)
+    try:
+        submit_scene(win, first)
+        # second frame without clears: draws over the first one's colour and depth
+        from softwarerenderer_b200.rasterizer import Rasterizer
+        d = second.draws[0]
+        Rasterizer.RenderMesh(win, d.mesh.Vertices, d.mesh.Indices, d.model, d.view, d.proj, Shaders.StockVertexShader,
+                              Shaders.StockFragmentShader(None), d.cull, d.depth, d.blend)
+        win.RenderFrame()
+        st = win.Stats()
+        assert st.clipped_triangles == n and st.pipeline_used == 1
+        gc, gd = win.ColorBuffer, win.DepthBuffer
+    finally:
+        win.Close()
+    _, _, _, w = oracle.render_scene(first, threads=4, return_window=True)
+    oc, od, ost = oracle.render_scene(second, threads=4, clear=(False, False), window=w)
+    compare(gc, gd, oc, od)
+
+
+def test_bands_with_a_projection_that_keeps_negative_w(oracle):
+    """Band and block culling assume clip w > 0 for what they drop (for w < 0 the NDC position flips sides).  With
+    a projection whose clip z is constant 1, the reference's clip test z >= NearClip * w keeps every vertex with
+    w <= 10 -- also those behind the eye, w < 0 -- so triangles that straddle w = 0 are drawn with flipped corners.
+    Bands must still reproduce the full frame, and the full frame the oracle."""
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200.scene import DrawItem, Mesh, Scene, default_projection
+    from softwarerenderer_b200.shaders import Material, Shaders
+    W, H = 640, 368
+    rng = np.random.RandomState(5)
+    pos = []
+    for k in range(600):
+        c = np.array([rng.uniform(-6, 6), rng.uniform(-4, 4), rng.uniform(-7, 3)])
+        pos += [tuple(c + rng.uniform(-2.5, 2.5, 3)) for _ in range(3)]
+    col = np.tile(np.c_[rng.uniform(0.2, 1, (600, 3)), np.ones(600)][:, None, :], (1, 3, 1)).reshape(-1, 4)
+    v = Shaders.make_vertices(pos, color=col)
+    p = np.asarray(default_projection(W, H), dtype=np.float32).reshape(4, 4).copy()
+    p[:, 2] = 0.0
+    p[3, 2] = 1.0
+    I = nm.identity()
+    draws = [DrawItem(Mesh(v[i:i + 450], np.arange(450, dtype=np.uint16), Material()), I, I, p, cull=0)
+             for i in range(0, 1800, 450)]
+    sc = Scene(W, H, draws)
+    wv = -np.array(pos)[:, 2].reshape(-1, 3)
+    assert ((wv < 0).any(1) & (wv > 0).any(1)).sum() > 100          # triangles that straddle w = 0
+    oc, od, _ = oracle.render_scene(sc, threads=8)
+    fc, fd, _ = _render_gpu(sc, 0)
+    compare(fc, fd, oc, od)
+    tiles_y = (H + 15) // 16
+    cuts = [0, 5, 11, 17, tiles_y]
+    for r0, r1 in zip(cuts[:-1], cuts[1:]):
+        bc, bd, _ = _render_gpu(sc, 0, band=(r0, r1))
+        y0, y1 = r0 * 16, min(r1 * 16, H)
+        assert np.array_equal(bd[y0:y1], fd[y0:y1]) and np.array_equal(bc[y0:y1], fc[y0:y1])

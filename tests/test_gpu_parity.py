@@ -23,12 +23,19 @@ def _render_gpu(scene, pipeline=0, band=None):
         win.Close()
 
 
+# numerics_fma in {0, 1}: whether Vector4.Transform / Vector*.Lerp fuse on a given .NET runtime is unknown
+# (Renderer.cs:832-834, Shaders.cs:52-55), so both forms of the vertex stage, the near clipper and
+# the fragment shader's Lerp are held to the oracle under the same switch.
+@pytest.mark.parametrize("fma", [0, 1])
 @pytest.mark.parametrize("pipeline", [1, 2])
 @pytest.mark.parametrize("cam", [0, 2, 5])
-def test_gun_1080p(oracle, pipeline, cam):
+def test_gun_1080p(oracle, pipeline, cam, fma):
     """BASELINE config 2: bundled Gun at 1920x1080 (partial last tile row), pixel-diff gate."""
     from softwarerenderer_b200 import scene as S
+    if fma == 0 and cam == 2:
+        pytest.skip("fma=0 is covered by cameras 0 and 5")
     sc = S.scene_model("Gun", 1920, 1080, view=S.gun_camera(cam))
+    sc.numerics_fma = fma
     oc, od, _ = oracle.render_scene(sc, threads=8)
     gc, gd, st = _render_gpu(sc, pipeline)
     stats = compare(gc, gd, oc, od)
@@ -36,16 +43,19 @@ def test_gun_1080p(oracle, pipeline, cam):
     print(stats)
 
 
+@pytest.mark.parametrize("fma", [0, 1])
 @pytest.mark.parametrize("pipeline", [1, 2])
-def test_city_small(oracle, pipeline):
+def test_city_small(oracle, pipeline, fma):
     """Config 3 shape at reduced size: multi-model scene, device FrustumCuller, near-plane clipping."""
     from softwarerenderer_b200 import scene as S
     sc = S.scene_city(1280, 720, n_instances=24)
+    sc.numerics_fma = fma
     oc, od, ost = oracle.render_scene(sc, threads=8)
     gc, gd, st = _render_gpu(sc, pipeline)
     stats = compare(gc, gd, oc, od)
     assert st.draws_visible == sum(oracle.frustum_flags(sc))
     assert st.triangles_setup + st.triangles_no_coverage == ost.triangles_drawn
+    assert st.clipped_triangles > 0                        # the near clipper's Lerp ran under this switch
     print(stats, st.draws_visible, st.triangles_setup, st.clipped_triangles, st.tile_pairs)
 
 

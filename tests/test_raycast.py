@@ -132,12 +132,13 @@ def test_against_a_float64_brute_force_on_the_gun(oracle):
 # ---------------------------------------------------------------------------
 # CUDA batch kernel vs the oracle
 # ---------------------------------------------------------------------------
-def _check_batch(oracle, win, mesh, M, origins, dirs, mask):
+def _check_batch(oracle, win, mesh, M, origins, dirs, mask, fma=1):
     import softwarerenderer_b200 as srb
+    win.Uniforms.NumericsFma = fma                      # both forms of Vector3.Transform
     got = srb.Physics.RaycastBatch(win, origins, dirs, mesh.Vertices, mesh.Indices, M, srb.RaycastFaceMask(mask))
     nhit = 0
     for k in range(len(origins)):
-        hit, dist, pt, nr, tri = oracle.raycast(origins[k], dirs[k], mesh.Vertices, mesh.Indices, M, face_mask=mask)
+        hit, dist, pt, nr, tri = oracle.raycast(origins[k], dirs[k], mesh.Vertices, mesh.Indices, M, face_mask=mask, fma=fma)
         g = got[k]
         assert bool(g["hit"]) == hit, (k, g, hit, dist, tri)
         assert g["triangle"] == tri
@@ -149,8 +150,9 @@ def _check_batch(oracle, win, mesh, M, origins, dirs, mask):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("fma", [0, 1])
 @pytest.mark.parametrize("mask", [0, 1, 2])
-def test_cuda_raycast_matches_the_oracle_on_the_bundled_models(oracle, mask):
+def test_cuda_raycast_matches_the_oracle_on_the_bundled_models(oracle, mask, fma):
     import softwarerenderer_b200 as srb
     from softwarerenderer_b200 import numerics as nm
     from softwarerenderer_b200 import scene as S
@@ -167,7 +169,7 @@ def test_cuda_raycast_matches_the_oracle_on_the_bundled_models(oracle, mask):
                 n = 150                                                      # > 2 ray chunks of 64
                 origins = (cw + rng.normal(size=(n, 3)) * 4 * r * 1.5).astype(np.float32)
                 dirs = (cw + rng.uniform(-0.7, 0.7, (n, 3)) * r * 1.5 - origins).astype(np.float32)
-                total += _check_batch(oracle, win, m, M, origins, dirs, mask)
+                total += _check_batch(oracle, win, m, M, origins, dirs, mask, fma)
         assert total > 100
     finally:
         win.Close()
@@ -194,7 +196,8 @@ def test_cuda_raycast_single_call_defaults_and_singular_model():
 
 
 @pytest.mark.gpu
-def test_cuda_raycast_large_batch_on_a_dense_grid(oracle):
+@pytest.mark.parametrize("fma", [0, 1])
+def test_cuda_raycast_large_batch_on_a_dense_grid(oracle, fma):
     """4,096 rays against a 64,800-triangle grid mesh of the stress scene; a sample is checked ray by ray."""
     import softwarerenderer_b200 as srb
     from softwarerenderer_b200 import scene as S
@@ -210,10 +213,11 @@ def test_cuda_raycast_large_batch_on_a_dense_grid(oracle):
     dirs = (tgt - origins).astype(np.float32)
     win = srb.MainWindow(64, 64)
     try:
+        win.Uniforms.NumericsFma = fma
         got = srb.Physics.RaycastBatch(win, origins, dirs, m.Vertices, m.Indices, M, srb.RaycastFaceMask.None_)
         assert got["hit"].mean() > 0.5
         for k in range(0, n, 64):
-            hit, dist, pt, nr, tri = oracle.raycast(origins[k], dirs[k], m.Vertices, m.Indices, M, face_mask=0)
+            hit, dist, pt, nr, tri = oracle.raycast(origins[k], dirs[k], m.Vertices, m.Indices, M, face_mask=0, fma=fma)
             assert bool(got[k]["hit"]) == hit and got[k]["triangle"] == tri and got[k]["distance"] == F(dist)
     finally:
         win.Close()
