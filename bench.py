@@ -207,8 +207,9 @@ def run_gpu(args):
     # ---- N>1: sort-first bands on tile-row boundaries.  Every rank rendered the whole frame once above,
     # so all ranks derive the same cost-balanced cuts from the same per-row bin counts (no exchange).
     cuts = [band_rows(tiles_y, world, r)[0] for r in range(world)] + [tiles_y]
+    full_frame_ms = float(st.gpu_ms)
+    w_rows = win.TileRowPairs().astype(np.float64) + 0.85 * ((W + 15) // 16)         # an empty tile costs about 0.85 pair
     if world > 1 and args.bands == "balanced":
-        w_rows = win.TileRowPairs().astype(np.float64) + 0.85 * ((W + 15) // 16)     # an empty tile costs about 0.85 pair
         # fused gather: the pixels of bands 1.. go to rank 0 as peer stores over NVLink, which costs their
         # tile kernel about --remote-cost pairs per tile; band 0 takes correspondingly more rows
         extra = args.remote_cost * ((W + 15) // 16) if args.gather == "fused" else 0.0
@@ -216,21 +217,25 @@ def run_gpu(args):
     r0, r1 = cuts[rank], cuts[rank + 1]
     fused = world > 1 and args.gather == "fused"
     rgba8_gather = fused and args.gather_format == "rgba8"
+    box = box8 = [None]
+
+    def use_gather(fmt):
+        """Band ranks: where the tile kernel stores final colour.  'rgba8': 4-byte peer stores into rank 0's RGBA8
+        frame (float4 colour stays local); 'float4': 16-byte peer stores into rank 0's ColorBuffer; None: local."""
+        if rank == 0:
+            return
+        win.SetGatherRgba8Target(box8[0] if fmt == "rgba8" else None)
+        win.SetColorTarget(box[0] if fmt == "float4" else None)
+
     if world > 1:
         win.SetBand(r0, r1)
-        if fused and rgba8_gather:
-            # rank 0 exports an RGBA8 frame; every rank's tile kernel stores its band's 8-bit colour into it
-            # (rank 0 locally, the others as 4-byte peer stores over NVLink); float4 colour stays on each rank
-            box = [win.ExportGatherRgba8() if rank == 0 else None]
-            dist.broadcast_object_list(box, src=0)
-            if rank != 0:
-                win.SetGatherRgba8Target(box[0])
-        elif fused:
-            # rank 0 exports its colour buffer; band ranks store their final colour straight into it
+        if fused:
+            # rank 0 exports its ColorBuffer and an RGBA8 frame (its own tile kernel fills its band of that one too)
             box = [win.ExportColorHandle() if rank == 0 else None]
+            box8 = [win.ExportGatherRgba8() if rank == 0 else None]
             dist.broadcast_object_list(box, src=0)
-            if rank != 0:
-                win.SetColorTarget(box[0])
+            dist.broadcast_object_list(box8, src=0)
+            use_gather(args.gather_format)
         S.submit_scene(win, scene)              # settle band-sized capacities
         st = win.Stats()
     y0, y1 = r0 * 16, min(r1 * 16, H)
@@ -254,12 +259,40 @@ def run_gpu(args):
     fb = torch.as_tensor(_DevArray(L.srb_device_color_ptr(ctx), (H, W, 4)), device=dev)
 
     token = torch.zeros(1, device=dev)
+    bar_stream = torch.cuda.Stream(device=dev) if world > 1 else None
+    bar_pending = []
 
-    def gather():
+    def frame_barrier():
+        """Fused gather: the pixels already went over NVLink as peer stores; what is left of the gather is the
+        "every band of frame k has landed" barrier, a 4-byte NCCL all-reduce.  'side' (default): the all-reduce of
+        frame k runs on its own stream behind tile kernel k, and tile kernel k+2 waits for it -- the ranks stay
+        within one frame of each other, and the collective's launch and latency are off the raster stream.
+        'inline': on the raster stream, between tile kernels k and k+1 (round 1)."""
+        if args.frame_barrier == "inline":
+            dist.all_reduce(token)
+            return
+        if args.frame_barrier == "none":        # diagnostic only: ranks run free (not a result)
+            return
+        e = torch.cuda.Event()
+        e.record(ext)
+        bar_stream.wait_event(e)
+        with torch.cuda.stream(bar_stream):
+            dist.all_reduce(token)
+            eb = torch.cuda.Event()
+            eb.record(bar_stream)
+        bar_pending.append(eb)
+        if len(bar_pending) > 1:
+            ext.wait_event(bar_pending.pop(0))
+
+    def gather(landed=False):
+        """landed=True: the caller reads the assembled frame next, so every band of THIS frame must be in place
+        (barrier on the raster stream); otherwise the ranks only have to stay within a frame of each other."""
         if world == 1:
             return
-        if fused:
-            dist.all_reduce(token)              # frame barrier only: the pixels already went over NVLink as peer stores
+        if fused and landed:
+            dist.all_reduce(token)
+        elif fused:
+            frame_barrier()
         else:
             gather_bands(fb, H, rank, world, dist, cuts=cuts)
 
@@ -278,7 +311,7 @@ def run_gpu(args):
         N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
         N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
         N.check(ctx, L.srb_end_frame(ctx))
-        gather()
+        gather(landed=True)
         if rank == 0:
             N.check(ctx, L.srb_present_rgb_async(ctx, C.c_void_p(host_rgb[e2e_count[0] & 1].data_ptr())))
             e2e_count[0] += 1
@@ -293,7 +326,7 @@ def run_gpu(args):
         N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
         N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
         N.check(ctx, L.srb_end_frame(ctx))
-        gather()
+        gather(landed=True)
         if rank == 0:
             if rgba8_gather:        # the assembled 8-bit frame is already in rank 0's gather frame: copy it out
                 N.check(ctx, L.srb_present_gathered_rgba8_async(ctx, C.c_void_p(host_rgba8[e2e_count[0] & 1].data_ptr())))
@@ -308,7 +341,7 @@ def run_gpu(args):
         N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
         N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
         N.check(ctx, L.srb_end_frame(ctx))
-        gather()
+        gather(landed=True)
         if rank == 0:
             N.check(ctx, L.srb_read_color(ctx, C.c_void_p(host.data_ptr())))
         if fused:
@@ -383,8 +416,22 @@ def run_gpu(args):
     # A 4-byte all-reduce behind a device-side fence on the previous copies is the "frame delivered" barrier.
     e2e_parallel = None
     if world > 1:
-        if fused and rank != 0 and not rgba8_gather:
-            win.SetColorTarget(None)            # final colour back into the local buffer
+        if fused:
+            use_gather(None)                    # final colour into the local buffer only
+        # Band cuts for THIS loop: a rank's frame time is its rendering plus the copy of its rows over its own PCIe
+        # link, and at 12 B per pixel the copy is ten times the rendering -- the raster-balanced cuts of `value`
+        # (rank 0 owns half the rows, all of them sky) would leave one link with half the frame.  Minimise the
+        # largest (render + copy) instead: per tile row, the measured full-frame time in proportion to the row's
+        # bin load, plus its bytes at the link rate.
+        t_render = full_frame_ms * w_rows / max(w_rows.sum(), 1e-9)
+        t_copy = np.full(tiles_y, 16 * W * 12 / (args.pcie_gbs * 1e6))
+        t_copy[-1] = (H - 16 * (tiles_y - 1)) * W * 12 / (args.pcie_gbs * 1e6)
+        cuts_e2e = balanced_cuts(t_render + t_copy, world)
+        e0r, e1r = cuts_e2e[rank], cuts_e2e[rank + 1]
+        win.SetBand(e0r, e1r)
+        S.submit_scene(win, scene)
+        win._draws = []
+        ye0, ye1 = e0r * 16, min(e1r * 16, H)
         nbytes = 2 * H * W * 12
         shm_path = "/dev/shm/srb200_frame_%s" % os.environ.get("MASTER_PORT", "0")
         if rank == 0:
@@ -402,7 +449,7 @@ def run_gpu(args):
             N.check(ctx, L.srb_end_frame(ctx))
             N.check(ctx, L.srb_present_fence(ctx))   # stream waits for the copies of the frames before this one
             dist.all_reduce(token)                   # => on every rank: all bands of the previous frame have landed
-            N.check(ctx, L.srb_present_rgb_rows_async(ctx, C.c_void_p(shared[par_count[0] & 1].ctypes.data), y0, y1))
+            N.check(ctx, L.srb_present_rgb_rows_async(ctx, C.c_void_p(shared[par_count[0] & 1].ctypes.data), ye0, ye1))
             par_count[0] += 1
 
         ms_p, wall_p, _ = timed(step_e2e_parallel, Ke, 3)
@@ -410,11 +457,13 @@ def run_gpu(args):
         dist.barrier()
         fps_p = Ke / max(wall_p, ms_p / 1000.0)
         # the assembled frame must be the frame: compare with this rank's own rows read the slow way
-        ok = bool(np.array_equal(shared[(par_count[0] - 1) & 1][y0:y1], win.ColorBuffer[y0:y1, :, :3]))
+        ok = bool(np.array_equal(shared[(par_count[0] - 1) & 1][ye0:ye1], win.ColorBuffer[ye0:ye1, :, :3]))
         oks = [None] * world
         dist.all_gather_object(oks, ok)
         e2e_parallel = {"value": fps_p, "unit": "frames/s", "ms_per_step": 1000.0 * max(wall_p, ms_p / 1000.0) / Ke,
                         "d2h_bytes_per_step": int(W * H * 12), "rows_verified": all(oks),
+                        "cuts_tile_rows": [int(x) for x in cuts_e2e],
+                        "cuts_policy": "minimise max over ranks of (render + rows x 12 B / %.0f GB/s)" % args.pcie_gbs,
                         "result": "every band rank copies its own rows of the packed RGB float frame into one shared "
                                   "pinned host frame over its own PCIe link (srb_present_rgb_rows_async); no NVLink gather"}
         torch.cuda.cudart().cudaHostUnregister(shared.ctypes.data)
@@ -422,8 +471,11 @@ def run_gpu(args):
         dist.barrier()
         if rank == 0:
             os.unlink(shm_path)
-        if fused and rank != 0 and not rgba8_gather:
-            win.SetColorTarget(box[0])
+        win.SetBand(r0, r1)                     # back to the cuts and the gather of `value`
+        if fused:
+            use_gather(args.gather_format)
+        S.submit_scene(win, scene)
+        win._draws = []
 
     # ---- single-frame latency (median and p5/p95 over >= 200 frames): one frame at a time,
     # synchronised, device time of begin..end of the pipeline from the library's own CUDA events (no overlap
@@ -456,30 +508,39 @@ def run_gpu(args):
         stage_ms_ranks = [None] * world
         dist.all_gather_object(stage_ms_ranks, stage_ms)
 
-    # ---- N>1, float4 gather: the same resident loop once more with the RGBA8 gather (reported beside `value`,
-    # never in its place): band ranks switch from float4 peer stores to 4-byte ones into rank 0's RGBA8 frame ----
-    rgba8_extra = None
-    if fused and not rgba8_gather and not args.no_rgba8_extra:
-        box8 = [win.ExportGatherRgba8() if rank == 0 else None]
-        dist.broadcast_object_list(box8, src=0)
-        if rank != 0:
-            win.SetColorTarget(None)
-            win.SetGatherRgba8Target(box8[0])
+    # ---- N>1: the same resident loop once more with the OTHER gather format (reported beside `value`, never in
+    # its place): band ranks switch between 4-byte stores into rank 0's RGBA8 frame and 16-byte stores into its
+    # float4 ColorBuffer ----
+    other_gather = None
+    if fused and not args.no_other_gather:
+        other = "float4" if rgba8_gather else "rgba8"
+        use_gather(other)
         dist.barrier()
         Kx = min(K, 300)
         ms_x, _, _ = timed(step_resident, Kx, 3)
-        full8 = torch.from_numpy(win.GatheredRgba8()).to(dev) if rank == 0 else torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
-        dist.broadcast(full8, src=0)
-        mine = np.rint(np.clip(win.ColorBuffer[y0:y1], 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
-        oks8 = [None] * world
-        dist.all_gather_object(oks8, bool(np.array_equal(full8[y0:y1].cpu().numpy(), mine)))
-        del full8
-        rgba8_extra = {"value": Kx / (ms_x / 1000.0), "unit": "frames/s", "steps": Kx, "verified": all(oks8),
-                       "note": "same loop, bands gathered at display precision (--gather-format rgba8): 4 B per pixel "
-                               "into one RGBA8 frame on GPU 0, float4 bands stay on the rendering GPU"}
-        if rank != 0:                               # back to the float4 gather
-            win.SetGatherRgba8Target(None)
-            win.SetColorTarget(box[0])
+        if other == "rgba8":
+            full8 = torch.from_numpy(win.GatheredRgba8()).to(dev) if rank == 0 else torch.empty((H, W, 4), dtype=torch.uint8, device=dev)
+            dist.broadcast(full8, src=0)
+            mine = np.rint(np.clip(win.ColorBuffer[y0:y1], 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+            ok_x = bool(np.array_equal(full8[y0:y1].cpu().numpy(), mine))
+            del full8
+        else:
+            # rank 0's ColorBuffer now holds every band: each rank compares its rows of it with a local re-render
+            fullc = torch.from_numpy(win.ColorBuffer).to(dev) if rank == 0 else torch.empty((H, W, 4), dtype=torch.float32, device=dev)
+            dist.broadcast(fullc, src=0)
+            got = fullc[y0:y1].cpu().numpy()
+            del fullc
+            use_gather(None)
+            N.check(ctx, L.srb_replay_frame(ctx))
+            ok_x = bool(np.array_equal(got, win.ColorBuffer[y0:y1]))
+        oks_x = [None] * world
+        dist.all_gather_object(oks_x, ok_x)
+        other_gather = {"format": other, "value": Kx / (ms_x / 1000.0), "unit": "frames/s", "steps": Kx, "verified": all(oks_x),
+                        "note": "same loop, bands gathered as " + ("display-precision RGBA8 (4 B per pixel into one frame on GPU 0; float4 "
+                                "bands stay on the rendering GPU)" if other == "rgba8" else
+                                "float4 (16 B per pixel into GPU 0's ColorBuffer: exact API parity; bound by GPU 0's NVLink ingress, "
+                                "%.0f MB per frame)" % (W * H * 16 * (world - 1) / world / 1e6))}
+        use_gather(args.gather_format)
         dist.barrier()
 
     # ---- roofline bookkeeping ----
@@ -520,7 +581,7 @@ def run_gpu(args):
             "mpixels_per_sec": W * H * fps / 1e6,
             "config": base_config(args.workload, scene),
             "config_detail": {"draws_visible": int(sum(visible)), "triangles_setup": int(st.triangles_setup),
-                              "triangles_direct": int(st.triangles_direct), "triangles_no_coverage": int(st.triangles_no_coverage),
+                              "triangles_no_coverage": int(st.triangles_no_coverage), "split_parts": int(st.split_parts),
                               "tile_pairs": int(st.tile_pairs), "pipeline": "visibility" if st.pipeline_used == 2 else "ordered",
                               "parallelism": f"bands{world}" if world > 1 else "single",
                               "bands": {"cuts_tile_rows": [int(x) for x in cuts], "policy": args.bands,
@@ -544,7 +605,7 @@ def run_gpu(args):
             "e2e_parallel_present": e2e_parallel,     # N>1: promoted to `e2e` below; the gather-to-GPU-0 loop is kept beside it
             "gpu_launches": int(st.kernel_launches) * K,          # timed region of `value`; each e2e step adds the flatten kernel
             "clocks": clocks,
-            "value_rgba8_gather": rgba8_extra,
+            "value_other_gather": other_gather,
             "frame_latency": frame_latency,
             "stage_ms": stage_ms,
             "stage_ms_ranks": stage_ms_ranks,
@@ -570,8 +631,8 @@ def run_gpu(args):
                 line["roofline_frame"]["fragments_tested"] = int(fr["tested"])
                 line["roofline_frame"]["fragments_shaded_in_submission_order"] = int(fr["shaded"])
     if world > 1:
-        if fused and rank != 0:                  # unmap rank 0's frame before rank 0 frees it
-            (win.SetGatherRgba8Target if rgba8_gather else win.SetColorTarget)(None)
+        if fused:                                # unmap rank 0's frames before rank 0 frees them
+            use_gather(None)
         torch.cuda.synchronize(dev)
         dist.barrier()
     win.Close()
@@ -634,10 +695,14 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="fused", choices=["fused", "nccl"], help="N>1: how bands reach rank 0")
-    ap.add_argument("--gather-format", default="float4", choices=["float4", "rgba8"],
-                    help="N>1, fused gather: what the band ranks store into rank 0's frame (float4 ColorBuffer, or the "
-                         "frame at display precision: a quarter of the NVLink traffic)")
-    ap.add_argument("--no-rgba8-extra", action="store_true", help="N>1: skip the additional RGBA8-gather measurement")
+    ap.add_argument("--gather-format", default="rgba8", choices=["float4", "rgba8"],
+                    help="N>1, fused gather: what the band ranks store into rank 0's frame -- the frame at display precision "
+                         "(RGBA8, the format of the parity gate; default) or the float4 ColorBuffer (four times the NVLink "
+                         "traffic: at 4K and N=8, 116 MB per frame into GPU 0, which caps the rate near 7,000 frames/s)")
+    ap.add_argument("--no-other-gather", action="store_true", help="N>1: skip the additional measurement with the other gather format")
+    ap.add_argument("--frame-barrier", default="side", choices=["side", "inline", "none"],
+                    help="N>1, fused gather: where the per-frame 4-byte all-reduce runs (see frame_barrier)")
+    ap.add_argument("--pcie-gbs", type=float, default=50.0, help="N>1 e2e: host link rate assumed by the band cuts of the e2e loop")
     ap.add_argument("--remote-cost", type=float, default=12.0,
                     help="N>1, fused gather: extra cost of a tile whose pixels are stored to rank 0 over NVLink, in bin pairs")
     ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"], help="N>1: band cut policy")

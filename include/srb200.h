@@ -107,8 +107,7 @@ typedef struct SrbStats {
     float   gpu_ms;               /* device time of the last end_frame (CUDA events) */
     int32_t triangles_no_coverage;/* accepted by the reference's setup, but at most 4x4 px and proven to pass its
                                      coverage test nowhere: not binned (triangles_setup + this = the reference's count) */
-    int32_t triangles_direct;     /* of triangles_setup: at most 4x4 px, unclipped, rasterized by the setup kernel itself
-                                     into the per-pixel winner keys (visibility pipeline; no record, no bin entry) */
+    int32_t split_parts;          /* CTAs beyond one per tile that the visibility tile kernel spent on split bins */
     int32_t _pad;
 } SrbStats;
 
@@ -121,6 +120,11 @@ const char* srb_last_error(SrbContext* ctx);                     /* ctx may be N
 /* Multi-GPU: restrict this context to tile rows [row0,row1) (16-px rows). */
 int srb_set_band(SrbContext* ctx, int tile_row0, int tile_row1);
 int srb_set_pipeline(SrbContext* ctx, int pipeline);
+/* Tuning (no reference counterpart; the image never depends on it): a tile whose bin holds at least min_entries
+ * (triangle, tile) pairs is rasterized by several CTAs of part_entries (a multiple of 32) each, merged through 64-bit atomic max; one
+ * threshold for contexts that render the whole frame, one for band contexts (multi-GPU).  0 = never split.
+ * Defaults 1024 / 256 / 128. */
+int srb_set_bin_split(SrbContext* ctx, int min_entries_full_frame, int min_entries_band, int part_entries);
 /* Multi-GPU band gather fused into the tile kernel (no reference counterpart):
  * rank 0 exports its colour buffer (CUDA IPC handle, 64 bytes); a band rank passes that handle as
  * its colour target and from then on stores its band's final colour straight into rank 0's

@@ -85,34 +85,46 @@ struct SrbContext {
     FrameParams fp;
     bool useVis = false;
     int visMode = 0;
-    DevBuf<DrawRec> dDraws;
     DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels: (draw, first element) of every run of
                                       // kGeomBlock vertices / triangles of a VISIBLE draw, compacted per frame by the frustum kernel
     int nVBlocks = 0, nTBlocks = 0;
-    DevBuf<int32_t> dTri2Draw;        // draw of every 64th global triangle (frustum kernel -> resolve of direct winners)
+    DevBuf<float4> dClip;
     DevBuf<TriRef> dRefs;
     DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
     DevBuf<uint32_t> dTileCount, dBinScratch;
+    unsigned long long* dSliceKeys = nullptr;   // key slices of split bins (kMaxExtra x 256), all zero between tile kernels
+    uint32_t* dSliceDone = nullptr;             // per slice: parts merged so far, zero between tile kernels
+    // Bins of >= splitMin entries are rasterized by several CTAs of splitPart entries each (srb_set_bin_split).
+    // A full frame is bound by the sum of its tiles, not by the longest one, and splitting costs a merge, so it
+    // starts late there; a band's floor IS its heaviest tile.
+    uint32_t splitMinFull = 1024, splitMinBand = 256, splitPart = 128;
     // Frame pipelining: the geometry stages of frame N+1 run on their own stream while the tile kernel of
     // frame N is still running on `stream`.  Everything the tile kernel reads and the geometry stages write
     // exists twice; frames alternate between the two sets.
     struct FrameBufs {
+        DevBuf<DrawRec> dDraws;           // this set's copy of the draw table (the frustum kernel writes into it)
+        uint64_t tableSerial = 0;         // which frame's table it holds
         DevBuf<float4> dWn;               // world normals (vertex stage -> shading)
-        DevBuf<float4> dClip;             // clip positions (vertex stage -> setup; resolve of direct winners)
-        DevBuf<unsigned long long> dGKeys;    // winner keys of the direct path, 256 per tile; all zero between frames
         DevBuf<float4> dRecsR, dRecsS;    // split setup records (RecStore)
         DevBuf<ClipAttr> dClipAttrs;
         DevBuf<uint32_t> dTileStart, dTileCursor, dBins;
         DevBuf<uint4> dOrder;             // tile launch order of the visibility kernel
         Counters* dCnt = nullptr;
-        Counters* hCnt = nullptr;         // pinned
+        Counters* hCnt = nullptr;         // pinned; copied right after the scan kernel (every counter is final by then)
+        cudaEvent_t cntReady = nullptr;   // ... and this event follows the copy: the host learns about a capacity
+                                          // overflow when the frame's GEOMETRY is done, not its rasterization
     } fb[2];
     int slot = 0;                         // set used by the most recently launched frame
     cudaStream_t geomStream = nullptr, lastGeomStream = nullptr;
-    cudaEvent_t geomDone[2] = {}, rasterDone[2] = {}, inputsReady = nullptr;
-    bool rasterRecorded[2] = {false, false}, inputsDirty = false;
-    DrawRec* hDraws = nullptr;        // pinned staging
-    size_t hDrawsCap = 0;
+    cudaEvent_t geomDone[2] = {}, rasterDone[2] = {};
+    bool rasterRecorded[2] = {false, false};
+    uint64_t frameSerial = 0;             // bumped by every srb_end_frame: the draw table in hDraws[tableSlot]
+    int tableSlot = 0;
+    DrawRec* hDraws[2] = {nullptr, nullptr};   // pinned staging of the draw table, two alternating buffers
+    size_t hDrawsCap[2] = {0, 0};
+    cudaEvent_t stagingDone[2] = {};  // the H2D copy out of hDraws[i] has finished
+    bool stagingBusy[2] = {false, false};
+    int stagingSlot = 0;
     SrbStats stats;
     bool profiling = false;
     cudaEvent_t stageEv[SRB_N_STAGES + 1] = {};
@@ -202,50 +214,52 @@ int launch_frame(SrbContext* c) {
         if (!c->profiling) return;
         for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], stage + 1 <= 5 ? gs : c->stream);
     };
-    if (c->inputsDirty) {             // the draw table was uploaded on c->stream
-        CK(c, cudaEventRecord(c->inputsReady, c->stream));
-        CK(c, cudaStreamWaitEvent(gs, c->inputsReady, 0));
-        c->inputsDirty = false;
-    }
     if (c->rasterRecorded[s]) CK(c, cudaStreamWaitEvent(gs, c->rasterDone[s], 0));   // the frame before last used this set
     if (c->lastGeomStream && c->lastGeomStream != gs)       // profiling toggled: keep the single-copy geometry buffers serial
         CK(c, cudaStreamWaitEvent(gs, c->geomDone[s ^ 1], 0));
     c->lastGeomStream = gs;
     CK(c, cudaEventRecord(c->ev0, gs));
+    if (B.tableSerial != c->frameSerial && fp.nDraws > 0) {
+        // Every set has its own device copy of the draw table, uploaded on the geometry stream the first time the
+        // set renders a new frame: a new frame's geometry then does not wait for the previous frame's tile kernel.
+        CK(c, cudaMemcpyAsync(B.dDraws.p, c->hDraws[c->tableSlot], (size_t)fp.nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, gs));
+        CK(c, cudaEventRecord(c->stagingDone[c->tableSlot], gs));
+        c->stagingBusy[c->tableSlot] = true;
+    }
+    B.tableSerial = c->frameSerial;
     CK(c, cudaMemsetAsync(B.dCnt, 0, sizeof(Counters), gs));
-    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, 2 * (size_t)nTiles * sizeof(uint32_t), gs));      // counts + dirty flags
-    uint32_t* const tileDirty = c->dTileCount.p + nTiles;
-    fp.directSmall = c->useVis ? 1 : 0;
-    fp.visMode = c->visMode;
+    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), gs));
     if (c->profiling) cudaEventRecord(c->stageEv[0], gs);
     if (fp.nDraws > 0) {
-        frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(c->dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
-                                                                                fp.bandRow1, fp.tilesY, c->dVBlocks.p, c->dTBlocks.p,
-                                                                                c->dTri2Draw.p);
+        frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(B.dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
+                                                                                fp.bandRow1, fp.tilesY, c->dVBlocks.p, c->dTBlocks.p);
         ++launches;
     }
     mark(1);
     if (c->nVBlocks > 0) {
         if (U.numerics_fma)
-            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
+            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
         else
-            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(c->dDraws.p, c->dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
+            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
         ++launches;
     }
     mark(2);
     if (c->nTBlocks > 0) {
         setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
-            c->dDraws.p, c->dTBlocks.p, fp, U, B.dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
-            c->dTileCount.p, B.dCnt, B.dGKeys.p, tileDirty);
+            B.dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
+            c->dTileCount.p, B.dCnt);
         bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
         launches += 2;
     }
     mark(3);
     if (bandTiles > 0) {
-        scan_tiles_kernel<<<kScanCtas, 1024, 0, gs>>>(c->dTileCount.p, tileDirty, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p,
-                                                     fp.bandRow0 * fp.tilesX, bandTiles, B.dCnt, fp.pairCap);
+        scan_tiles_kernel<<<kScanCtas, 1024, 0, gs>>>(c->dTileCount.p, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p,
+                                                     fp.bandRow0 * fp.tilesX, bandTiles, B.dCnt, fp.pairCap,
+                                                     c->useVis ? (fullFrame ? c->splitMinFull : c->splitMinBand) : 0u, c->splitPart);
         ++launches;
     }
+    CK(c, cudaMemcpyAsync(B.hCnt, B.dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, gs));
+    CK(c, cudaEventRecord(B.cntReady, gs));
     mark(4);
     if (fp.totalT > 0 && bandTiles > 0) {
         // grid-stride over the accepted-triangle list (its length is only known on the device)
@@ -272,29 +286,31 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaEventRecord(c->geomDone[s], gs));
     CK(c, cudaStreamWaitEvent(c->stream, c->geomDone[s], 0));
     RasterArgs A;
-    A.draws = c->dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
-    A.clip = B.dClip.p; A.tri2draw = c->dTri2Draw.p; A.gkeys = B.dGKeys.p;
+    A.draws = B.dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
+    A.gkeys = c->dSliceKeys; A.sliceDone = c->dSliceDone; A.bandTiles = bandTiles;
     A.clipAttrs = B.dClipAttrs.p; A.tileStart = B.dTileStart.p; A.tileEnd = B.dTileCursor.p;
     A.bins = B.dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = B.dCnt;
     A.colorOut = c->colorTarget ? c->colorTarget : c->color;
     A.color8Out = c->color8Target ? c->color8Target : c->color8;
 #ifdef SRB_TILE_TIMING
-    if (c->dBinScratch.reserve((size_t)nTiles * 8) != cudaSuccess) return fail(c, SRB_ERR_CUDA, "dbg alloc");
+    if (c->dBinScratch.reserve(((size_t)nTiles + kMaxExtra) * 8) != cudaSuccess) return fail(c, SRB_ERR_CUDA, "dbg alloc");
+    CK(c, cudaMemsetAsync(c->dBinScratch.p, 0, ((size_t)nTiles + kMaxExtra) * 32, c->stream));
     A.dbg = (ulonglong4*)c->dBinScratch.p;
 #endif
     if (bandTiles > 0) {
         if (c->useVis) {
             mark(6);                       // no sort stage on the visibility path
             const bool out8 = A.color8Out != nullptr;
+            const unsigned visGrid = (unsigned)bandTiles + kMaxExtra;      // the first kMaxExtra CTAs: parts of split bins
             switch (c->visMode) {
-                case 0: if (out8) vis_tile_kernel<0, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
-                        else vis_tile_kernel<0, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
-                case 1: if (out8) vis_tile_kernel<1, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
-                        else vis_tile_kernel<1, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
-                case 2: if (out8) vis_tile_kernel<2, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
-                        else vis_tile_kernel<2, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
-                default: if (out8) vis_tile_kernel<3, true><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U);
-                         else vis_tile_kernel<3, false><<<bandTiles, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 0: if (out8) vis_tile_kernel<0, true><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U);
+                        else vis_tile_kernel<0, false><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 1: if (out8) vis_tile_kernel<1, true><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U);
+                        else vis_tile_kernel<1, false><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                case 2: if (out8) vis_tile_kernel<2, true><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U);
+                        else vis_tile_kernel<2, false><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U); break;
+                default: if (out8) vis_tile_kernel<3, true><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U);
+                         else vis_tile_kernel<3, false><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U); break;
             }
             ++launches;
         } else {
@@ -307,7 +323,6 @@ int launch_frame(SrbContext* c) {
     }
     mark(7);
     CK(c, cudaGetLastError());
-    CK(c, cudaMemcpyAsync(B.hCnt, B.dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaEventRecord(c->rasterDone[s], c->stream));
     c->rasterRecorded[s] = true;
     CK(c, cudaEventRecord(c->ev1, c->stream));
@@ -317,18 +332,20 @@ int launch_frame(SrbContext* c) {
     return SRB_OK;
 }
 
-// Wait for the pending frame; if a device-side capacity overflowed, grow and re-run.
-int complete_frame(SrbContext* c) {
-    CK(c, cudaStreamSynchronize(c->stream));
-    if (!c->framePending) return SRB_OK;
+// Settle the pending frame: wait until its geometry stages are done (the counters are final after the scan kernel),
+// and if a device-side capacity overflowed, grow the buffers and run the frame again -- every raster kernel of the
+// overflowed attempt returns at once, so the framebuffer is untouched, also for frames that do not clear.
+// waitRaster: additionally wait for the frame's pixels (read-backs, accessors, statistics with timings).
+int complete_frame(SrbContext* c, bool waitRaster = true) {
+    if (!c->framePending) {
+        if (waitRaster) CK(c, cudaStreamSynchronize(c->stream));
+        return SRB_OK;
+    }
+    CK(c, cudaEventSynchronize(c->fb[c->slot].cntReady));
     for (int attempt = 0; attempt < 8; ++attempt) {
         const Counters& k = *c->fb[c->slot].hCnt;
         if (!k.overflow) break;
-        // Every overflow flag is raised by the setup or scan kernel, and every raster kernel returns at once when
-        // one is set: the framebuffer is untouched, so the frame can be run again -- also one that does not clear.
-        // What the aborted frame did leave behind are direct-path keys in its set's global key buffer.
-        if (c->useVis && c->fb[c->slot].dGKeys.p)
-            CK(c, cudaMemsetAsync(c->fb[c->slot].dGKeys.p, 0, (size_t)c->tilesX * c->tilesY * kTile * kTile * sizeof(unsigned long long), c->stream));
+        // (cudaFree inside reserve() waits for the device: nothing is freed under a running kernel.)
         if (k.overflow & 1u) {
             size_t want = (size_t)k.nPairs + k.nPairs / 8 + 1024;
             for (auto& b : c->fb) CK(c, b.dBins.reserve(want));
@@ -346,17 +363,19 @@ int complete_frame(SrbContext* c) {
         }
         int rc = launch_frame(c);
         if (rc != SRB_OK) return rc;
-        CK(c, cudaStreamSynchronize(c->stream));
+        CK(c, cudaEventSynchronize(c->fb[c->slot].cntReady));
     }
     if (c->fb[c->slot].hCnt->overflow) return fail(c, SRB_ERR_CUDA, "bin capacity overflow persisted after regrow");
-    c->framePending = false;
     const Counters& k = *c->fb[c->slot].hCnt;
     c->stats.draws_visible = k.nVisibleDraws;
-    c->stats.triangles_setup = (int64_t)k.nRefs + k.nDirect;
-    c->stats.triangles_direct = k.nDirect;
+    c->stats.triangles_setup = k.nRefs;
+    c->stats.split_parts = (int32_t)std::min<uint32_t>(k.nExtra, 0x7fffffffu);
     c->stats.triangles_no_coverage = (int32_t)k.nNoCover;
     c->stats.tile_pairs = k.nPairs;
     c->stats.clipped_triangles = k.nClippedTris;
+    if (!waitRaster) return SRB_OK;
+    CK(c, cudaStreamSynchronize(c->stream));
+    c->framePending = false;
     float ms = 0.0f;
     if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) == cudaSuccess) c->stats.gpu_ms = ms;
     if (c->profiling)
@@ -410,14 +429,19 @@ int srb_create(int device, int width, int height, SrbContext** out_ctx) {
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
         if ((e = cudaStreamCreateWithPriority(&c->geomStream, cudaStreamNonBlocking, hi)) != cudaSuccess) return bail("cudaStreamCreate", e);
     }
-    if ((e = cudaEventCreateWithFlags(&c->inputsReady, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     for (int s = 0; s < 2; ++s) {
         if ((e = cudaEventCreateWithFlags(&c->geomDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
         if ((e = cudaEventCreateWithFlags(&c->rasterDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->fb[s].cntReady, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->stagingDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
         if ((e = cudaMalloc((void**)&c->fb[s].dCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc", e);
         if ((e = cudaMallocHost((void**)&c->fb[s].hCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMallocHost", e);
         std::memset(c->fb[s].hCnt, 0, sizeof(Counters));
     }
+    if ((e = cudaMalloc((void**)&c->dSliceKeys, (size_t)kMaxExtra * kTile * kTile * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc((void**)&c->dSliceDone, (size_t)kMaxExtra * sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMemsetAsync(c->dSliceKeys, 0, (size_t)kMaxExtra * kTile * kTile * sizeof(unsigned long long), c->stream)) != cudaSuccess) return bail("cudaMemset", e);
+    if ((e = cudaMemsetAsync(c->dSliceDone, 0, (size_t)kMaxExtra * sizeof(uint32_t), c->stream)) != cudaSuccess) return bail("cudaMemset", e);
     int rc = alloc_framebuffer(c, width, height);
     if (rc != SRB_OK) { g_createError = c->err; delete c; return rc; }
     *out_ctx = c;
@@ -433,11 +457,13 @@ int srb_destroy(SrbContext* c) {
     if (c->color8) cudaFree(c->color8);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
-    c->dDraws.release(); c->dVBlocks.release(); c->dTBlocks.release(); c->dTri2Draw.release();
+    c->dVBlocks.release(); c->dTBlocks.release(); c->dClip.release();
+    if (c->dSliceKeys) cudaFree(c->dSliceKeys);
+    if (c->dSliceDone) cudaFree(c->dSliceDone);
     c->dRayScratch.release();
     c->dRefs.release(); c->dBigQ.release(); c->dTileCount.release(); c->dBinScratch.release();
     for (auto& b : c->fb) {
-        b.dWn.release(); b.dClip.release(); b.dGKeys.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
+        b.dDraws.release(); b.dWn.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
         b.dTileCursor.release(); b.dBins.release(); b.dOrder.release();
         if (b.dCnt) cudaFree(b.dCnt);
         if (b.hCnt) cudaFreeHost(b.hCnt);
@@ -445,8 +471,10 @@ int srb_destroy(SrbContext* c) {
     for (int s = 0; s < 2; ++s) {
         if (c->geomDone[s]) cudaEventDestroy(c->geomDone[s]);
         if (c->rasterDone[s]) cudaEventDestroy(c->rasterDone[s]);
+        if (c->fb[s].cntReady) cudaEventDestroy(c->fb[s].cntReady);
+        if (c->stagingDone[s]) cudaEventDestroy(c->stagingDone[s]);
+        if (c->hDraws[s]) cudaFreeHost(c->hDraws[s]);
     }
-    if (c->inputsReady) cudaEventDestroy(c->inputsReady);
     if (c->geomStream) { cudaStreamSynchronize(c->geomStream); cudaStreamDestroy(c->geomStream); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
     for (int s = 0; s < 2; ++s) {
@@ -456,7 +484,6 @@ int srb_destroy(SrbContext* c) {
     }
     if (c->color) cudaFree(c->color);
     if (c->depth) cudaFree(c->depth);
-    if (c->hDraws) cudaFreeHost(c->hDraws);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     for (auto& e : c->stageEv) if (e) cudaEventDestroy(e);
@@ -574,6 +601,17 @@ int srb_get_tile_row_pairs(SrbContext* c, uint32_t* out, int n) {
         for (int x = 0; x < c->tilesX; ++x) s += h[(size_t)r * c->tilesX + x];
         out[r] = (uint32_t)std::min<uint64_t>(s, 0xffffffffu);
     }
+    return SRB_OK;
+}
+
+int srb_set_bin_split(SrbContext* c, int min_entries_full_frame, int min_entries_band, int part_entries) {
+    if (!c) return SRB_ERR_ARG;
+    if (min_entries_full_frame < 0 || min_entries_band < 0 || part_entries < 32 || part_entries % 32 != 0 ||
+        (min_entries_full_frame != 0 && min_entries_full_frame < 64) || (min_entries_band != 0 && min_entries_band < 64))
+        return fail(c, SRB_ERR_ARG, "bin split: thresholds are 0 (off) or >= 64 entries, parts a multiple of 32 entries");
+    c->splitMinFull = (uint32_t)min_entries_full_frame;
+    c->splitMinBand = (uint32_t)min_entries_band;
+    c->splitPart = (uint32_t)part_entries;
     return SRB_OK;
 }
 
@@ -774,18 +812,28 @@ int srb_end_frame(SrbContext* c) {
     if (!c->inFrame) return fail(c, SRB_ERR_STATE, "end_frame without begin_frame");
     c->inFrame = false;
     CK(c, cudaSetDevice(c->device));
-    int rc = complete_frame(c);          // previous frame's staging buffers are reused below
+    // The previous frame only has to be past its geometry stages (capacities settled, or grown and re-run): its
+    // tile kernel keeps running while this frame is prepared.  Everything queued below is ordered behind it on
+    // c->stream, and the pinned staging buffers alternate.
+    int rc = complete_frame(c, false);
     if (rc != SRB_OK) return rc;
     std::stable_sort(c->queue.begin(), c->queue.end(),
                      [](const QueuedDraw& a, const QueuedDraw& b) { return a.order < b.order; });
     const int nDraws = (int)c->queue.size();
-    if ((size_t)nDraws + 1 > c->hDrawsCap) {
-        if (c->hDraws) cudaFreeHost(c->hDraws);
-        c->hDraws = nullptr;
-        size_t cap = (size_t)nDraws + nDraws / 2 + 64;
-        CK(c, cudaMallocHost((void**)&c->hDraws, cap * sizeof(DrawRec)));
-        c->hDrawsCap = cap;
+    const int hs = c->stagingSlot;
+    c->stagingSlot ^= 1;
+    if (c->stagingBusy[hs]) {                    // an upload of the frame before last
+        CK(c, cudaEventSynchronize(c->stagingDone[hs]));
+        c->stagingBusy[hs] = false;
     }
+    if ((size_t)nDraws + 1 > c->hDrawsCap[hs]) {
+        if (c->hDraws[hs]) cudaFreeHost(c->hDraws[hs]);
+        c->hDraws[hs] = nullptr;
+        size_t cap = (size_t)nDraws + nDraws / 2 + 64;
+        CK(c, cudaMallocHost((void**)&c->hDraws[hs], cap * sizeof(DrawRec)));
+        c->hDrawsCap[hs] = cap;
+    }
+    DrawRec* const hDraws = c->hDraws[hs];
     size_t nVB = 0, nTB = 0;
     for (int i = 0; i < nDraws; ++i) {
         const MeshRes& m = c->meshes[c->queue[i].cmd.mesh - 1];
@@ -798,7 +846,7 @@ int srb_end_frame(SrbContext* c) {
     for (int i = 0; i < nDraws; ++i) {
         const SrbDrawCmd& q = c->queue[i].cmd;
         const MeshRes& m = c->meshes[q.mesh - 1];
-        DrawRec& d = c->hDraws[i];
+        DrawRec& d = hDraws[i];
         std::memcpy(d.model, q.model, 64); std::memcpy(d.view, q.view, 64); std::memcpy(d.proj, q.proj, 64);
         std::memcpy(d.sphere, q.sphere, 16);
         d.vtx = m.vtx; d.idx = m.idx;
@@ -823,7 +871,7 @@ int srb_end_frame(SrbContext* c) {
         if (q.blend != SRB_BLEND_ALPHA && q.blend != SRB_BLEND_NONE) eligible = false;
         if (!m.opaque || !texOpaque) eligible = false;
     }
-    if (totalV > 0x3ffffff0 || totalT > 0x3ffffff0) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
+    if (totalV > 0x3fffffff || totalT > 0x3fffffff) return fail(c, SRB_ERR_ARG, "frame too large (>2^30 vertices or triangles)");
     if (c->colorTarget && !(c->clearFlags & SRB_CLEAR_COLOR))
         return fail(c, SRB_ERR_STATE, "a remote colour target needs frames that clear colour");
     if (c->uniforms.debug_mode == SRB_DEBUG_WIREFRAME) eligible = false;   // DrawLine: depth 1/d, W != 0 writes -- ordered replay only
@@ -839,18 +887,13 @@ int srb_end_frame(SrbContext* c) {
         default: c->visMode = 0; break;
     }
     const int nTiles = c->tilesX * c->tilesY;
-    CK(c, c->dDraws.reserve((size_t)nDraws + 1));
+    for (auto& b : c->fb) CK(c, b.dDraws.reserve((size_t)nDraws + 1));
     CK(c, c->dVBlocks.reserve(nVB + 1));
     CK(c, c->dTBlocks.reserve(nTB + 1));
-    for (auto& b : c->fb) CK(c, b.dOrder.reserve(nTiles));
-    CK(c, c->dTri2Draw.reserve(((size_t)totalT >> kTri2DrawShift) + 2));
+    for (auto& b : c->fb) CK(c, b.dOrder.reserve((size_t)nTiles + kMaxExtra));
+    CK(c, c->dClip.reserve((size_t)totalV + 1));
     for (auto& b : c->fb) {
         CK(c, b.dWn.reserve((size_t)totalV + 1));
-        CK(c, b.dClip.reserve((size_t)totalV + 1));
-        if (c->useVis && b.dGKeys.cap < (size_t)nTiles * kTile * kTile) {
-            CK(c, b.dGKeys.reserve((size_t)nTiles * kTile * kTile));
-            CK(c, cudaMemsetAsync(b.dGKeys.p, 0, b.dGKeys.cap * sizeof(unsigned long long), c->stream));
-        }
         CK(c, b.dRecsR.reserve(3 * (2 * (size_t)totalT + 2)));
         CK(c, b.dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
         CK(c, b.dClipAttrs.reserve(4096));
@@ -860,11 +903,10 @@ int srb_end_frame(SrbContext* c) {
     }
     CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
     CK(c, c->dBigQ.reserve(1u << 16));
-    CK(c, c->dTileCount.reserve(2 * (size_t)nTiles));
+    CK(c, c->dTileCount.reserve(nTiles));
     CK(c, c->dBinScratch.reserve(std::max(c->fb[0].dBins.cap, c->fb[1].dBins.cap)));
-    if (nDraws > 0) {
-        CK(c, cudaMemcpyAsync(c->dDraws.p, c->hDraws, (size_t)nDraws * sizeof(DrawRec), cudaMemcpyHostToDevice, c->stream));
-    }
+    c->tableSlot = hs;                // launch_frame uploads it to whichever set renders next (and to the other
+    ++c->frameSerial;                 // one when that set is first used for this frame, e.g. by srb_replay_frame)
     c->nVBlocks = (int)nVB; c->nTBlocks = (int)nTB;
     FrameParams& fp = c->fp;
     fp.W = c->W; fp.H = c->H; fp.tilesX = c->tilesX; fp.tilesY = c->tilesY;
@@ -881,7 +923,6 @@ int srb_end_frame(SrbContext* c) {
     c->stats.draws_submitted = nDraws;
     c->stats.triangles_submitted = totalT;
     c->haveFrame = true;
-    c->inputsDirty = true;            // the uploads above are on c->stream; the geometry stream waits for them
     return launch_frame(c);
 }
 
@@ -988,8 +1029,9 @@ static int present_rows_async(SrbContext* c, void* out, int y0, int y1, bool rgb
     if (!c || !out) return SRB_ERR_ARG;
     if (gathered && !c->color8) return fail(c, SRB_ERR_STATE, "no RGBA8 gather frame on this context (srb_gather_rgba8_export first)");
     if (y0 < 0 || y1 < y0 || y1 > c->H) return fail(c, SRB_ERR_ARG, "row range out of bounds");
-    int rc = srb_sync(c);                                  // frame finished and capacity overflows settled
-    if (rc != SRB_OK) return rc;
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c, false);                     // capacity overflows settled; the flatten below is queued
+    if (rc != SRB_OK) return rc;                           // behind the frame's tile kernel, nobody waits for it here
     if (y1 == y0) return SRB_OK;
     const size_t n = (size_t)c->W * (y1 - y0), first = (size_t)c->W * y0;
     if (!c->copyStream) CK(c, cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));

@@ -140,11 +140,10 @@ __global__ void __launch_bounds__(kGeomBlock, 8)
 setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks, FrameParams fp,
              SrbUniforms U, const float4* __restrict__ clipIn, const float4* __restrict__ wnIn,
              RecStore recs, ClipAttr* __restrict__ clipAttrs, TriRef* __restrict__ refs, BigEntry* __restrict__ bigQ,
-             uint32_t* __restrict__ tileCount, Counters* cnt, unsigned long long* __restrict__ gkeys,
-             uint32_t* __restrict__ tileDirty) {
+             uint32_t* __restrict__ tileCount, Counters* cnt) {
     const unsigned full = 0xffffffffu;
     __shared__ TileAgg agg;
-    __shared__ uint32_t sNoCover, sDirect;
+    __shared__ uint32_t sNoCover;
     // tblocks is the live table the frustum kernel of this frame compacted (visible draws only); stride loop and
     // early first-entry load as in vertex_kernel.
     int2 blk = tblocks[blockIdx.x];
@@ -157,13 +156,12 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         continue;                                             // uniform over the CTA: the whole block is off band / off screen
 #endif
     agg_clear(agg);
-    if (threadIdx.x == 0) { sNoCover = 0u; sDirect = 0u; }
+    if (threadIdx.x == 0) sNoCover = 0u;
     __syncthreads();
     const int t = blk.y + threadIdx.x;
     SetupOut out;
     out.n = 0;
     out.nNoCover = 0;
-    out.nDirect = 0;
     out.bigMask = 0u;
     out.seq[0] = out.seq[1] = 0; out.tx[0] = out.tx[1] = 0; out.ty[0] = out.ty[1] = 0;
     if (t < d.n_triangles) {
@@ -181,7 +179,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
             int minX, maxX, minY, maxY;
             if (setup_tri(c, fp.W, fp.H, d.cull, r, minX, maxX, minY, maxY)) {
                 r.meta = (uint32_t)di;
-                accept_tri(r, 2u * (uint32_t)g, minX, maxX, minY, maxY, fp, recs, out, gkeys, tileDirty, true);
+                accept_tri(r, 2u * (uint32_t)g, minX, maxX, minY, maxY, fp, recs, out);
             }
         }
     }
@@ -206,7 +204,6 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         if (lane >= o) incl += v;
     }
     if (out.nNoCover) atomicAdd(&sNoCover, (uint32_t)out.nNoCover);      // statistics; flushed once per CTA below
-    if (out.nDirect) atomicAdd(&sDirect, (uint32_t)out.nDirect);
     const unsigned long long tot = __shfl_sync(full, incl, 31);
     if (tot) {                                                // uniform over the warp
         unsigned long long base = 0ull;
@@ -245,7 +242,6 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     __syncthreads();
     agg_flush<0>(agg, tileCount);
     if (threadIdx.x == 0 && sNoCover) atomicAdd(&cnt->nNoCover, sNoCover);
-    if (threadIdx.x == 0 && sDirect) atomicAdd(&cnt->nDirect, sDirect);
     __syncthreads();                                          // the table and sNoCover are reused by the next block
   }
 }
@@ -261,6 +257,14 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
 // so it ends as the bin's end offset).
 // ---------------------------------------------------------------------------
 constexpr uint32_t kHeavyBin = 192, kMediumBin = 32;
+// Bin splitting.  A bin of >= splitMin entries is rasterized by several CTAs, each walking partSize of its entries
+// into its own shared-memory keys and merging them into one global 256-key slice with 64-bit atomic max; the CTA
+// that finishes last (a counter per slice) resolves the tile.  The extra launch-order entries (one per part beyond
+// the first) live behind the one-per-tile entries and are launched FIRST.  At most kMaxExtra of them: partSize grows
+// with the frame's total of split entries so that they always fit.  A distant crowd puts 500-1000 triangles into
+// single tiles; one CTA walks such a bin in 128-entry chunks for 40-80 us, which is the floor of any band that owns
+// one (multi-GPU) however few tiles the band has.
+constexpr uint32_t kMaxExtra = 4096;
 constexpr int kScanIters = 16;                         // per chunk each warp scans 16 x 32 consecutive tiles
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
@@ -276,20 +280,20 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 constexpr int kScanCtas = 8;
 
 __global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
-scan_tiles_kernel(const uint32_t* __restrict__ tileCount, const uint32_t* __restrict__ tileDirty,
-                  uint32_t* __restrict__ tileStart, uint32_t* __restrict__ tileCursor, uint4* __restrict__ order,
-                  int tile0, int nTiles, Counters* cnt, uint32_t pairCap) {
+scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
+                  uint32_t* __restrict__ tileCursor, uint4* __restrict__ order, int tile0, int nTiles,
+                  Counters* cnt, uint32_t pairCap, const uint32_t splitMin, const uint32_t splitPart) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
-    __shared__ uint32_t wsum[3][32];
-    __shared__ uint32_t ctaTot[3];                      // this CTA's range totals: pairs, heavy, medium (read remotely)
+    __shared__ uint32_t wsum[4][32];
+    __shared__ uint32_t ctaTot[4];                      // this CTA's range totals: pairs, heavy, medium, entries of split bins (read remotely)
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int rank = (int)cluster.block_rank();
     const int per = (((nTiles + kScanCtas - 1) / kScanCtas) + 31) & ~31;
     const int r0 = min(tile0 + rank * per, tile0 + nTiles), r1 = min(r0 + per, tile0 + nTiles);
     // phase 1: totals of this CTA's range
-    uint32_t ns = 0, nh = 0, nm = 0;
+    uint32_t ns = 0, nh = 0, nm = 0, nsp = 0;
     for (int i0 = r0 + (int)threadIdx.x; i0 < r1; i0 += 4 * 1024) {
         uint32_t c[4];
 #pragma unroll
@@ -299,24 +303,28 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, const uint32_t* __rest
             ns += c[u];
             nh += c[u] >= kHeavyBin;
             nm += (c[u] >= kMediumBin && c[u] < kHeavyBin);
+            nsp += (splitMin != 0u && c[u] >= splitMin) ? c[u] : 0u;
         }
     }
-    ns = warp_sum(ns); nh = warp_sum(nh); nm = warp_sum(nm);
-    if (lane == 0) { wsum[0][wid] = ns; wsum[1][wid] = nh; wsum[2][wid] = nm; }
+    ns = warp_sum(ns); nh = warp_sum(nh); nm = warp_sum(nm); nsp = warp_sum(nsp);
+    if (lane == 0) { wsum[0][wid] = ns; wsum[1][wid] = nh; wsum[2][wid] = nm; wsum[3][wid] = nsp; }
     __syncthreads();
     if (wid == 0) {
-        uint32_t a = warp_sum(wsum[0][lane]), b = warp_sum(wsum[1][lane]), d = warp_sum(wsum[2][lane]);
-        if (lane == 0) { ctaTot[0] = a; ctaTot[1] = b; ctaTot[2] = d; }
+        uint32_t a = warp_sum(wsum[0][lane]), b = warp_sum(wsum[1][lane]), d = warp_sum(wsum[2][lane]), e = warp_sum(wsum[3][lane]);
+        if (lane == 0) { ctaTot[0] = a; ctaTot[1] = b; ctaTot[2] = d; ctaTot[3] = e; }
     }
     cluster.sync();
-    uint32_t carry = 0, carryH = 0, carryM = 0, tp = 0, th = 0, tm = 0;
+    uint32_t carry = 0, carryH = 0, carryM = 0, tp = 0, th = 0, tm = 0, tsp = 0;
 #pragma unroll
     for (int r = 0; r < kScanCtas; ++r) {
         const uint32_t* t = cluster.map_shared_rank(ctaTot, r);
         const uint32_t a = t[0], b = t[1], d = t[2];
         if (r < rank) { carry += a; carryH += b; carryM += d; }
-        tp += a; th += b; tm += d;
+        tp += a; th += b; tm += d; tsp += t[3];
     }
+    // Entries per part: a multiple of 32, at least splitPart, and large enough that the parts beyond the first of
+    // all split bins fit kMaxExtra (sum over bins of ceil(c/ps) - 1 <= sum of c/ps).
+    const uint32_t partSize = 32u * max(max(splitPart, 32u) / 32u, (tsp + 32u * kMaxExtra - 1u) / (32u * kMaxExtra));
     cluster.sync();                                     // nobody leaves (or reuses wsum) while its totals are being read
     // phase 2: offsets and order; warp w owns kScanIters*32 consecutive tiles of each chunk
     for (int chunk = r0; chunk < r1; chunk += 1024 * kScanIters) {
@@ -344,6 +352,26 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, const uint32_t* __rest
         }
         uint32_t orest = (uint32_t)(min(wb, r1) - tile0) - oh - om;      // earlier tiles that are neither
         if (wb >= r1) continue;                            // (uniform per warp; no barrier below)
+        // Split bins: the launch-order entries of their parts beyond the first are reserved with ONE atomic per warp
+        // and chunk (a reservation per iteration below put 16 dependent L2 round trips into this latency-bound kernel).
+        uint32_t ebase = 0u;
+        if (splitMin != 0u) {
+            uint32_t mine = 0u;
+#pragma unroll
+            for (int k = 0; k < kScanIters; ++k)
+                if (c[k] >= splitMin && c[k] > partSize) mine += (c[k] + partSize - 1u) / partSize - 1u;     // c[k] == 0 past r1
+            uint32_t inc = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(full, inc, o);
+                if (lane >= o) inc += t;
+            }
+            const uint32_t tot = __shfl_sync(full, inc, 31);
+            if (tot) {                                     // uniform over the warp
+                if (lane == 31) ebase = atomicAdd(&cnt->nExtra, tot);
+                ebase = __shfl_sync(full, ebase, 31) + inc - mine;
+            }
+        }
 #pragma unroll
         for (int k = 0; k < kScanIters; ++k) {
             const int i = wb + k * 32 + lane;
@@ -357,16 +385,27 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, const uint32_t* __rest
             const bool hv = valid && c[k] >= kHeavyBin, md = valid && c[k] >= kMediumBin && !hv;
             const unsigned mh = __ballot_sync(full, hv), mm = __ballot_sync(full, md), mv = __ballot_sync(full, valid);
             const unsigned lt = (1u << lane) - 1u;
+            const uint32_t excl = run + incl - c[k];
+            uint32_t pos = 0u;
+            if (hv) pos = oh + __popc(mh & lt);
+            else if (md) pos = th + om + __popc(mm & lt);
+            else pos = th + tm + orest + __popc(mv & ~mh & ~mm & lt);
+            // Split bins: the tile's own entry becomes part 0; the index of its first extra entry doubles as the id
+            // of its key slice.
+            uint32_t w = 0u, firstEnd = excl + c[k];
+            if (splitMin != 0u && c[k] >= splitMin && c[k] > partSize) {
+                const uint32_t extra = (c[k] + partSize - 1u) / partSize - 1u;
+                w = (extra + 1u) | (ebase << 16);          // parts (<= kMaxExtra + 1) | slice (< kMaxExtra)
+                firstEnd = excl + partSize;
+                for (uint32_t q = 1; q <= extra; ++q)
+                    order[(uint32_t)nTiles + ebase + q - 1u] =
+                        make_uint4((uint32_t)i, excl + q * partSize, min(excl + (q + 1u) * partSize, excl + c[k]), w);
+                ebase += extra;
+            }
             if (valid) {
-                const uint32_t excl = run + incl - c[k];
                 tileStart[i] = excl;
                 tileCursor[i] = excl;
-                uint32_t pos;
-                if (hv) pos = oh + __popc(mh & lt);
-                else if (md) pos = th + om + __popc(mm & lt);
-                else pos = th + tm + orest + __popc(mv & ~mh & ~mm & lt);
-                // tile, bin start, bin end, "the setup kernel rasterized small triangles straight into this tile's keys"
-                order[pos] = make_uint4((uint32_t)i, excl, excl + c[k], __ldg(tileDirty + i));
+                order[pos] = make_uint4((uint32_t)i, excl, firstEnd, w);      // tile, bin start, bin end, split info
             }
             run += __shfl_sync(full, incl, 31);
             oh += __popc(mh); om += __popc(mm); orest += __popc(mv & ~mh & ~mm);

@@ -201,31 +201,24 @@ __device__ __forceinline__ float ord2f(uint32_t o) {
 // ---- per-pixel winner keys of the visibility path ----
 // MODE: 0 LessEqual (max depth, later wins ties), 1 Less (max, earlier wins),
 //       2 GreaterEqual (min, later wins), 3 Greater (min, earlier wins).
-// Low word: 2*seq + direct, ordered like seq.  `direct` marks a triangle that was rasterized by the setup kernel
-// straight into the global key buffer and has no setup record (the resolve step rebuilds it from the mesh).
-// A valid key is never 0: 0 is the "nothing here" value of the global key buffer in every mode.
-__device__ __forceinline__ unsigned long long make_key_rt(int mode, float depth, uint32_t seq, uint32_t direct) {
+// A valid key is never 0 (low word >= 1 in the even modes, depth bits never all-zero with ~seq in the odd ones
+// for any seq < 2^31 - 1): 0 is the "nothing here" value of the global key slices of split bins.
+template <int MODE>
+__device__ __forceinline__ unsigned long long make_key(float depth, uint32_t seq) {
     uint32_t hi = f2ord(depth);
-    if (mode >= 2) hi = ~hi;
-    const uint32_t ord = 2u * seq + direct;
-    const uint32_t lo = (mode & 1) ? (0xfffffffeu - ord) : (ord + 1u);
+    if (MODE >= 2) hi = ~hi;
+    const uint32_t lo = (MODE & 1) ? (0xfffffffeu - seq) : (seq + 1u);
     return ((unsigned long long)hi << 32) | lo;
 }
-__device__ __forceinline__ unsigned long long clear_key_rt(int mode) {
+template <int MODE>
+__device__ __forceinline__ unsigned long long clear_key() {
     uint32_t hi = f2ord(kClearDepth);
-    if (mode >= 2) hi = ~hi;
-    const uint32_t lo = (mode & 1) ? 0xffffffffu : 0u;
+    if (MODE >= 2) hi = ~hi;
+    const uint32_t lo = (MODE & 1) ? 0xffffffffu : 0u;
     return ((unsigned long long)hi << 32) | lo;
 }
 template <int MODE>
-__device__ __forceinline__ unsigned long long make_key(float depth, uint32_t seq, uint32_t direct = 0u) {
-    return make_key_rt(MODE, depth, seq, direct);
-}
-template <int MODE>
-__device__ __forceinline__ unsigned long long clear_key() { return clear_key_rt(MODE); }
-// seq and the direct flag of a winner key.
-template <int MODE>
-__device__ __forceinline__ uint32_t key_ord(unsigned long long key) {
+__device__ __forceinline__ uint32_t key_seq(unsigned long long key) {
     const uint32_t lo = (uint32_t)key;
     return (MODE & 1) ? (0xfffffffeu - lo) : (lo - 1u);
 }

@@ -19,9 +19,6 @@ struct FrameParams {
     int loadColor, loadDepth;     // 1 = keep existing framebuffer contents (no clear this frame)
     int depthMode;                // visibility path: the frame's common depth test
     int wireframe;                // Rasterizer.RenderDebugMode == Wireframe (Rasterizer.cs:419-425): ordered path only
-    int directSmall;              // visibility path: unclipped triangles of <= kDirectPx x kDirectPx pixels are rasterized
-                                  // by the setup kernel straight into the global key buffer (no record, no bin entry)
-    int visMode;                  // winner-key mode of the visibility path (make_key_rt)
 };
 
 // Device-side counters of one frame.
@@ -39,7 +36,7 @@ struct Counters {
     uint32_t _gap[23];
     uint32_t nNoCover;            // small triangles dropped because they provably cover no pixel
     uint32_t nVLive, nTLive;      // live entries of the compacted vertex / triangle block tables (frustum kernel)
-    uint32_t nDirect;             // triangles rasterized by the setup kernel itself (direct path), >= 1 pixel covered
+    uint32_t nExtra;              // launch-order entries of split bins beyond the one-per-tile entries (scan kernel)
     uint32_t _pad1[28];
 };
 static_assert(sizeof(Counters) == 256, "Counters layout");
@@ -192,23 +189,14 @@ __device__ __forceinline__ bool block_outside(const DrawRec& d, int block) {
 // (Measured, no effect on the 12 us stage: eight lanes per draw with one frustum plane each.)
 // Also compacts the block tables: every draw that survives appends its runs of kGeomBlock vertices / triangles to the
 // live tables, so that the vertex and setup kernels spend no CTA on culled draws (city4k: 63 % of the blocks).
-// Also writes the draw of every kTri2Draw-th global triangle (culled draws included): the resolve step of the tile
-// kernel finds the draw of a directly rasterized winner from it (one load and a short walk instead of a search).
-constexpr int kTri2DrawShift = 6;
 __global__ void frustum_draws_kernel(DrawRec* draws, int nDraws, int fma, Counters* cnt, int W, int H, int bandRow0,
-                                     int bandRow1, int tilesY, int2* __restrict__ vLive, int2* __restrict__ tLive,
-                                     int32_t* __restrict__ tri2draw) {
+                                     int bandRow1, int tilesY, int2* __restrict__ vLive, int2* __restrict__ tLive) {
     // One warp per draw: every lane repeats the (broadcast-load) sphere tests, lane 0 owns the writes and the
     // reservations, and the 32 lanes write the draw's table entries together (one thread per draw writing them in
     // series cost 3 us on a single 50k-triangle draw).
     const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (i >= nDraws) return;                                   // uniform over the warp
     DrawRec& d = draws[i];
-    if (tri2draw != nullptr && d.n_triangles > 0) {
-        const int step = 1 << kTri2DrawShift;
-        const int k0 = (d.tbase + step - 1) >> kTri2DrawShift, k1 = (d.tbase + d.n_triangles - 1) >> kTri2DrawShift;
-        for (int k = k0 + lane; k <= k1; k += 32) tri2draw[k] = i;
-    }
     int vis = 1;
     if (d.flags & SRB_DRAW_FRUSTUM_CULL) {
         vis = fma ? sphere_in_frustum<true>(d.sphere, d.model, d.view, d.proj)
@@ -347,8 +335,7 @@ struct BinGeom {
 };
 struct SetupOut {
     int n;                 // accepted triangles of this thread (0..2)
-    int nNoCover;          // triangles dropped by small_tri_may_cover or found empty by the direct path (statistics only)
-    int nDirect;           // triangles rasterized by the direct path (statistics only)
+    int nNoCover;          // triangles dropped by small_tri_may_cover (statistics only)
     uint32_t seq[2];
     uint32_t tx[2], ty[2]; // packed tile ranges
     uint32_t bigMask;      // bit k: triangle k spans more than kSmallTiles tiles (goes to the large-triangle queue)
@@ -361,74 +348,17 @@ struct __align__(16) BigEntry {
     uint32_t seq, tx, ty, _pad;
 };
 static_assert(sizeof(BigEntry) == 48, "BigEntry is read as three float4");
-// ---------------------------------------------------------------------------
-// Direct path (visibility pipeline only).  A triangle whose clamped pixel bbox is at most kDirectPx x kDirectPx is
-// rasterized here, by the setup thread that owns it: the reference's walk (Rasterizer.cs:462-535) replayed per tile
-// of its bbox -- row base by the direct formula at the tile-clipped start pixel, one rounded add per x and per y
-// step, the inclusive test, depth -- and every covered pixel raises the 64-bit winner key of that pixel in a global
-// key buffer (tile-major: 256 keys per 16x16 tile) with one atomic max.  Such a triangle gets no setup record, no
-// list entry and no bin entry; the tile kernel starts a tile that received direct fragments (tileDirty) from the
-// buffer's keys instead of the clear key.  Same device functions as the tile kernel's walk, hence the same bits.
-// Why: a distant mesh puts hundreds of 1-3 pixel triangles into one tile; as records (80 B) + bin entries they cost
-// more memory traffic than the pixels they produce and make the one CTA that owns the tile the tail of the frame.
-// ---------------------------------------------------------------------------
-#ifndef SRB_DIRECT_PX
-#define SRB_DIRECT_PX 4
-#endif
-constexpr int kDirectPx = SRB_DIRECT_PX;
-__device__ __forceinline__ bool direct_raster(const TriRec& r, const uint32_t seq, const int minX, const int maxX,
-                                              const int minY, const int maxY, const int tyFirst, const int tyLast,
-                                              const FrameParams& fp, unsigned long long* __restrict__ gkeys,
-                                              uint32_t* __restrict__ tileDirty) {
-    const TriEq e = tri_eq(r);
-    const unsigned long long ckey = clear_key_rt(fp.visMode);
-    bool any = false;
-    for (int tY = tyFirst; tY <= tyLast; ++tY) {
-        const int py0 = tY * kTile;
-        const int startY = max(minY, py0), endY = min(maxY, py0 + kTile - 1);
-        for (int tX = minX / kTile; tX <= maxX / kTile; ++tX) {
-            const int px0 = tX * kTile;
-            const int startX = max(minX, px0), endX = min(maxX, px0 + kTile - 1);
-            float w0, w1, w2;
-            row_base(r, e, startX, startY, w0, w1, w2);                         // :481-483
-            const int tile = tY * fp.tilesX + tX;
-            unsigned long long* tk = gkeys + (size_t)tile * (kTile * kTile);
-            bool anyT = false;
-            for (int y = startY; y <= endY; ++y) {
-                float a0 = w0, a1 = w1, a2 = w2;
-                for (int x = startX; x <= endX; ++x) {
-                    if (inside3_minmax(a0, a1, a2)) {                           // :493-494 (a NaN edge value: NaN depth below)
-                        float w0f, w1f, w2f;
-                        const float depth = frag_depth(r.d0, r.d1, r.d2, e.invArea, a0, a1, a2, w0f, w1f, w2f);
-                        const unsigned long long key = make_key_rt(fp.visMode, depth, seq, 1u);
-                        if (depth == depth && key > ckey) {                     // a key <= the clear key can never win
-                            atomicMax(tk + (y & (kTile - 1)) * kTile + (x & (kTile - 1)), key);
-                            anyT = true;
-                        }
-                    }
-                    a0 = add(a0, e.a12); a1 = add(a1, e.a20); a2 = add(a2, e.a01);      // :527-529
-                }
-                w0 = add(w0, e.b12); w1 = add(w1, e.b20); w2 = add(w2, e.b01);          // :532-534
-            }
-            if (anyT) tileDirty[tile] = 1u;                                     // every writer stores the same value
-            any = any || anyT;
-        }
-    }
-    return any;
-}
-
-// Common tail of the accepted-triangle paths: band clamp, direct path or no-coverage test, record store.
+// Common tail of the accepted-triangle paths: band clamp, no-coverage test, record store.
+// (Measured and rejected, round 2: rasterizing unclipped triangles of <= 4x4 or <= 8x8 px right here, one global
+// 64-bit atomicMax per covered pixel into a per-pixel key buffer, no record / list / bin entry, winners rebuilt from
+// the mesh in the resolve step.  Bit-exact, but slower everywhere: city4k 5,740 -> 5,260 / 4,830 frames/s, stress8k
+// 499 -> 291 / 430 -- the setup warp serialises on its few small-triangle lanes, the global atomics cost more than
+// the 80-byte records they replace, and rebuilding a winner is a chain of five dependent gathers per pixel.
+// profiles/r02a_*_directpath_experiment.json.)
 __device__ __forceinline__ void accept_tri(const TriRec& r, uint32_t seq, int minX, int maxX, int minY, int maxY,
-                                           const FrameParams& fp, const RecStore& recs, SetupOut& out,
-                                           unsigned long long* __restrict__ gkeys, uint32_t* __restrict__ tileDirty,
-                                           const bool unclipped) {
+                                           const FrameParams& fp, const RecStore& recs, SetupOut& out) {
     const int ty0 = max(minY / kTile, fp.bandRow0), ty1 = min(maxY / kTile, fp.bandRow1 - 1);
     if (ty0 > ty1) return;
-    if (fp.directSmall && unclipped && maxX - minX < kDirectPx && maxY - minY < kDirectPx) {
-        if (direct_raster(r, seq, minX, maxX, minY, maxY, ty0, ty1, fp, gkeys, tileDirty)) ++out.nDirect;
-        else ++out.nNoCover;                        // exact here: the reference's walk passes its test at no pixel
-        return;
-    }
 #ifndef SRB_EXP_NO_SMALLCULL
     // Triangles of a few pixels that provably pass the reference's test nowhere are dropped here: they would
     // only be walked for nothing (about 30 % of the accepted triangles of the city scene).
@@ -512,7 +442,7 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int 
         ca.draw = drawIndex;
         clipAttrs[slot] = ca;
         r.meta = 0x80000000u | slot;
-        accept_tri(r, 2u * gtri + (uint32_t)f, minX, maxX, minY, maxY, fp, recs, out, nullptr, nullptr, false);
+        accept_tri(r, 2u * gtri + (uint32_t)f, minX, maxX, minY, maxY, fp, recs, out);
     }
 }
 

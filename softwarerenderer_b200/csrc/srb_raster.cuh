@@ -233,26 +233,8 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
     }
 }
 
-// Setup record of a directly rasterized triangle (fan 0 of an unclipped triangle), rebuilt from the mesh for the
-// resolve step: the draw from the tri2draw table, then the same setup_tri the setup kernel ran on the same clip
-// positions -- the same bits.  The triangle was accepted there, so cull state and rejections need no second look.
-__device__ __forceinline__ TriRec rebuild_rec(const RasterArgs& A, const FrameParams& fp, const uint32_t seq) {
-    const int g = (int)(seq >> 1);
-    int di = __ldg(A.tri2draw + (g >> kTri2DrawShift));
-    while (g >= A.draws[di].tbase + A.draws[di].n_triangles) ++di;       // short: draws of fewer than 64 triangles in between
-    const DrawRec& d = A.draws[di];
-    const int t = g - d.tbase;
-    const int i0 = (int)__ldg(d.idx + 3 * t), i1 = (int)__ldg(d.idx + 3 * t + 1), i2 = (int)__ldg(d.idx + 3 * t + 2);
-    const float4 c[3] = {A.clip[d.vbase + i2], A.clip[d.vbase + i1], A.clip[d.vbase + i0]};     // :367 order {v2,v1,v0}
-    TriRec r;
-    int minX, maxX, minY, maxY;
-    setup_tri(c, fp.W, fp.H, SRB_CULL_NONE, r, minX, maxX, minY, maxY);
-    r.meta = (uint32_t)di;
-    return r;
-}
-
-template <int MODE, bool OUT8, bool DIRECT>
-__device__ __forceinline__ void vis_resolve(const unsigned long long* keys, const unsigned long long ckey, const bool dirty,
+template <int MODE, bool OUT8>
+__device__ __forceinline__ void vis_resolve(const unsigned long long* keys, const unsigned long long ckey,
                                             const int tx0, const int ty0, const float4 clearCol, const RasterArgs& A,
                                             const FrameParams& fp, const SrbUniforms& U) {
     for (int p = threadIdx.x; p < kTile * kTile; p += kVisThreads) {
@@ -268,10 +250,9 @@ __device__ __forceinline__ void vis_resolve(const unsigned long long* keys, cons
         if (key != ckey) {
 #endif
             uint32_t hi = (uint32_t)(key >> 32);
-            const uint32_t ord = key_ord<MODE>(key), seq = ord >> 1;
-            if (((ord & 1u) != 0u) != DIRECT) continue;                 // the other pass's pixel (never taken in a clean tile)
+            const uint32_t seq = key_seq<MODE>(key);
             if (MODE >= 2) hi = ~hi;
-            const TriRec r = DIRECT ? rebuild_rec(A, fp, seq) : load_rec(A.recs, seq);
+            const TriRec r = load_rec(A.recs, seq);
             const TriEq e = tri_eq(r);
             const int startX = max(e.minX, tx0), startY = max(e.minY, ty0);
             float w0, w1, w2, w0f, w1f, w2f;
@@ -283,8 +264,6 @@ __device__ __forceinline__ void vis_resolve(const unsigned long long* keys, cons
             // the blend destination is immaterial at 8 bits; use the clear colour.
             outc = blend_px(c, clearCol, A.draws[di].blend);
             outd = ord2f(hi);
-        } else if (DIRECT) {
-            continue;                                                   // clear pixels were written by the first pass
         }
         const size_t pidx = (size_t)y * fp.W + x;
         __stcs(A.colorOut + pidx, outc);
@@ -298,6 +277,7 @@ struct VisSmem {
                                                 // unpadded 128-byte row pitch would put them all on the same two banks
     float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
     int warpRows[kVisWarps];
+    int last;                              // split bins: this CTA merged last and resolves the tile
     unsigned short items[kVisThreads * kTile];   // (triangle slot | row << 8) per work item of the chunk
 #ifdef SRB_TILE_TIMING
     unsigned long long phase[2];           // diagnostic: time after the first chunk's load+scan, time before resolve
@@ -313,8 +293,8 @@ template <int MODE, bool OUT8>
 #define SRB_BE be
 #endif
 __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t bs, const uint32_t SRB_BE,
-                                                 const bool dirty, const RasterArgs& A, const FrameParams& fp,
-                                                 const SrbUniforms& U, VisSmem& sm) {
+                                                 const uint32_t parts, const uint32_t slice, const RasterArgs& A,
+                                                 const FrameParams& fp, const SrbUniforms& U, VisSmem& sm) {
     unsigned long long* keys = sm.keys;
     float (*S)[kVisThreads] = sm.S;
     int* warpRows = sm.warpRows;
@@ -328,7 +308,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
 #ifdef SRB_EXP_ALL_EMPTY                         /* diagnostic builds only: every tile takes the clear-only path */
     if (true) {
 #else
-    if (bs == SRB_BE && !dirty) {
+    if (bs == SRB_BE) {
 #endif
 #ifdef SRB_EXP_SKIP_EMPTY
         return;
@@ -350,19 +330,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     const uint32_t be = min(be_, bs + (uint32_t)SRB_EXP_CAP_BIN);
 #endif
     const unsigned long long ckey = clear_key<MODE>();
-    if (dirty) {
-        // The setup kernel rasterized small triangles straight into this tile's slice of the global key buffer
-        // (direct_raster): start from those keys and hand the slice back empty for the frame after next.
-        unsigned long long* gk = A.gkeys + (size_t)tile * (kTile * kTile);
-        for (int i = tid; i < kTile * kTile; i += kVisThreads) {
-            const unsigned long long k = gk[i];
-            gk[i] = 0ull;
-            keys[(i >> 4) * kKeyPitch + (i & 15)] = max(k, ckey);
-        }
-    } else {
-        for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
-    }
-    if (bs == SRB_BE) __syncthreads();              // no chunk loop below: its barriers are what orders the key init otherwise
+    for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
 
     for (uint32_t cb = bs; cb < be; cb += kVisThreads) {
         // ---- one triangle per thread: derive its raster constants for this tile ----
@@ -439,11 +407,30 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
 #ifdef SRB_TILE_TIMING
     if (tid == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(sm.phase[1]));
 #endif
-    // ---- resolve: shade each pixel's winner once, write colour + depth.  Winners of the direct path (no setup
-    // record: rebuilt from the mesh) are left to a second pass that only dirty tiles run, so that the rebuild's
-    // registers do not weigh on the common loop. ----
-    vis_resolve<MODE, OUT8, false>(keys, ckey, dirty, tx0, ty0, clearCol, A, fp, U);
-    if (dirty) vis_resolve<MODE, OUT8, true>(keys, ckey, dirty, tx0, ty0, clearCol, A, fp, U);
+    if (parts > 1u) {
+        // One of several CTAs of a split bin: merge this part's keys into the bin's global slice; whoever arrives
+        // last takes the merged keys back (leaving the slice and its counter zero for the next user) and resolves.
+        unsigned long long* gk = A.gkeys + (size_t)slice * (kTile * kTile);
+        for (int i = tid; i < kTile * kTile; i += kVisThreads) {
+            const unsigned long long k = keys[(i >> 4) * kKeyPitch + (i & 15)];
+            if (k != ckey) atomicMax(gk + i, k);
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) sm.last = atomicAdd(A.sliceDone + slice, 1u) == parts - 1u;
+        __syncthreads();
+        if (!sm.last) return;
+        __threadfence();
+        for (int i = tid; i < kTile * kTile; i += kVisThreads) {
+            const unsigned long long k = __ldcg(gk + i);             // written by other SMs' atomics: not through L1
+            gk[i] = 0ull;
+            keys[(i >> 4) * kKeyPitch + (i & 15)] = max(k, ckey);
+        }
+        if (tid == 0) A.sliceDone[slice] = 0u;
+        __syncthreads();
+    }
+    // ---- resolve: shade each pixel's winner once, write colour + depth ----
+    vis_resolve<MODE, OUT8>(keys, ckey, tx0, ty0, clearCol, A, fp, U);
 }
 
 #ifndef SRB_VIS_MINBLOCKS
@@ -463,15 +450,18 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     // included, M = 2..8: raster 115 -> 117..124 us.)
     // One load gives the tile and its bin range.  (Measured and rejected: clearing the frame on a second
     // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
-    const uint4 o = __ldg(A.order + blockIdx.x);
+    // The extra entries of split bins (heavy work, behind the one-per-tile entries in memory) are launched first.
+    const bool extra = blockIdx.x < kMaxExtra;
+    const uint4 o = __ldg(A.order + (extra ? (uint32_t)A.bandTiles + blockIdx.x : blockIdx.x - kMaxExtra));
     if (A.cnt->overflow) return;
+    if (extra && blockIdx.x >= A.cnt->nExtra) return;       // unused slot (stale entry of an earlier frame)
 #ifdef SRB_TILE_TIMING
     unsigned long long t0, t1;
     unsigned smid;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
 #endif
-    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, o.w != 0u, A, fp, U, sm);
+    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, o.w & 0xffffu, o.w >> 16, A, fp, U, sm);
 #ifdef SRB_TILE_TIMING
     __syncthreads();
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));

@@ -8,9 +8,10 @@ namespace srb {
 // Everything the tile kernels need to reach per-frame data.
 struct RasterArgs {
     const DrawRec* draws;
-    const float4* clip;           // clip positions from vertex_kernel (the resolve step rebuilds direct winners from them)
-    const int32_t* tri2draw;      // draw of every 2^kTri2DrawShift-th global triangle (frustum kernel)
-    unsigned long long* gkeys;    // global winner keys of the direct path, 256 per tile, 0 = nothing (read and reset per tile)
+    unsigned long long* gkeys;    // key slices of split bins: 256 winner keys each, 0 = nothing; the CTAs of a split bin
+                                  // merge into one with atomic max, the last one reads it back and zeroes it again
+    uint32_t* sliceDone;          // per slice: parts that have merged so far (reset by the last one)
+    int bandTiles;                // one-per-tile launch-order entries; the extra entries of split bins follow them
     const float4* wn;             // world normals from vertex_kernel
     RecStore recs;
     const ClipAttr* clipAttrs;

