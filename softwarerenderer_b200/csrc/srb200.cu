@@ -85,23 +85,33 @@ struct SrbContext {
     FrameParams fp;
     bool useVis = false;
     int visMode = 0;
-    DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels: (draw, first element) of every run of
-                                      // kGeomBlock vertices / triangles of a VISIBLE draw, compacted per frame by the frustum kernel
     int nVBlocks = 0, nTBlocks = 0;
-    DevBuf<float4> dClip;
-    DevBuf<TriRef> dRefs;
-    DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
-    DevBuf<uint32_t> dTileCount, dBinScratch;
+    DevBuf<uint32_t> dBinScratch;
     unsigned long long* dSliceKeys = nullptr;   // key slices of split bins (kMaxExtra x 256), all zero between tile kernels
     uint32_t* dSliceDone = nullptr;             // per slice: parts merged so far, zero between tile kernels
     // Bins of >= splitMin entries are rasterized by several CTAs of splitPart entries each (srb_set_bin_split).
     // A full frame is bound by the sum of its tiles, not by the longest one, and splitting costs a merge, so it
     // starts late there; a band's floor IS its heaviest tile.
-    uint32_t splitMinFull = 1024, splitMinBand = 256, splitPart = 128;
-    // Frame pipelining: the geometry stages of frame N+1 run on their own stream while the tile kernel of
-    // frame N is still running on `stream`.  Everything the tile kernel reads and the geometry stages write
-    // exists twice; frames alternate between the two sets.
+    uint32_t splitMinFull = 0, splitMinBand = 128, splitPart = 64;
+    // Frame pipelining: the geometry stages of the next frames run on their own streams while the tile kernel of
+    // frame N is still running on `stream`.  Everything a frame's stages write exists once per SET; frames take the
+    // sets in turn, each set has its own geometry stream, and a set is reused when the tile kernel of its previous
+    // frame is done.  With two sets the geometry of frame N+1 overlaps the tile kernel of frame N; with more, the
+    // geometry chains of consecutive frames -- dependent, latency-bound launches that leave most of the machine idle --
+    // also overlap each other, which is what a band context with a short tile kernel needs (srb_set_pipeline_depth).
+    static constexpr int kMaxSets = 4;
+    static constexpr int nSets = kMaxSets;    // every set is allocated; `depth` says how many take turns
+    int pipeDepth = 0;                        // 0 = chosen per frame (launch_frame), else 2..4
     struct FrameBufs {
+        cudaStream_t geomStream = nullptr;
+        cudaEvent_t geomDone = nullptr, rasterDone = nullptr, geomStarted = nullptr;
+        bool rasterRecorded = false;
+        DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels: (draw, first element) of every run of
+                                          // kGeomBlock vertices / triangles of a VISIBLE draw, compacted per frame by the frustum kernel
+        DevBuf<float4> dClip;             // clip positions (vertex stage -> setup)
+        DevBuf<TriRef> dRefs;             // accepted triangles (setup -> fill)
+        DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
+        DevBuf<uint32_t> dCntTiles;       // [64 words: Counters][per-tile counts]: one memset per frame clears both
         DevBuf<DrawRec> dDraws;           // this set's copy of the draw table (the frustum kernel writes into it)
         uint64_t tableSerial = 0;         // which frame's table it holds
         DevBuf<float4> dWn;               // world normals (vertex stage -> shading)
@@ -109,15 +119,14 @@ struct SrbContext {
         DevBuf<ClipAttr> dClipAttrs;
         DevBuf<uint32_t> dTileStart, dTileCursor, dBins;
         DevBuf<uint4> dOrder;             // tile launch order of the visibility kernel
-        Counters* dCnt = nullptr;
-        Counters* hCnt = nullptr;         // pinned; copied right after the scan kernel (every counter is final by then)
+        Counters* dCnt = nullptr;         // = dCntTiles.p
+        uint32_t* dTileCount = nullptr;   // = dCntTiles.p + 64
+        Counters* hCnt = nullptr;         // pinned; written by the scan kernel itself (every counter is final by then)
         cudaEvent_t cntReady = nullptr;   // ... and this event follows the copy: the host learns about a capacity
                                           // overflow when the frame's GEOMETRY is done, not its rasterization
-    } fb[2];
+    } fb[kMaxSets];
     int slot = 0;                         // set used by the most recently launched frame
-    cudaStream_t geomStream = nullptr, lastGeomStream = nullptr;
-    cudaEvent_t geomDone[2] = {}, rasterDone[2] = {};
-    bool rasterRecorded[2] = {false, false};
+    cudaStream_t lastGeomStream = nullptr;
     uint64_t frameSerial = 0;             // bumped by every srb_end_frame: the draw table in hDraws[tableSlot]
     int tableSlot = 0;
     DrawRec* hDraws[2] = {nullptr, nullptr};   // pinned staging of the draw table, two alternating buffers
@@ -183,6 +192,19 @@ int alloc_framebuffer(SrbContext* c, int w, int h) {
     return SRB_OK;
 }
 
+// Frame-dependent capacities are the smallest over the sets in use.
+void refresh_caps(SrbContext* c) {
+    size_t pairs = ~(size_t)0, clips = ~(size_t)0, big = ~(size_t)0;
+    for (int i = 0; i < c->nSets; ++i) {
+        pairs = std::min(pairs, c->fb[i].dBins.cap);
+        clips = std::min(clips, c->fb[i].dClipAttrs.cap);
+        big = std::min(big, c->fb[i].dBigQ.cap);
+    }
+    c->fp.pairCap = (uint32_t)std::min<size_t>(pairs, 0xffffffffu);
+    c->fp.clipCap = (uint32_t)std::min<size_t>(clips, 0xffffffffu);
+    c->fp.bigCap = (uint32_t)std::min<size_t>(big, 0xffffffffu);
+}
+
 // Launch the whole pipeline for the resident draw list.
 int launch_frame(SrbContext* c) {
     FrameParams& fp = c->fp;
@@ -204,19 +226,32 @@ int launch_frame(SrbContext* c) {
     const int floorCtas = c->smCount * 16;
     const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, std::max<int>(floorCtas, (int)(prevV + prevV / 8 + 16))) : c->nVBlocks);
     const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, std::max<int>(floorCtas, (int)(prevT + prevT / 8 + 16))) : c->nTBlocks);
-    const int s = c->slot ^ 1;
+    // Frames in flight.  A frame whose tile kernel outlasts its geometry chain gains nothing from more than two sets
+    // (measured, city4k: 5,950 frames/s with 2, 5,800 with 4 -- more geometry kernels beside the tile kernel only
+    // take SMs from it); a frame with a short tile kernel is bound by the LATENCY of its chain of geometry launches,
+    // and overlapping those chains is all there is to gain (gun1080: 17,600 -> 29,300; one tile row of city4k:
+    // 14,400 -> 21,500).  The tile kernel's time is estimated from the last frame's counters.
+    int depthNow = c->pipeDepth;
+    if (depthNow == 0) {
+        const float estTileUs = 0.9e-3f * (float)bandTiles + 0.26e-3f * (float)c->fb[c->slot].hCnt->nPairs;
+        depthNow = estTileUs < 70.0f ? 4 : 2;
+    }
+    const int sPrev = c->slot;
+    const int s = (c->slot + 1) % depthNow;
     c->slot = s;
     SrbContext::FrameBufs& B = c->fb[s];
     // geometry + binning stream; the tile kernel stays on c->stream.  Stage profiling runs everything on
     // c->stream: the per-stage events then bracket kernels only, not cross-stream hand-overs.
-    cudaStream_t gs = c->profiling ? c->stream : c->geomStream;
+    cudaStream_t gs = c->profiling ? c->stream : B.geomStream;
     auto mark = [&](int next) {       // close stages [stage, next) at this point of the pipeline
         if (!c->profiling) return;
         for (; stage < next; ++stage) cudaEventRecord(c->stageEv[stage + 1], stage + 1 <= 5 ? gs : c->stream);
     };
-    if (c->rasterRecorded[s]) CK(c, cudaStreamWaitEvent(gs, c->rasterDone[s], 0));   // the frame before last used this set
-    if (c->lastGeomStream && c->lastGeomStream != gs)       // profiling toggled: keep the single-copy geometry buffers serial
-        CK(c, cudaStreamWaitEvent(gs, c->geomDone[s ^ 1], 0));
+    if (B.rasterRecorded) CK(c, cudaStreamWaitEvent(gs, B.rasterDone, 0));   // this set's previous frame
+    // Geometry chains start in frame order (a later frame's short kernels must not take the SMs from an earlier
+    // frame's): behind the previous frame's frustum kernel, not behind its whole chain.
+    if (c->lastGeomStream && c->lastGeomStream != gs && c->fb[sPrev].geomStarted)
+        CK(c, cudaStreamWaitEvent(gs, c->fb[sPrev].geomStarted, 0));
     c->lastGeomStream = gs;
     CK(c, cudaEventRecord(c->ev0, gs));
     if (B.tableSerial != c->frameSerial && fp.nDraws > 0) {
@@ -227,38 +262,43 @@ int launch_frame(SrbContext* c) {
         c->stagingBusy[c->tableSlot] = true;
     }
     B.tableSerial = c->frameSerial;
-    CK(c, cudaMemsetAsync(B.dCnt, 0, sizeof(Counters), gs));
-    CK(c, cudaMemsetAsync(c->dTileCount.p, 0, (size_t)nTiles * sizeof(uint32_t), gs));
+    CK(c, cudaMemsetAsync(B.dCntTiles.p, 0, (64 + (size_t)nTiles) * sizeof(uint32_t), gs));
     if (c->profiling) cudaEventRecord(c->stageEv[0], gs);
     if (fp.nDraws > 0) {
         frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(B.dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
-                                                                                fp.bandRow1, fp.tilesY, c->dVBlocks.p, c->dTBlocks.p);
+                                                                                fp.bandRow1, fp.tilesY, B.dVBlocks.p, B.dTBlocks.p);
         ++launches;
     }
+    CK(c, cudaEventRecord(B.geomStarted, gs));
     mark(1);
     if (c->nVBlocks > 0) {
         if (U.numerics_fma)
-            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
+            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, B.dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
         else
-            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, c->dVBlocks.p, B.dCnt, c->dClip.p, B.dWn.p);
+            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, B.dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
         ++launches;
     }
     mark(2);
     if (c->nTBlocks > 0) {
         setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
-            B.dDraws.p, c->dTBlocks.p, fp, U, c->dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, c->dRefs.p, c->dBigQ.p,
-            c->dTileCount.p, B.dCnt);
-        bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, c->dTileCount.p, nullptr);
+            B.dDraws.p, B.dTBlocks.p, fp, U, B.dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, B.dRefs.p, B.dBigQ.p,
+            B.dTileCount, B.dCnt);
+        bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCount, nullptr);
         launches += 2;
     }
     mark(3);
     if (bandTiles > 0) {
-        scan_tiles_kernel<<<kScanCtas, 1024, 0, gs>>>(c->dTileCount.p, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p,
-                                                     fp.bandRow0 * fp.tilesX, bandTiles, B.dCnt, fp.pairCap,
-                                                     c->useVis ? (fullFrame ? c->splitMinFull : c->splitMinBand) : 0u, c->splitPart);
+        const uint32_t splitMin = c->useVis ? (fullFrame ? c->splitMinFull : c->splitMinBand) : 0u;
+        if (splitMin)
+            scan_tiles_kernel<true><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
+                                                               bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt);
+        else
+            scan_tiles_kernel<false><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
+                                                                bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt);
         ++launches;
+    } else {
+        publish_counters_kernel<<<1, sizeof(Counters) / 4, 0, gs>>>(B.dCnt, (uint32_t*)B.hCnt);
     }
-    CK(c, cudaMemcpyAsync(B.hCnt, B.dCnt, sizeof(Counters), cudaMemcpyDeviceToHost, gs));
     CK(c, cudaEventRecord(B.cntReady, gs));
     mark(4);
     if (fp.totalT > 0 && bandTiles > 0) {
@@ -273,18 +313,18 @@ int launch_frame(SrbContext* c) {
         // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
         // bins up to order, which no consumer depends on).
         if (prevBig > 0 && prevRefs <= (fullFrame ? 16384u : wave * 256u)) {
-            fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(c->dRefs.p, c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
+            fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(B.dRefs.p, B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
                                                                B.dBins.p, wave);
         } else {
-            fill_bins_kernel<<<grid, 256, 0, gs>>>(c->dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
-            bin_big_kernel<1><<<wave, 256, 0, gs>>>(c->dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
+            fill_bins_kernel<<<grid, 256, 0, gs>>>(B.dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
+            bin_big_kernel<1><<<wave, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
             ++launches;
         }
         ++launches;
     }
     mark(5);
-    CK(c, cudaEventRecord(c->geomDone[s], gs));
-    CK(c, cudaStreamWaitEvent(c->stream, c->geomDone[s], 0));
+    CK(c, cudaEventRecord(B.geomDone, gs));
+    CK(c, cudaStreamWaitEvent(c->stream, B.geomDone, 0));
     RasterArgs A;
     A.draws = B.dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
     A.gkeys = c->dSliceKeys; A.sliceDone = c->dSliceDone; A.bandTiles = bandTiles;
@@ -323,8 +363,8 @@ int launch_frame(SrbContext* c) {
     }
     mark(7);
     CK(c, cudaGetLastError());
-    CK(c, cudaEventRecord(c->rasterDone[s], c->stream));
-    c->rasterRecorded[s] = true;
+    CK(c, cudaEventRecord(B.rasterDone, c->stream));
+    B.rasterRecorded = true;
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->stats.kernel_launches = launches;
     c->stats.pipeline_used = c->useVis ? SRB_PIPELINE_VISIBILITY : SRB_PIPELINE_ORDERED;
@@ -346,21 +386,14 @@ int complete_frame(SrbContext* c, bool waitRaster = true) {
         const Counters& k = *c->fb[c->slot].hCnt;
         if (!k.overflow) break;
         // (cudaFree inside reserve() waits for the device: nothing is freed under a running kernel.)
-        if (k.overflow & 1u) {
-            size_t want = (size_t)k.nPairs + k.nPairs / 8 + 1024;
-            for (auto& b : c->fb) CK(c, b.dBins.reserve(want));
-            CK(c, c->dBinScratch.reserve(c->fb[0].dBins.cap));
-            c->fp.pairCap = (uint32_t)std::min<size_t>(std::min(c->fb[0].dBins.cap, c->fb[1].dBins.cap), 0xffffffffu);
+        for (int i = 0; i < c->nSets; ++i) {
+            SrbContext::FrameBufs& b = c->fb[i];
+            if (k.overflow & 1u) CK(c, b.dBins.reserve((size_t)k.nPairs + k.nPairs / 8 + 1024));
+            if (k.overflow & 2u) CK(c, b.dClipAttrs.reserve(std::max<size_t>(4 * (size_t)k.nClipped, 4096)));
+            if (k.overflow & 4u) CK(c, b.dBigQ.reserve((size_t)k.nBig + k.nBig / 4 + 1024));
         }
-        if (k.overflow & 2u) {
-            size_t want = std::max<size_t>(4 * (size_t)k.nClipped, 4096);
-            for (auto& b : c->fb) CK(c, b.dClipAttrs.reserve(want));
-            c->fp.clipCap = (uint32_t)std::min(c->fb[0].dClipAttrs.cap, c->fb[1].dClipAttrs.cap);
-        }
-        if (k.overflow & 4u) {
-            CK(c, c->dBigQ.reserve((size_t)k.nBig + k.nBig / 4 + 1024));
-            c->fp.bigCap = (uint32_t)c->dBigQ.cap;
-        }
+        if (k.overflow & 1u) CK(c, c->dBinScratch.reserve(c->fb[0].dBins.cap));
+        refresh_caps(c);
         int rc = launch_frame(c);
         if (rc != SRB_OK) return rc;
         CK(c, cudaEventSynchronize(c->fb[c->slot].cntReady));
@@ -424,17 +457,17 @@ int srb_create(int device, int width, int height, SrbContext** out_ctx) {
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail("cudaEventCreate", e);
-    {   // geometry kernels are short and latency-bound: let their CTAs go ahead of the queued tile CTAs of the previous frame
-        int lo = 0, hi = 0;
-        cudaDeviceGetStreamPriorityRange(&lo, &hi);
-        if ((e = cudaStreamCreateWithPriority(&c->geomStream, cudaStreamNonBlocking, hi)) != cudaSuccess) return bail("cudaStreamCreate", e);
-    }
-    for (int s = 0; s < 2; ++s) {
-        if ((e = cudaEventCreateWithFlags(&c->geomDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-        if ((e = cudaEventCreateWithFlags(&c->rasterDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-        if ((e = cudaEventCreateWithFlags(&c->fb[s].cntReady, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    int prioLo = 0, prioHi = 0;       // geometry kernels are short and latency-bound: let their CTAs go ahead of the queued
+    cudaDeviceGetStreamPriorityRange(&prioLo, &prioHi);     // tile CTAs of the previous frame
+    for (int s = 0; s < 2; ++s)
         if ((e = cudaEventCreateWithFlags(&c->stagingDone[s], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-        if ((e = cudaMalloc((void**)&c->fb[s].dCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMalloc", e);
+    for (int s = 0; s < SrbContext::kMaxSets; ++s) {
+        if ((e = cudaStreamCreateWithPriority(&c->fb[s].geomStream, cudaStreamNonBlocking, prioHi)) != cudaSuccess) return bail("cudaStreamCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->fb[s].geomDone, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->fb[s].geomStarted, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->fb[s].rasterDone, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->fb[s].cntReady, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+
         if ((e = cudaMallocHost((void**)&c->fb[s].hCnt, sizeof(Counters))) != cudaSuccess) return bail("cudaMallocHost", e);
         std::memset(c->fb[s].hCnt, 0, sizeof(Counters));
     }
@@ -457,25 +490,26 @@ int srb_destroy(SrbContext* c) {
     if (c->color8) cudaFree(c->color8);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
-    c->dVBlocks.release(); c->dTBlocks.release(); c->dClip.release();
+
     if (c->dSliceKeys) cudaFree(c->dSliceKeys);
     if (c->dSliceDone) cudaFree(c->dSliceDone);
     c->dRayScratch.release();
-    c->dRefs.release(); c->dBigQ.release(); c->dTileCount.release(); c->dBinScratch.release();
+    c->dBinScratch.release();
     for (auto& b : c->fb) {
         b.dDraws.release(); b.dWn.release(); b.dRecsR.release(); b.dRecsS.release(); b.dClipAttrs.release(); b.dTileStart.release();
         b.dTileCursor.release(); b.dBins.release(); b.dOrder.release();
-        if (b.dCnt) cudaFree(b.dCnt);
+        b.dVBlocks.release(); b.dTBlocks.release(); b.dClip.release(); b.dRefs.release(); b.dBigQ.release(); b.dCntTiles.release();
+        if (b.geomStream) { cudaStreamSynchronize(b.geomStream); cudaStreamDestroy(b.geomStream); }
+        if (b.geomDone) cudaEventDestroy(b.geomDone);
+        if (b.geomStarted) cudaEventDestroy(b.geomStarted);
+        if (b.rasterDone) cudaEventDestroy(b.rasterDone);
+        if (b.cntReady) cudaEventDestroy(b.cntReady);
         if (b.hCnt) cudaFreeHost(b.hCnt);
     }
     for (int s = 0; s < 2; ++s) {
-        if (c->geomDone[s]) cudaEventDestroy(c->geomDone[s]);
-        if (c->rasterDone[s]) cudaEventDestroy(c->rasterDone[s]);
-        if (c->fb[s].cntReady) cudaEventDestroy(c->fb[s].cntReady);
         if (c->stagingDone[s]) cudaEventDestroy(c->stagingDone[s]);
         if (c->hDraws[s]) cudaFreeHost(c->hDraws[s]);
     }
-    if (c->geomStream) { cudaStreamSynchronize(c->geomStream); cudaStreamDestroy(c->geomStream); }
     if (c->copyStream) { cudaStreamSynchronize(c->copyStream); cudaStreamDestroy(c->copyStream); }
     for (int s = 0; s < 2; ++s) {
         c->dPresent[s].release();
@@ -595,7 +629,7 @@ int srb_get_tile_row_pairs(SrbContext* c, uint32_t* out, int n) {
     if (!c->haveFrame) return fail(c, SRB_ERR_STATE, "no completed frame");
     const int nTiles = c->tilesX * c->tilesY;
     std::vector<uint32_t> h((size_t)nTiles);
-    CK(c, cudaMemcpy(h.data(), c->dTileCount.p, (size_t)nTiles * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    CK(c, cudaMemcpy(h.data(), c->fb[c->slot].dTileCount, (size_t)nTiles * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     for (int r = 0; r < n && r < c->tilesY; ++r) {
         uint64_t s = 0;
         for (int x = 0; x < c->tilesX; ++x) s += h[(size_t)r * c->tilesX + x];
@@ -612,6 +646,13 @@ int srb_set_bin_split(SrbContext* c, int min_entries_full_frame, int min_entries
     c->splitMinFull = (uint32_t)min_entries_full_frame;
     c->splitMinBand = (uint32_t)min_entries_band;
     c->splitPart = (uint32_t)part_entries;
+    return SRB_OK;
+}
+
+int srb_set_pipeline_depth(SrbContext* c, int sets) {
+    if (!c) return SRB_ERR_ARG;
+    if (sets != 0 && (sets < 2 || sets > SrbContext::kMaxSets)) return fail(c, SRB_ERR_ARG, "pipeline depth must be 0 (automatic) or 2..4 buffer sets");
+    c->pipeDepth = sets;
     return SRB_OK;
 }
 
@@ -887,12 +928,13 @@ int srb_end_frame(SrbContext* c) {
         default: c->visMode = 0; break;
     }
     const int nTiles = c->tilesX * c->tilesY;
-    for (auto& b : c->fb) CK(c, b.dDraws.reserve((size_t)nDraws + 1));
-    CK(c, c->dVBlocks.reserve(nVB + 1));
-    CK(c, c->dTBlocks.reserve(nTB + 1));
-    for (auto& b : c->fb) CK(c, b.dOrder.reserve((size_t)nTiles + kMaxExtra));
-    CK(c, c->dClip.reserve((size_t)totalV + 1));
-    for (auto& b : c->fb) {
+    for (int i = 0; i < c->nSets; ++i) {
+        SrbContext::FrameBufs& b = c->fb[i];
+        CK(c, b.dDraws.reserve((size_t)nDraws + 1));
+        CK(c, b.dVBlocks.reserve(nVB + 1));
+        CK(c, b.dTBlocks.reserve(nTB + 1));
+        CK(c, b.dOrder.reserve((size_t)nTiles + kMaxExtra));
+        CK(c, b.dClip.reserve((size_t)totalV + 1));
         CK(c, b.dWn.reserve((size_t)totalV + 1));
         CK(c, b.dRecsR.reserve(3 * (2 * (size_t)totalT + 2)));
         CK(c, b.dRecsS.reserve(2 * (2 * (size_t)totalT + 2)));
@@ -900,21 +942,19 @@ int srb_end_frame(SrbContext* c) {
         CK(c, b.dTileStart.reserve(nTiles));
         CK(c, b.dTileCursor.reserve(nTiles));
         CK(c, b.dBins.reserve(std::max<size_t>(1u << 20, 3 * (size_t)totalT)));
+        CK(c, b.dRefs.reserve(2 * (size_t)totalT + 64));
+        CK(c, b.dBigQ.reserve(1u << 16));
+        CK(c, b.dCntTiles.reserve(64 + (size_t)nTiles));
+        b.dCnt = reinterpret_cast<Counters*>(b.dCntTiles.p);
+        b.dTileCount = b.dCntTiles.p + 64;
     }
-    CK(c, c->dRefs.reserve(2 * (size_t)totalT + 64));
-    CK(c, c->dBigQ.reserve(1u << 16));
-    CK(c, c->dTileCount.reserve(nTiles));
-    CK(c, c->dBinScratch.reserve(std::max(c->fb[0].dBins.cap, c->fb[1].dBins.cap)));
-    c->tableSlot = hs;                // launch_frame uploads it to whichever set renders next (and to the other
-    ++c->frameSerial;                 // one when that set is first used for this frame, e.g. by srb_replay_frame)
+    CK(c, c->dBinScratch.reserve(c->fb[0].dBins.cap));
     c->nVBlocks = (int)nVB; c->nTBlocks = (int)nTB;
     FrameParams& fp = c->fp;
     fp.W = c->W; fp.H = c->H; fp.tilesX = c->tilesX; fp.tilesY = c->tilesY;
     fp.bandRow0 = c->band0; fp.bandRow1 = c->band1;
     fp.nDraws = nDraws; fp.totalV = (int)totalV; fp.totalT = (int)totalT;
-    fp.pairCap = (uint32_t)std::min<size_t>(std::min(c->fb[0].dBins.cap, c->fb[1].dBins.cap), 0xffffffffu);
-    fp.clipCap = (uint32_t)std::min(c->fb[0].dClipAttrs.cap, c->fb[1].dClipAttrs.cap);
-    fp.bigCap = (uint32_t)c->dBigQ.cap;
+    refresh_caps(c);
     std::memcpy(fp.clearColor, c->clear, 16);
     fp.loadColor = (c->clearFlags & SRB_CLEAR_COLOR) ? 0 : 1;
     fp.loadDepth = (c->clearFlags & SRB_CLEAR_DEPTH) ? 0 : 1;
@@ -923,6 +963,8 @@ int srb_end_frame(SrbContext* c) {
     c->stats.draws_submitted = nDraws;
     c->stats.triangles_submitted = totalT;
     c->haveFrame = true;
+    c->tableSlot = hs;                // launch_frame uploads the table to whichever set renders next (and to the others
+    ++c->frameSerial;                 // when they are first used for this frame, e.g. by srb_replay_frame)
     return launch_frame(c);
 }
 

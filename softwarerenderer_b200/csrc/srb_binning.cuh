@@ -279,10 +279,23 @@ __device__ __forceinline__ uint32_t warp_sum(uint32_t v) {
 // per-thread strided layout (32 sectors per instruction) would bound this kernel.
 constexpr int kScanCtas = 8;
 
+// The frame's counters are final when this kernel ends (nothing after it writes them).  It publishes them to the
+// host itself, as plain stores into mapped pinned memory: a copy-engine transfer on this stream would queue behind
+// whatever the D2H engine is doing -- the 100 MB present copy of the previous frame, for one -- and hold up the
+// rest of the frame with it.
+__global__ void publish_counters_kernel(const Counters* __restrict__ cnt, uint32_t* __restrict__ hostCnt) {
+    hostCnt[threadIdx.x] = reinterpret_cast<const uint32_t*>(cnt)[threadIdx.x];
+    __threadfence_system();
+}
+
+// SPLIT: bins may be split (visibility path); the plain instance carries none of that code.
+template <bool SPLIT>
 __global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
 scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
                   uint32_t* __restrict__ tileCursor, uint4* __restrict__ order, int tile0, int nTiles,
-                  Counters* cnt, uint32_t pairCap, const uint32_t splitMin, const uint32_t splitPart) {
+                  Counters* cnt, uint32_t pairCap, const uint32_t splitMin_, const uint32_t splitPart,
+                  uint32_t* __restrict__ hostCnt) {
+    const uint32_t splitMin = SPLIT ? splitMin_ : 0u;
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     __shared__ uint32_t wsum[4][32];
@@ -303,14 +316,16 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
             ns += c[u];
             nh += c[u] >= kHeavyBin;
             nm += (c[u] >= kMediumBin && c[u] < kHeavyBin);
-            nsp += (splitMin != 0u && c[u] >= splitMin) ? c[u] : 0u;
+            if (SPLIT) nsp += (splitMin != 0u && c[u] >= splitMin) ? c[u] : 0u;
         }
     }
-    ns = warp_sum(ns); nh = warp_sum(nh); nm = warp_sum(nm); nsp = warp_sum(nsp);
+    ns = warp_sum(ns); nh = warp_sum(nh); nm = warp_sum(nm);
+    if (SPLIT) nsp = warp_sum(nsp);
     if (lane == 0) { wsum[0][wid] = ns; wsum[1][wid] = nh; wsum[2][wid] = nm; wsum[3][wid] = nsp; }
     __syncthreads();
     if (wid == 0) {
-        uint32_t a = warp_sum(wsum[0][lane]), b = warp_sum(wsum[1][lane]), d = warp_sum(wsum[2][lane]), e = warp_sum(wsum[3][lane]);
+        uint32_t a = warp_sum(wsum[0][lane]), b = warp_sum(wsum[1][lane]), d = warp_sum(wsum[2][lane]);
+        uint32_t e = SPLIT ? warp_sum(wsum[3][lane]) : 0u;
         if (lane == 0) { ctaTot[0] = a; ctaTot[1] = b; ctaTot[2] = d; ctaTot[3] = e; }
     }
     cluster.sync();
@@ -320,7 +335,8 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
         const uint32_t* t = cluster.map_shared_rank(ctaTot, r);
         const uint32_t a = t[0], b = t[1], d = t[2];
         if (r < rank) { carry += a; carryH += b; carryM += d; }
-        tp += a; th += b; tm += d; tsp += t[3];
+        tp += a; th += b; tm += d;
+        if (SPLIT) tsp += t[3];
     }
     // Entries per part: a multiple of 32, at least splitPart, and large enough that the parts beyond the first of
     // all split bins fit kMaxExtra (sum over bins of ceil(c/ps) - 1 <= sum of c/ps).
@@ -355,7 +371,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
         // Split bins: the launch-order entries of their parts beyond the first are reserved with ONE atomic per warp
         // and chunk (a reservation per iteration below put 16 dependent L2 round trips into this latency-bound kernel).
         uint32_t ebase = 0u;
-        if (splitMin != 0u) {
+        if (SPLIT && splitMin != 0u) {
             uint32_t mine = 0u;
 #pragma unroll
             for (int k = 0; k < kScanIters; ++k)
@@ -393,7 +409,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
             // Split bins: the tile's own entry becomes part 0; the index of its first extra entry doubles as the id
             // of its key slice.
             uint32_t w = 0u, firstEnd = excl + c[k];
-            if (splitMin != 0u && c[k] >= splitMin && c[k] > partSize) {
+            if (SPLIT && splitMin != 0u && c[k] >= splitMin && c[k] > partSize) {
                 const uint32_t extra = (c[k] + partSize - 1u) / partSize - 1u;
                 w = (extra + 1u) | (ebase << 16);          // parts (<= kMaxExtra + 1) | slice (< kMaxExtra)
                 firstEnd = excl + partSize;
@@ -414,6 +430,11 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
     if (rank == 0 && threadIdx.x == 0) {
         cnt->nPairs = tp;
         if (tp > pairCap) atomicOr(&cnt->overflow, 1u);
+    }
+    cluster.sync();                                     // every CTA's reservations (nExtra) are in
+    if (rank == 0 && threadIdx.x < sizeof(Counters) / 4) {
+        hostCnt[threadIdx.x] = reinterpret_cast<volatile uint32_t*>(cnt)[threadIdx.x];
+        __threadfence_system();
     }
 }
 

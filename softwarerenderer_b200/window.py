@@ -149,6 +149,10 @@ class MainWindow:
         """Tuning only (never changes the image): bins of at least this many entries are rasterized by several CTAs."""
         N.check(self._ctx, N.lib().srb_set_bin_split(self._ctx, min_entries_full_frame, min_entries_band, part_entries))
 
+    def SetPipelineDepth(self, buffer_sets: int) -> None:
+        """Tuning only: frames in flight on the device (2..4, 0 = chosen per frame)."""
+        N.check(self._ctx, N.lib().srb_set_pipeline_depth(self._ctx, buffer_sets))
+
     def SetPipeline(self, pipeline: int) -> None:
         N.check(self._ctx, N.lib().srb_set_pipeline(self._ctx, pipeline))
 

@@ -88,3 +88,93 @@ def test_rgba8_band_gather_assembles_the_quantised_frame(tmp_path, oracle):
     oc, _, _ = oracle.render_scene(S.scene_city(1280, 720, n_instances=24), threads=8)
     d8 = np.abs(frame.astype(np.int32) - to_u8(oc)).max(axis=-1)
     assert (d8 <= 1).mean() >= 0.999 and d8.max() <= 1
+
+
+# ---------------------------------------------------------------------------
+# Real multi-GPU: one rank per DEVICE (skipped on a one-GPU box), NCCL frame barrier on the raster stream, two
+# DIFFERENT frames back to back with no host synchronisation in between -- a band rank's peer stores of frame B must
+# not reach rank 0 before rank 0 has taken frame A, and the assembled frames are compared with the ORACLE.
+# ---------------------------------------------------------------------------
+def _worker_multi(rank, world, port, out_path):
+    import torch
+    import torch.distributed as dist
+
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import _native as N
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.bands import balanced_cuts
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        a = S.scene_city(1280, 720, n_instances=24)
+        b = S.scene_model("Gun", 1280, 720, view=S.gun_camera(3))
+        win = srb.MainWindow(1280, 720, device=rank)
+        win.SetBinSplit(64, 64, 32)                               # split bins on every band rank as well
+        S.submit_scene(win, a)
+        cuts = balanced_cuts(win.TileRowPairs().astype(np.float64) + 0.85 * 80, world)
+        win.SetBand(cuts[rank], cuts[rank + 1])
+        box = [win.ExportColorHandle() if rank == 0 else None]
+        box8 = [win.ExportGatherRgba8() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        dist.broadcast_object_list(box8, src=0)
+        ext = torch.cuda.ExternalStream(N.lib().srb_stream(win._ctx), device=dev)
+        token = torch.zeros(1, device=dev)
+        got = {}
+        for fmt in ("float4", "rgba8"):
+            if rank != 0:
+                win.SetGatherRgba8Target(box8[0] if fmt == "rgba8" else None)
+                win.SetColorTarget(box[0] if fmt == "float4" else None)
+            dist.barrier()
+            snaps = []
+            with torch.cuda.stream(ext):
+                for sc in (a, b, a, b):
+                    S.submit_scene(win, sc)                       # no host sync: frames are pipelined on every rank
+                    dist.all_reduce(token)                        # every band of this frame has landed ...
+                    if rank == 0:                                 # ... rank 0 takes the frame on the same stream
+                        src = torch.as_tensor(_DevArray(N.lib().srb_device_gathered_rgba8_ptr(win._ctx), (720, 1280), "<u4") if fmt == "rgba8"
+                                              else _DevArray(N.lib().srb_device_color_ptr(win._ctx), (720, 1280, 4)), device=dev)
+                        snaps.append(src.clone())
+                    dist.all_reduce(token)                        # ... before any rank stores the next one
+            torch.cuda.synchronize(dev)
+            if rank == 0:
+                got[fmt] = [s.cpu().numpy() for s in snaps]
+        if rank == 0:
+            np.savez(out_path, cuts=np.array(cuts), **{f"{f}_{i}": x for f, xs in got.items() for i, x in enumerate(xs)})
+        dist.barrier()
+        if rank != 0:
+            win.SetGatherRgba8Target(None)
+            win.SetColorTarget(None)
+        dist.barrier()
+        win.Close()
+    finally:
+        dist.destroy_process_group()
+
+
+class _DevArray:
+    def __init__(self, ptr, shape, typestr="<f4"):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def test_bands_on_different_gpus_assemble_the_oracle_frame(tmp_path, oracle):
+    import torch
+    import torch.multiprocessing as mp
+
+    from softwarerenderer_b200 import scene as S
+    from tests.util import to_u8
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least two GPUs")
+    out = str(tmp_path / "multi.npz")
+    mp.spawn(_worker_multi, args=(world, _free_port(), out), nprocs=world, join=True)
+    z = np.load(out)
+    want = [oracle.render_scene(S.scene_city(1280, 720, n_instances=24), threads=8)[0],
+            oracle.render_scene(S.scene_model("Gun", 1280, 720, view=S.gun_camera(3)), threads=8)[0]]
+    for i in range(4):
+        o8 = to_u8(want[i & 1])
+        d8 = np.abs(to_u8(z[f"float4_{i}"]) - o8).max(axis=-1)
+        assert (d8 <= 1).mean() >= 0.999 and d8.max() <= 1, (i, "float4")
+        g8 = z[f"rgba8_{i}"].view(np.uint8).reshape(720, 1280, 4).astype(np.int32)
+        d8 = np.abs(g8 - o8).max(axis=-1)
+        assert (d8 <= 1).mean() >= 0.999 and d8.max() <= 1, (i, "rgba8")

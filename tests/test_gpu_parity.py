@@ -236,3 +236,37 @@ def test_pipelined_frames_do_not_disturb_each_other():
         assert np.array_equal(win.ColorBuffer, want_b[0]) and np.array_equal(win.DepthBuffer, want_b[1])
     finally:
         win.Close()
+
+
+@pytest.mark.parametrize("depth", [0, 2, 3, 4])
+def test_pipeline_depth_leaves_the_image_alone(oracle, depth):
+    """2..4 frames in flight (srb_set_pipeline_depth: one buffer set and one geometry stream per frame in flight):
+    bursts of replays and of alternating scenes without host synchronisation leave exactly the last frame."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import submit_scene
+    a = S.scene_city(1280, 720, n_instances=12)
+    b = S.scene_model("Gun", 1280, 720, view=S.gun_camera(4))
+    oa, ob = oracle.render_scene(a, threads=8), oracle.render_scene(b, threads=8)
+    win = srb.MainWindow(1280, 720)
+    try:
+        win.SetPipelineDepth(depth)
+        submit_scene(win, a)
+        for _ in range(11):
+            win.ReplayFrame()
+        compare(win.ColorBuffer, win.DepthBuffer, oa[0], oa[1])
+        for k in range(9):                                      # a b a b ... a, no read-back in between
+            submit_scene(win, a if k % 2 == 0 else b)
+        compare(win.ColorBuffer, win.DepthBuffer, oa[0], oa[1])
+        submit_scene(win, b)
+        for _ in range(7):
+            win.ReplayFrame()
+        compare(win.ColorBuffer, win.DepthBuffer, ob[0], ob[1])
+        win.SetBand(10, 30)                                     # a band context, deeper pipeline, split bins
+        win.SetBinSplit(64, 64, 32)
+        submit_scene(win, a)
+        for _ in range(9):
+            win.ReplayFrame()
+        assert np.array_equal(win.DepthBuffer[160:480], oa[1][160:480])
+    finally:
+        win.Close()

@@ -19,10 +19,11 @@ r0, r1 = int(sys.argv[1]), int(sys.argv[2])
 wl = sys.argv[3] if len(sys.argv) > 3 else "city4k"
 scene = bench.build_scene(wl)
 L = N.lib()
-for split in ((0, 0, 128), (1024, 1024, 128), (512, 512, 128), (256, 256, 128), (192, 192, 128), (256, 256, 256)):
+for split, depth in (((0, 0, 128), 2), ((0, 0, 128), 3), ((0, 0, 128), 4), ((128, 128, 64), 2), ((128, 128, 64), 3), ((128, 128, 64), 4)):
     win = srb.MainWindow(scene.width, scene.height)
     ctx = win._ctx
     win.SetBinSplit(*split)
+    win.SetPipelineDepth(depth)
     if r1 > r0:
         win.SetBand(r0, r1)
     S.submit_scene(win, scene)
@@ -30,6 +31,11 @@ for split in ((0, 0, 128), (1024, 1024, 128), (512, 512, 128), (256, 256, 128), 
     st = win.Stats()
     for _ in range(20):
         N.check(ctx, L.srb_replay_frame(ctx))
+    win.Sync()
+    th = time.perf_counter()
+    for _ in range(24):                       # host cost of queueing a frame (nothing to wait for: the queue is empty)
+        N.check(ctx, L.srb_replay_frame(ctx))
+    host_us = (time.perf_counter() - th) / 24 * 1e6
     win.Sync()
     t0 = time.perf_counter()
     K = 300
@@ -46,6 +52,6 @@ for split in ((0, 0, 128), (1024, 1024, 128), (512, 512, 128), (256, 256, 128), 
         if i >= 3:
             acc += np.array(list(buf))
     N.check(ctx, L.srb_set_profiling(ctx, 0))
-    print(f"band {r0}-{r1} split {split}: {fps:8.0f} frames/s  parts {st.split_parts:5d}  pairs {st.tile_pairs}  "
+    print(f"band {r0}-{r1} split {split} depth {depth}: {fps:8.0f} frames/s  parts {st.split_parts:5d}  pairs {st.tile_pairs}  host {host_us:.1f} us/frame  "
           + " ".join(f"{n}={a / 30 * 1000:.1f}" for n, a in zip(bench.STAGES, acc)), flush=True)
     win.Close()
