@@ -229,6 +229,11 @@ def run_gpu(args):
 
     if world > 1:
         win.SetBand(r0, r1)
+        if fused and args.frame_barrier == "peer":
+            bar_rows = [None] * world
+            dist.all_gather_object(bar_rows, win.BarrierExport())
+            dist.barrier()                      # every row is zeroed before anyone posts into it
+            win.BarrierConnect(rank, world, bar_rows)
         if fused:
             # rank 0 exports its ColorBuffer and an RGBA8 frame (its own tile kernel fills its band of that one too)
             box = [win.ExportColorHandle() if rank == 0 else None]
@@ -264,10 +269,15 @@ def run_gpu(args):
 
     def frame_barrier():
         """Fused gather: the pixels already went over NVLink as peer stores; what is left of the gather is the
-        "every band of frame k has landed" barrier, a 4-byte NCCL all-reduce.  'side' (default): the all-reduce of
+        "every band of frame k has landed" barrier.  'peer' (default): srb_frame_barrier -- every rank posts its frame
+        counter into every rank's flag row over NVLink and waits for the others' previous frame; no collective, no host
+        work beyond one launch.  The NCCL forms remain for comparison, a 4-byte all-reduce.  'side': the all-reduce of
         frame k runs on its own stream behind tile kernel k, and tile kernel k+2 waits for it -- the ranks stay
         within one frame of each other, and the collective's launch and latency are off the raster stream.
         'inline': on the raster stream, between tile kernels k and k+1 (round 1)."""
+        if args.frame_barrier == "peer":        # the library's own barrier: flags in peer memory, one 32-thread kernel
+            N.check(ctx, L.srb_frame_barrier(ctx, 1))
+            return
         if args.frame_barrier == "inline":
             dist.all_reduce(token)
             return
@@ -284,13 +294,20 @@ def run_gpu(args):
         if len(bar_pending) > 1:
             ext.wait_event(bar_pending.pop(0))
 
+    def hard_barrier():
+        """Every rank has reached this point of its raster stream (device-side; the host does not wait)."""
+        if args.frame_barrier == "peer" and fused:
+            N.check(ctx, L.srb_frame_barrier(ctx, 0))
+        else:
+            dist.all_reduce(token)
+
     def gather(landed=False):
         """landed=True: the caller reads the assembled frame next, so every band of THIS frame must be in place
         (barrier on the raster stream); otherwise the ranks only have to stay within a frame of each other."""
         if world == 1:
             return
         if fused and landed:
-            dist.all_reduce(token)
+            hard_barrier()
         elif fused:
             frame_barrier()
         else:
@@ -316,7 +333,7 @@ def run_gpu(args):
             N.check(ctx, L.srb_present_rgb_async(ctx, C.c_void_p(host_rgb[e2e_count[0] & 1].data_ptr())))
             e2e_count[0] += 1
         if fused:
-            dist.all_reduce(token)              # band ranks must not start the next frame before rank 0 has flattened this one
+            hard_barrier()                      # band ranks must not start the next frame before rank 0 has flattened this one
 
     host_rgba8 = [torch.empty((H, W, 4), dtype=torch.uint8, pin_memory=True) for _ in range(2)]
 
@@ -334,7 +351,7 @@ def run_gpu(args):
                 N.check(ctx, L.srb_present_rgba8_async(ctx, C.c_void_p(host_rgba8[e2e_count[0] & 1].data_ptr())))
             e2e_count[0] += 1
         if fused:
-            dist.all_reduce(token)
+            hard_barrier()
 
     def step_e2e_colorbuffer():
         """Same, but the result is the float4 ColorBuffer itself, read synchronously (srb_read_color)."""
@@ -345,7 +362,7 @@ def run_gpu(args):
         if rank == 0:
             N.check(ctx, L.srb_read_color(ctx, C.c_void_p(host.data_ptr())))
         if fused:
-            dist.all_reduce(token)
+            hard_barrier()
 
     def timed(step, K, Wm, sampler=None):
         with torch.cuda.stream(ext):
@@ -448,7 +465,7 @@ def run_gpu(args):
             N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
             N.check(ctx, L.srb_end_frame(ctx))
             N.check(ctx, L.srb_present_fence(ctx))   # stream waits for the copies of the frames before this one
-            dist.all_reduce(token)                   # => on every rank: all bands of the previous frame have landed
+            hard_barrier()                           # => on every rank: all bands of the previous frame have landed
             N.check(ctx, L.srb_present_rgb_rows_async(ctx, C.c_void_p(shared[par_count[0] & 1].ctypes.data), ye0, ye1))
             par_count[0] += 1
 
@@ -633,6 +650,10 @@ def run_gpu(args):
     if world > 1:
         if fused:                                # unmap rank 0's frames before rank 0 frees them
             use_gather(None)
+            if args.frame_barrier == "peer":
+                win.Sync()
+                dist.barrier()
+                win.BarrierConnect(rank, world, None)
         torch.cuda.synchronize(dev)
         dist.barrier()
     win.Close()
@@ -700,7 +721,7 @@ def main():
                          "(RGBA8, the format of the parity gate; default) or the float4 ColorBuffer (four times the NVLink "
                          "traffic: at 4K and N=8, 116 MB per frame into GPU 0, which caps the rate near 7,000 frames/s)")
     ap.add_argument("--no-other-gather", action="store_true", help="N>1: skip the additional measurement with the other gather format")
-    ap.add_argument("--frame-barrier", default="side", choices=["side", "inline", "none"],
+    ap.add_argument("--frame-barrier", default="peer", choices=["peer", "side", "inline", "none"],
                     help="N>1, fused gather: where the per-frame 4-byte all-reduce runs (see frame_barrier)")
     ap.add_argument("--pcie-gbs", type=float, default=50.0, help="N>1 e2e: host link rate assumed by the band cuts of the e2e loop")
     ap.add_argument("--remote-cost", type=float, default=12.0,

@@ -58,6 +58,9 @@ namespace SoftwareRenderer
         [DllImport(Lib)] public static extern int srb_get_size(IntPtr ctx, out int width, out int height);
         [DllImport(Lib)] public static extern IntPtr srb_last_error(IntPtr ctx);
         [DllImport(Lib)] public static extern int srb_set_band(IntPtr ctx, int tileRow0, int tileRow1);
+        [DllImport(Lib)] public static extern int srb_barrier_export(IntPtr ctx, byte* handleOut);
+        [DllImport(Lib)] public static extern int srb_barrier_connect(IntPtr ctx, int rank, int world, byte* handles);
+        [DllImport(Lib)] public static extern int srb_frame_barrier(IntPtr ctx, int slack);
         [DllImport(Lib)] public static extern int srb_set_bin_split(IntPtr ctx, int minEntriesFullFrame, int minEntriesBand, int partEntries);
         [DllImport(Lib)] public static extern int srb_set_pipeline_depth(IntPtr ctx, int bufferSets);
         [DllImport(Lib)] public static extern int srb_set_pipeline(IntPtr ctx, int pipeline);

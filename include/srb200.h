@@ -204,6 +204,17 @@ int srb_present_rgba8_rows_async(SrbContext* ctx, uint8_t* rgba8_out, int y0, in
  * present copies queued so far have landed.  A collective placed behind it is a "frame delivered" barrier
  * across band ranks that never blocks the host. */
 int srb_present_fence(SrbContext* ctx);
+/* Frame barrier between the band contexts of one frame, ONE CONTEXT PER GPU (no reference counterpart; SURVEY.md
+ * 8(e)).  Every rank exports its row of flags, the rows are exchanged (any transport), every rank connects with all
+ * of them (handles: world x 64 bytes, indexed by rank; its own entry is ignored).  srb_frame_barrier queues a
+ * 32-thread kernel behind the frame on the context's stream: it posts "this rank has finished frame k" into every
+ * rank's row over NVLink and waits until all ranks have posted frame k - slack (slack 0: every band of this frame
+ * has landed, the kernel sits on the raster stream; slack >= 1: ranks only stay close -- the kernel runs on a side
+ * stream and the raster stream waits for the previous call's barrier, i.e. ranks stay within slack + 1 frames).
+ * The wait is bounded (4 s), a time-out turns into an error of the next call.  handles == NULL disconnects. */
+int srb_barrier_export(SrbContext* ctx, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]);
+int srb_barrier_connect(SrbContext* ctx, int rank, int world, const uint8_t* handles);
+int srb_frame_barrier(SrbContext* ctx, int slack);
 int srb_present_wait(SrbContext* ctx);
 int srb_read_color_rows(SrbContext* ctx, float* rgba_out, int y0, int y1);
 int srb_get_pixel(SrbContext* ctx, int x, int y, float rgba_out[4]);   /* :390-398 */

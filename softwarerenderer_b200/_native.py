@@ -86,7 +86,7 @@ EXPORTS = [
     "srb_mesh_create", "srb_mesh_destroy", "srb_set_uniforms", "srb_begin_frame", "srb_draw",
     "srb_submit_draws", "srb_end_frame", "srb_replay_frame", "srb_sync", "srb_read_color",
     "srb_read_depth", "srb_read_color_rgba8", "srb_present_rgb", "srb_present_rgb_async", "srb_present_rgb_rows_async",
-    "srb_present_rgba8", "srb_present_rgba8_async", "srb_present_rgba8_rows_async", "srb_present_wait", "srb_present_fence",
+    "srb_present_rgba8", "srb_present_rgba8_async", "srb_present_rgba8_rows_async", "srb_present_wait", "srb_present_fence", "srb_barrier_export", "srb_barrier_connect", "srb_frame_barrier",
     "srb_read_color_rows", "srb_get_pixel", "srb_set_pixel",
     "srb_get_depth", "srb_set_depth", "srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream",
     "srb_frustum_test", "srb_raycast", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
@@ -159,6 +159,9 @@ def lib() -> C.CDLL:
     L.srb_present_wait.argtypes = [vp]
     L.srb_raycast.argtypes = [vp, C.c_int32, vp, vp, C.c_int, C.c_int, vp]
     L.srb_present_fence.argtypes = [vp]
+    L.srb_barrier_export.argtypes = [vp, vp]
+    L.srb_barrier_connect.argtypes = [vp, i32, i32, vp]
+    L.srb_frame_barrier.argtypes = [vp, i32]
     L.srb_read_color_rows.argtypes = [vp, vp, i32, i32]
     L.srb_get_pixel.argtypes = [vp, i32, i32, f32p]
     L.srb_set_pixel.argtypes = [vp, i32, i32, f32p]

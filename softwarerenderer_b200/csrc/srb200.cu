@@ -87,6 +87,15 @@ struct SrbContext {
     int visMode = 0;
     int nVBlocks = 0, nTBlocks = 0;
     DevBuf<uint32_t> dBinScratch;
+    // peer-memory frame barrier (multi-GPU bands, one rank per GPU)
+    uint32_t* barRow = nullptr;                 // this rank's row of flags (exported)
+    BarrierRows barRows = {};                   // every rank's row: own + peers' opened through IPC handles
+    int barRank = -1, barWorld = 0;
+    uint32_t barCount = 0;                      // barriers issued so far
+    uint32_t* barTimedOut = nullptr;            // pinned, mapped
+    cudaStream_t barStream = nullptr;           // slack >= 1: the barrier kernel runs beside the raster stream
+    cudaEvent_t barFrame = nullptr, barDone[2] = {};
+    int barPending = -1;                        // barDone[] index of the last side-stream barrier, -1: none
     unsigned long long* dSliceKeys = nullptr;   // key slices of split bins (kMaxExtra x 256), all zero between tile kernels
     uint32_t* dSliceDone = nullptr;             // per slice: parts merged so far, zero between tile kernels
     // Bins of >= splitMin entries are rasterized by several CTAs of splitPart entries each (srb_set_bin_split).
@@ -146,6 +155,14 @@ namespace {
 
 void close_color_target(SrbContext* c) {
     if (c->colorTarget) { cudaIpcCloseMemHandle(c->colorTarget); c->colorTarget = nullptr; }
+}
+void barrier_close(SrbContext* c) {
+    if (c->barStream) cudaStreamSynchronize(c->barStream);
+    c->barPending = -1;
+    for (int r = 0; r < c->barWorld; ++r)
+        if (r != c->barRank && c->barRows.row[r]) cudaIpcCloseMemHandle(c->barRows.row[r]);
+    c->barRows = BarrierRows{};
+    c->barRank = -1; c->barWorld = 0;
 }
 void close_color8_target(SrbContext* c) {
     if (c->color8Target) { cudaIpcCloseMemHandle(c->color8Target); c->color8Target = nullptr; }
@@ -487,6 +504,12 @@ int srb_destroy(SrbContext* c) {
     cudaStreamSynchronize(c->stream);
     close_color_target(c);
     close_color8_target(c);
+    barrier_close(c);
+    if (c->barStream) { cudaStreamSynchronize(c->barStream); cudaStreamDestroy(c->barStream); }
+    if (c->barFrame) cudaEventDestroy(c->barFrame);
+    for (auto& e : c->barDone) if (e) cudaEventDestroy(e);
+    if (c->barRow) cudaFree(c->barRow);
+    if (c->barTimedOut) cudaFreeHost(c->barTimedOut);
     if (c->color8) cudaFree(c->color8);
     for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
@@ -1140,6 +1163,86 @@ int srb_present_fence(SrbContext* c) {
     CK(c, cudaSetDevice(c->device));
     for (int s = 0; s < 2; ++s)
         if (c->presentBusy[s]) CK(c, cudaStreamWaitEvent(c->stream, c->presentCopied[s], 0));
+    return SRB_OK;
+}
+
+/* ---- peer-memory frame barrier ---- */
+int srb_barrier_export(SrbContext* c, uint8_t handle_out[SRB_IPC_HANDLE_BYTES]) {
+    if (!c || !handle_out) return SRB_ERR_ARG;
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    if (!c->barRow) {
+        CK(c, cudaMalloc((void**)&c->barRow, (size_t)kMaxRanks * kFlagStride * sizeof(uint32_t)));
+        CK(c, cudaMallocHost((void**)&c->barTimedOut, sizeof(uint32_t)));
+    }
+    CK(c, cudaMemset(c->barRow, 0, (size_t)kMaxRanks * kFlagStride * sizeof(uint32_t)));
+    *c->barTimedOut = 0u;
+    c->barCount = 0;
+    cudaIpcMemHandle_t h;
+    CK(c, cudaIpcGetMemHandle(&h, c->barRow));
+    std::memcpy(handle_out, &h, sizeof(h));
+    return SRB_OK;
+}
+
+int srb_barrier_connect(SrbContext* c, int rank, int world, const uint8_t* handles) {
+    if (!c) return SRB_ERR_ARG;
+    CK(c, cudaSetDevice(c->device));
+    int rc = complete_frame(c);
+    if (rc != SRB_OK) return rc;
+    barrier_close(c);
+    if (!handles) return SRB_OK;                                  // disconnect
+    if (world < 1 || world > kMaxRanks || rank < 0 || rank >= world) return fail(c, SRB_ERR_ARG, "barrier: need 0 <= rank < world <= 16");
+    if (!c->barRow) return fail(c, SRB_ERR_STATE, "srb_barrier_export first");
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) { c->barRows.row[r] = c->barRow; continue; }
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + (size_t)r * SRB_IPC_HANDLE_BYTES, sizeof(h));
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            c->barWorld = r; c->barRank = rank;
+            barrier_close(c);
+            return fail(c, SRB_ERR_CUDA, std::string("cudaIpcOpenMemHandle (barrier): ") + cudaGetErrorString(e));
+        }
+        c->barRows.row[r] = (uint32_t*)p;
+    }
+    c->barRank = rank; c->barWorld = world;
+    return SRB_OK;
+}
+
+int srb_frame_barrier(SrbContext* c, int slack) {
+    if (!c) return SRB_ERR_ARG;
+    if (c->barWorld <= 0) return fail(c, SRB_ERR_STATE, "frame barrier is not connected");
+    if (slack < 0 || slack > 2) return fail(c, SRB_ERR_ARG, "barrier slack must be 0..2 frames");
+    if (*c->barTimedOut) return fail(c, SRB_ERR_CUDA, "frame barrier timed out: a rank is missing or far behind");
+    CK(c, cudaSetDevice(c->device));
+    const uint32_t k = ++c->barCount;
+    const uint32_t waitFor = k > (uint32_t)slack ? k - (uint32_t)slack : 0u;
+    if (!c->barStream) {
+        CK(c, cudaStreamCreateWithFlags(&c->barStream, cudaStreamNonBlocking));
+        CK(c, cudaEventCreateWithFlags(&c->barFrame, cudaEventDisableTiming));
+        for (auto& e : c->barDone) CK(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    if (slack == 0) {
+        // The caller reads the assembled frame next: the barrier sits on the raster stream itself (behind any
+        // side-stream barrier still in flight, so that this rank's counter never steps back).
+        if (c->barPending >= 0) { CK(c, cudaStreamWaitEvent(c->stream, c->barDone[c->barPending], 0)); c->barPending = -1; }
+        frame_barrier_kernel<<<1, 32, 0, c->stream>>>(c->barRows, c->barRank, c->barWorld, k, waitFor, c->barTimedOut);
+    } else {
+        // Ranks only have to stay close: the kernel runs on a stream of its own behind this frame's tile kernel, and
+        // the raster stream waits for the PREVIOUS call's barrier -- in effect slack + 1 frames.  (On the raster
+        // stream, between tile kernels k and k+1, the launch gap and the NVLink round trip of the flag stores cost
+        // 5 % of an N=2 city4k frame: 7,400 -> 7,050 frames/s.)
+        CK(c, cudaEventRecord(c->barFrame, c->stream));
+        CK(c, cudaStreamWaitEvent(c->barStream, c->barFrame, 0));
+        frame_barrier_kernel<<<1, 32, 0, c->barStream>>>(c->barRows, c->barRank, c->barWorld, k, waitFor, c->barTimedOut);
+        const int cur = c->barPending == 0 ? 1 : 0;
+        CK(c, cudaEventRecord(c->barDone[cur], c->barStream));
+        if (c->barPending >= 0) CK(c, cudaStreamWaitEvent(c->stream, c->barDone[c->barPending], 0));
+        c->barPending = cur;
+    }
+    CK(c, cudaGetLastError());
     return SRB_OK;
 }
 

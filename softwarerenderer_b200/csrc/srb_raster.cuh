@@ -473,6 +473,38 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
 #endif
 }
 
+// ---------------------------------------------------------------------------
+// Frame barrier between the band ranks of a multi-GPU frame (one rank per GPU), in peer memory.  Every rank owns a
+// row of flags, one per rank; barrier k of rank r stores k into flag r of every rank's row (peer stores over NVLink,
+// after a system-scope fence: this rank's tile kernel, which precedes the barrier on the stream, stored its band
+// into rank 0's frame the same way), then waits until every flag of its own row has reached `waitFor` -- k itself
+// when the caller reads the assembled frame next, k - 1 when the ranks only have to stay within a frame of each
+// other.  One 32-thread launch per frame instead of a 4-byte NCCL all-reduce.  The wait is bounded: after
+// kBarrierTimeoutNs the kernel gives up and raises *timedOut (mapped host memory), so a missing rank becomes an
+// error code, never a hung device.
+// ---------------------------------------------------------------------------
+constexpr int kMaxRanks = 16;
+constexpr int kFlagStride = 32;                       // uint32 per flag: every flag on a 128-byte line of its own
+constexpr unsigned long long kBarrierTimeoutNs = 4000000000ull;
+struct BarrierRows { uint32_t* row[kMaxRanks]; };
+__global__ void frame_barrier_kernel(BarrierRows rows, int rank, int world, uint32_t k, uint32_t waitFor,
+                                     uint32_t* __restrict__ timedOut) {
+    const int t = threadIdx.x;
+    __threadfence_system();
+    if (t < world) *reinterpret_cast<volatile uint32_t*>(rows.row[t] + rank * kFlagStride) = k;
+    __threadfence_system();
+    if (t < world && waitFor != 0u) {
+        const volatile uint32_t* f = rows.row[rank] + t * kFlagStride;
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int32_t)(*f - waitFor) < 0) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > kBarrierTimeoutNs) { *timedOut = 1u; break; }
+        }
+    }
+    __threadfence_system();
+}
+
 __global__ void texture_sample_kernel(const uchar4* __restrict__ tex, int tw, int th, const float2* __restrict__ uv,
                                       int n, int filter, float4* __restrict__ out) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

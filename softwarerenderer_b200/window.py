@@ -138,6 +138,23 @@ class MainWindow:
         N.check(self._ctx, N.lib().srb_read_gathered_rgba8(self._ctx, N.ptr(out)))
         return out
 
+    # -- frame barrier in peer memory (one window per GPU) ------------------------------------
+    def BarrierExport(self) -> bytes:
+        buf = (C.c_uint8 * 64)()
+        N.check(self._ctx, N.lib().srb_barrier_export(self._ctx, buf))
+        return bytes(buf)
+
+    def BarrierConnect(self, rank: int, world: int, handles) -> None:
+        """handles: every rank's BarrierExport() in rank order (None disconnects)."""
+        if handles is None:
+            N.check(self._ctx, N.lib().srb_barrier_connect(self._ctx, 0, 0, None))
+            return
+        blob = (C.c_uint8 * (64 * world)).from_buffer_copy(b"".join(handles))
+        N.check(self._ctx, N.lib().srb_barrier_connect(self._ctx, rank, world, blob))
+
+    def FrameBarrier(self, slack: int = 0) -> None:
+        N.check(self._ctx, N.lib().srb_frame_barrier(self._ctx, slack))
+
     def TileRowPairs(self) -> np.ndarray:
         """(triangle, tile) pairs binned into each 16-px tile row by the last frame."""
         n = (self.RenderHeight + 15) // 16

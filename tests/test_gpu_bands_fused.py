@@ -121,6 +121,16 @@ def _worker_multi(rank, world, port, out_path):
         dist.broadcast_object_list(box8, src=0)
         ext = torch.cuda.ExternalStream(N.lib().srb_stream(win._ctx), device=dev)
         token = torch.zeros(1, device=dev)
+        bar_rows = [None] * world                                 # the library's own barrier (flags in peer memory)
+        dist.all_gather_object(bar_rows, win.BarrierExport())
+        dist.barrier()
+        win.BarrierConnect(rank, world, bar_rows)
+
+        def barrier(fmt):                                         # float4 frames: NCCL all-reduce; rgba8 frames: srb_frame_barrier
+            if fmt == "rgba8":
+                win.FrameBarrier(0)
+            else:
+                dist.all_reduce(token)
         got = {}
         for fmt in ("float4", "rgba8"):
             if rank != 0:
@@ -131,12 +141,12 @@ def _worker_multi(rank, world, port, out_path):
             with torch.cuda.stream(ext):
                 for sc in (a, b, a, b):
                     S.submit_scene(win, sc)                       # no host sync: frames are pipelined on every rank
-                    dist.all_reduce(token)                        # every band of this frame has landed ...
+                    barrier(fmt)                                  # every band of this frame has landed ...
                     if rank == 0:                                 # ... rank 0 takes the frame on the same stream
                         src = torch.as_tensor(_DevArray(N.lib().srb_device_gathered_rgba8_ptr(win._ctx), (720, 1280), "<u4") if fmt == "rgba8"
                                               else _DevArray(N.lib().srb_device_color_ptr(win._ctx), (720, 1280, 4)), device=dev)
                         snaps.append(src.clone())
-                    dist.all_reduce(token)                        # ... before any rank stores the next one
+                    barrier(fmt)                                  # ... before any rank stores the next one
             torch.cuda.synchronize(dev)
             if rank == 0:
                 got[fmt] = [s.cpu().numpy() for s in snaps]
@@ -146,6 +156,7 @@ def _worker_multi(rank, world, port, out_path):
         if rank != 0:
             win.SetGatherRgba8Target(None)
             win.SetColorTarget(None)
+        win.BarrierConnect(rank, world, None)
         dist.barrier()
         win.Close()
     finally:
