@@ -89,6 +89,7 @@ namespace SoftwareRenderer
         [DllImport(Lib)] public static extern int srb_present_rgba8_async(IntPtr ctx, byte* rgba8Out);
         [DllImport(Lib)] public static extern int srb_present_rgba8_rows_async(IntPtr ctx, byte* rgba8Out, int y0, int y1);
         [DllImport(Lib)] public static extern int srb_raycast(IntPtr ctx, int mesh, float* model, float* rays, int n, int faceMask, SrbRayHit* hits);
+        [DllImport(Lib)] public static extern int srb_raycast_static(IntPtr ctx, int mesh, float* model, float* rays, int n, int faceMask, SrbRayHit* hits);
         [DllImport(Lib)] public static extern int srb_gather_rgba8_export(IntPtr ctx, byte* handleOut);
         [DllImport(Lib)] public static extern int srb_gather_rgba8_target(IntPtr ctx, byte* handle);
         [DllImport(Lib)] public static extern int srb_read_gathered_rgba8(IntPtr ctx, byte* rgba8Out);

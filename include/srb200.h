@@ -248,6 +248,17 @@ typedef struct SrbRayHit {
 int srb_raycast(SrbContext* ctx, SrbMesh mesh, const float model[16], const float* rays /* n*6 */, int n,
                 int face_mask, SrbRayHit* out /* n */);
 
+/* srb_raycast for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments,
+ * same results bit for bit, but the call performs no cudaMalloc / cudaFree / allocating library routine: its scratch
+ * (96 bytes per ray) is one fixed device array inside the library, 384 KiB, held by every GPU that loads the library
+ * until the process exits.  n > SRB_RAYCAST_STATIC_MAX_RAYS is refused (SRB_ERR_ARG).  All calls on a device share
+ * the array and it keeps the last call's contents; the call waits for its own result, but calls that overlap on the
+ * GPU (different contexts of one device, from different threads) race -- serialise them. */
+#define SRB_RAYCAST_STATIC_MAX_RAYS 4096
+int srb_raycast_static(SrbContext* ctx, SrbMesh mesh, const float model[16], const float* rays /* n x 6 */, int n,
+                       int face_mask, SrbRayHit* out /* n */);
+
 int srb_get_stats(SrbContext* ctx, SrbStats* out);
 /* Per-stage device times of the last completed frame (CUDA events on the pipeline stream).
  * Enable with srb_set_profiling(ctx, 1); stages: 0 frustum, 1 vertex, 2 setup+count, 3 scan,

@@ -20,6 +20,7 @@ SRB_ERR_ARG, SRB_ERR_CUDA, SRB_ERR_HANDLE, SRB_ERR_STATE, SRB_ERR_UNSUPPORTED = 
 SRB_CLEAR_COLOR, SRB_CLEAR_DEPTH = 1, 2
 SRB_DRAW_FRUSTUM_CULL = 1
 SRB_PIPELINE_AUTO, SRB_PIPELINE_ORDERED, SRB_PIPELINE_VISIBILITY = 0, 1, 2
+SRB_RAYCAST_STATIC_MAX_RAYS = 4096          # include/srb200.h
 
 
 class SrbUniforms(C.Structure):
@@ -89,7 +90,7 @@ EXPORTS = [
     "srb_present_rgba8", "srb_present_rgba8_async", "srb_present_rgba8_rows_async", "srb_present_wait", "srb_present_fence", "srb_barrier_export", "srb_barrier_connect", "srb_frame_barrier",
     "srb_read_color_rows", "srb_get_pixel", "srb_set_pixel",
     "srb_get_depth", "srb_set_depth", "srb_device_color_ptr", "srb_device_depth_ptr", "srb_stream",
-    "srb_frustum_test", "srb_raycast", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
+    "srb_frustum_test", "srb_raycast", "srb_raycast_static", "srb_get_stats", "srb_version", "srb_set_profiling", "srb_get_stage_ms",
 ]
 
 _lib = None
@@ -158,6 +159,7 @@ def lib() -> C.CDLL:
     L.srb_present_rgba8_rows_async.argtypes = [vp, vp, C.c_int, C.c_int]
     L.srb_present_wait.argtypes = [vp]
     L.srb_raycast.argtypes = [vp, C.c_int32, vp, vp, C.c_int, C.c_int, vp]
+    L.srb_raycast_static.argtypes = [vp, C.c_int32, vp, vp, C.c_int, C.c_int, vp]
     L.srb_present_fence.argtypes = [vp]
     L.srb_barrier_export.argtypes = [vp, vp]
     L.srb_barrier_connect.argtypes = [vp, i32, i32, vp]

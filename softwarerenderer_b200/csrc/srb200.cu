@@ -1348,6 +1348,82 @@ int srb_raycast(SrbContext* c, SrbMesh mesh, const float model[16], const float*
     return SRB_OK;
 }
 
+/* ---- srb_raycast without any allocation ----
+ * No counterpart in the reference; added for callers that cannot allocate (CUDA
+ * graph capture, tight serving loops).  Same kernels as srb_raycast, the per-call scratch (ray copies, normalised
+ * directions, 64-bit winner keys, hit records: 96 bytes per ray) lives in ONE file-scope device array of fixed size
+ * instead of the context's growable buffer.  Every GPU that loads the library holds the array until the process ends.
+ * All calls share it, whatever the context: it keeps the last call's contents (ray_prepare_kernel rewrites every key
+ * and direction a call uses before they are read), and calls that overlap on the GPU would race -- this entry point
+ * serialises on the context's stream and waits for its result, so only concurrent callers on DIFFERENT contexts of
+ * one device have to take turns themselves. */
+namespace {
+constexpr size_t kStaticRayBytes = (size_t)SRB_RAYCAST_STATIC_MAX_RAYS * (24 + 16 + 8 + sizeof(RayHit));
+static __device__ __align__(256) unsigned char g_rayScratch[kStaticRayBytes];
+std::mutex g_rayScratchMu;
+unsigned char* g_rayScratchAddr[64] = {};                       // per device: the array's DEVICE address (the name above is
+                                                                // only a host-side stand-in and must never reach a kernel)
+int static_scratch_address(SrbContext* c, unsigned char** out) {
+    if (c->device < 0 || c->device >= 64) return fail(c, SRB_ERR_ARG, "device index beyond the static scratch table");
+    std::lock_guard<std::mutex> lk(g_rayScratchMu);
+    if (!g_rayScratchAddr[c->device]) {                         // once per device, with that device current
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_rayScratch);
+        if (e != cudaSuccess || !p) return fail(c, SRB_ERR_CUDA, std::string("cudaGetSymbolAddress(g_rayScratch): ") + cudaGetErrorString(e));
+        g_rayScratchAddr[c->device] = (unsigned char*)p;
+    }
+    *out = g_rayScratchAddr[c->device];
+    return SRB_OK;
+}
+}  // namespace
+
+int srb_raycast_static(SrbContext* c, SrbMesh mesh, const float model[16], const float* rays, int n, int face_mask, SrbRayHit* out) {
+    if (!c || !model || !rays || !out || n < 0) return SRB_ERR_ARG;
+    if (n > SRB_RAYCAST_STATIC_MAX_RAYS)
+        return fail(c, SRB_ERR_ARG, "srb_raycast_static: at most " + std::to_string(SRB_RAYCAST_STATIC_MAX_RAYS) +
+                                    " rays per call (fixed device scratch); use srb_raycast or split the batch");
+    if (mesh <= 0 || (size_t)mesh > c->meshes.size() || !c->meshes[mesh - 1].alive) return fail(c, SRB_ERR_HANDLE, "unknown mesh handle");
+    if (face_mask < 0 || face_mask > 3) return fail(c, SRB_ERR_ARG, "face_mask must be a combination of 1 (IgnoreBackfaces) and 2 (IgnoreFrontfaces)");
+    if (n == 0) return SRB_OK;
+    CK(c, cudaSetDevice(c->device));
+    const MeshRes& m = c->meshes[mesh - 1];
+    Mat4 M, NM;
+    std::memcpy(M.m, model, 64);
+    float inv[16];
+    if (!invert4(model, inv)) {                                  // Physics.cs:30-36: no hit, distance float.MaxValue, zero vectors
+        for (int r = 0; r < n; ++r) {
+            std::memset(&out[r], 0, sizeof(SrbRayHit));
+            out[r].distance = 3.402823466e+38f; out[r].triangle = -1;
+        }
+        return SRB_OK;
+    }
+    for (int r = 0; r < 4; ++r) for (int k = 0; k < 4; ++k) NM.m[4 * r + k] = inv[4 * k + r];
+    unsigned char* base = nullptr;
+    int rc = static_scratch_address(c, &base);
+    if (rc != SRB_OK) return rc;
+    // fixed layout for the maximum batch: directions | hits | keys | rays (each region 16-byte aligned)
+    const size_t N = SRB_RAYCAST_STATIC_MAX_RAYS;
+    float4* dDirs = (float4*)base;
+    RayHit* dHits = (RayHit*)(base + N * 16);
+    unsigned long long* dKeys = (unsigned long long*)(base + N * (16 + sizeof(RayHit)));
+    float* dRays = (float*)(base + N * (16 + sizeof(RayHit) + 8));
+    cudaStream_t s = c->stream;
+    CK(c, cudaMemcpyAsync(dRays, rays, (size_t)n * 24, cudaMemcpyHostToDevice, s));
+    ray_prepare_kernel<<<(n + 255) / 256, 256, 0, s>>>(dRays, n, dDirs, dKeys);      // (re)initialises every key and direction used below
+    const int nTri = m.nI / 3;
+    if (nTri > 0) {
+        dim3 grid((nTri + 255) / 256, (n + kRayChunk - 1) / kRayChunk);
+        if (c->uniforms.numerics_fma) raycast_kernel<true><<<grid, 256, 0, s>>>(m.vtx, m.idx, nTri, M, dRays, dDirs, n, face_mask, dKeys);
+        else raycast_kernel<false><<<grid, 256, 0, s>>>(m.vtx, m.idx, nTri, M, dRays, dDirs, n, face_mask, dKeys);
+    }
+    if (c->uniforms.numerics_fma) ray_resolve_kernel<true><<<(n + 127) / 128, 128, 0, s>>>(m.vtx, m.idx, M, NM, dRays, dDirs, n, face_mask, dKeys, dHits);
+    else ray_resolve_kernel<false><<<(n + 127) / 128, 128, 0, s>>>(m.vtx, m.idx, M, NM, dRays, dDirs, n, face_mask, dKeys, dHits);
+    CK(c, cudaGetLastError());
+    CK(c, cudaMemcpyAsync(out, dHits, (size_t)n * sizeof(RayHit), cudaMemcpyDeviceToHost, s));
+    CK(c, cudaStreamSynchronize(s));
+    return SRB_OK;
+}
+
 void* srb_device_color_ptr(SrbContext* c) { return c ? (void*)c->color : nullptr; }
 void* srb_device_depth_ptr(SrbContext* c) { return c ? (void*)c->depth : nullptr; }
 void* srb_stream(SrbContext* c) { return c ? (void*)c->stream : nullptr; }
