@@ -24,6 +24,7 @@ namespace SoftwareRenderer
         public int Pad;
         public fixed float ExtraDir[16];
         public fixed float ExtraColor[16];
+        public fixed float ExtraAtten[16];
     }
 
     [StructLayout(LayoutKind.Sequential)]

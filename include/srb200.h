@@ -71,12 +71,13 @@ typedef struct SrbUniforms {
     float near_clip;          /* Rasterizer.NearClip */
     int32_t numerics_fma;     /* 1 = System.Numerics Transform/Lerp fused (net9.0 on FMA hardware) */
     int32_t tex_filter;       /* 0 nearest+repeat (Texture.cs:42-63); 1 bilinear+repeat (extension) */
-    int32_t n_extra_lights;   /* extension: 0..4 extra directional lights */
+    int32_t n_extra_lights;   /* extension (BASELINE config 5): 0..4 extra lights */
     int32_t debug_mode;       /* Rasterizer.RenderDebugMode (Rasterizer.cs:14-22): 0 None, 1 Wireframe (every triangle is
                                  drawn as three DrawLine calls, Rasterizer.cs:419-425, 232-340; ordered pipeline only) */
     int32_t _pad;
-    float extra_dir[4][4];
-    float extra_color[4][4];
+    float extra_dir[4][4];    /* w == 0: directional light, xyz = Light.Direction; w != 0: point light, xyz = Light.Position */
+    float extra_color[4][4];  /* Light.Color */
+    float extra_atten[4][4];  /* point lights: AttenuationConstant, AttenuationLinear, AttenuationQuadratic (Light.cs:13-15) */
 } SrbUniforms;
 
 /* One Rasterizer.RenderMesh call (Rasterizer.cs:163-174) for batched submission. */

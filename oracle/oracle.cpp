@@ -99,6 +99,7 @@ struct VOut {
     V3 normal;    // Normal (object space, passed through)
     V2 screen;    // ScreenCoords
     V3 wn;        // Data["WorldNormal"]
+    V3 wpos;      // EXTENSION (point lights only): world position, the vertex shader's `world` (Renderer.cs:832)
 };
 
 // Renderer.VertexShader (Renderer.cs:830-846).
@@ -113,6 +114,7 @@ inline VOut vertex_shader(const float* vin, const float* M, const float* V, cons
     o.color  = {vin[8], vin[9], vin[10], vin[11]};
     o.normal = n;
     o.screen = {0.0f, 0.0f};
+    o.wpos   = {world.x, world.y, world.z};
     return o;
 }
 
@@ -130,6 +132,8 @@ inline VOut vout_lerp(const VOut& a, const VOut& b, float t, bool fma) {
     o.wn     = {lerp1(a.wn.x, b.wn.x, t, fma), lerp1(a.wn.y, b.wn.y, t, fma),
                 lerp1(a.wn.z, b.wn.z, t, fma)};
     o.screen = {0.0f, 0.0f};
+    o.wpos   = {lerp1(a.wpos.x, b.wpos.x, t, fma), lerp1(a.wpos.y, b.wpos.y, t, fma),
+                lerp1(a.wpos.z, b.wpos.z, t, fma)};     // EXTENSION (point lights): Lerp'd like the other varyings
     return o;
 }
 
@@ -209,7 +213,8 @@ inline V4 tex_bilinear(const uint8_t* px, int tw, int th, float uu, float vv) {
 }
 
 // Renderer.FragmentShader (Renderer.cs:848-860).
-inline V4 fragment_shader(V3 wn, V4 color, V2 uv, float clipZ, const OrcDraw& d, const OrcUniforms& U) {
+inline V4 fragment_shader(V3 wn, V4 color, V2 uv, float clipZ, const OrcDraw& d, const OrcUniforms& U,
+                          V3 wpos = {0.0f, 0.0f, 0.0f}) {
     bool fma = U.numerics_fma != 0;
     V3 negL = {-U.light_dir[0], -U.light_dir[1], -U.light_dir[2]};
     float diffuse = net_max(0.25f, dot3(wn, negL));
@@ -223,10 +228,20 @@ inline V4 fragment_shader(V3 wn, V4 color, V2 uv, float clipZ, const OrcDraw& d,
     float k = 0.1f + 0.9f * diffuse;
     V4 lit = {base.x * k * U.light_color[0], base.y * k * U.light_color[1],
               base.z * k * U.light_color[2], base.w * k * U.light_color[3]};
-    // EXTENSION: extra directional lights add Color*max(0, N.-Dir)*base (no ambient floor).
+    // EXTENSION: extra lights add Color*max(0, N.L)*base (no ambient floor).  Directional:
+    // L = -Direction.  Point (Light.cs:9, 13-15): L = normalised (Position - fragment world position), scaled by
+    // 1 / (AttenuationConstant + AttenuationLinear*d + AttenuationQuadratic*d*d).
     for (int i = 0; i < U.n_extra_lights && i < 4; ++i) {
         V3 nd = {-U.extra_dir[i][0], -U.extra_dir[i][1], -U.extra_dir[i][2]};
-        float di = net_max(0.0f, dot3(wn, nd));
+        float att = 1.0f;
+        if (U.extra_dir[i][3] != 0.0f) {
+            V3 L = {U.extra_dir[i][0] - wpos.x, U.extra_dir[i][1] - wpos.y, U.extra_dir[i][2] - wpos.z};
+            float dist = sqrtf(dot3(L, L));
+            float inv = 1.0f / dist;
+            nd = {L.x * inv, L.y * inv, L.z * inv};
+            att = 1.0f / ((U.extra_atten[i][0] + U.extra_atten[i][1] * dist) + U.extra_atten[i][2] * (dist * dist));
+        }
+        float di = net_max(0.0f, dot3(wn, nd)) * att;
         lit.x = lit.x + base.x * di * U.extra_color[i][0];
         lit.y = lit.y + base.y * di * U.extra_color[i][1];
         lit.z = lit.z + base.z * di * U.extra_color[i][2];
@@ -293,6 +308,7 @@ struct SetupTri {
     V4 col[3];
     V2 uv[3];
     V3 wn[3];
+    V3 wpos[3];       // EXTENSION (point lights)
     float invArea;
     float a01, b01, a12, b12, a20, b20;
     int minX, maxX, minY, maxY;
@@ -315,6 +331,7 @@ inline bool setup_triangle(const VOut& v0, const VOut& v1, const VOut& v2, int W
         t.d[i]   = (nz + 1.0f) * 0.5f;                // :388
         t.cz[i] = o[i]->clip.z; t.cw[i] = o[i]->clip.w;
         t.col[i] = o[i]->color; t.uv[i] = o[i]->uv; t.wn[i] = o[i]->wn;
+        t.wpos[i] = o[i]->wpos;
     }
     if (v0.clip.w == 0 || v1.clip.w == 0 || v2.clip.w == 0) return false;   // :393
     float area = edge_fn(t.s[0], t.s[1], t.s[2]);     // :396, :411
@@ -343,7 +360,7 @@ inline bool setup_triangle(const VOut& v0, const VOut& v1, const VOut& v2, int W
 // Object Normal, ScreenCoords, Barycentric and clip x/y/w are unobservable
 // through the stock fragment shader and are not computed.
 inline void interpolate(const SetupTri& t, float w0, float w1, float w2,
-                        V3& wn, V4& col, V2& uv, float& clipZ) {
+                        V3& wn, V4& col, V2& uv, float& clipZ, V3* wpos = nullptr) {
     float ra = w0 / t.cw[0], rb = w1 / t.cw[1], rc = w2 / t.cw[2];   // :576-578
     float sum = ra + rb + rc;
     float w = 1.0f / sum;
@@ -364,6 +381,11 @@ inline void interpolate(const SetupTri& t, float w0, float w1, float w2,
         n = {n.x * inv, n.y * inv, n.z * inv};
     }
     wn = n;
+    if (wpos) {      // EXTENSION: world position, perspective-correct like the Vector3 varyings of :598-606
+        wpos->x = ((t.wpos[0].x * ra + t.wpos[1].x * rb) + t.wpos[2].x * rc) * w;
+        wpos->y = ((t.wpos[0].y * ra + t.wpos[1].y * rb) + t.wpos[2].y * rc) * w;
+        wpos->z = ((t.wpos[0].z * ra + t.wpos[1].z * rb) + t.wpos[2].z * rc) * w;
+    }
 }
 
 struct LocalStats { int64_t tested = 0, shaded = 0; };
@@ -397,8 +419,9 @@ inline void raster_tile_fill(OrcWindow& win, const SetupTri& t, const OrcDraw& d
                 if (depth_pass(d.depth_test, depth, old)) {
                     ++st.shaded;
                     V3 wn; V4 col; V2 uv; float cz;
-                    interpolate(t, w0f, w1f, w2f, wn, col, uv, cz);
-                    V4 c = fragment_shader(wn, col, uv, cz, d, U);
+                    V3 wp = {0.0f, 0.0f, 0.0f};
+                    interpolate(t, w0f, w1f, w2f, wn, col, uv, cz, &wp);
+                    V4 c = fragment_shader(wn, col, uv, cz, d, U, wp);
                     if (c.w > 0.0f) {                                         // :511
                         win.color[idx] = blend(c, win.color[idx], d.blend);
                         if (needsDepth) win.depth[idx] = depth;
@@ -426,6 +449,7 @@ inline void raster_tile_wire(OrcWindow& win, const SetupTri& t, const OrcDraw& d
     int tey = tsy + kTile - 1; if (tey > H - 1) tey = H - 1;
     SetupTri ends = t;                                   // Interpolate(outputs[0], outputs[1], outputs[0], 1-t, t, 0) (:314)
     ends.cz[2] = t.cz[0]; ends.cw[2] = t.cw[0]; ends.col[2] = t.col[0]; ends.uv[2] = t.uv[0]; ends.wn[2] = t.wn[0];
+    ends.wpos[2] = t.wpos[0];
     for (int k = 0; k < 3; ++k) {
         const V2 p0 = t.s[k], p1 = t.s[(k + 1) % 3];
         int minX = sat_int(net_max(net_min(p0.x, p1.x), 0.0f));                    // :242-245
@@ -456,8 +480,9 @@ inline void raster_tile_wire(OrcWindow& win, const SetupTri& t, const OrcDraw& d
                 if (!depth_pass(d.depth_test, depth, win.depth[idx])) continue;    // :318-319
                 ++st.shaded;
                 V3 wn; V4 col; V2 uv; float cz;
-                interpolate(ends, omt, tt, 0.0f, wn, col, uv, cz);
-                V4 c = fragment_shader(wn, col, uv, cz, d, U);
+                V3 wp = {0.0f, 0.0f, 0.0f};
+                interpolate(ends, omt, tt, 0.0f, wn, col, uv, cz, &wp);
+                V4 c = fragment_shader(wn, col, uv, cz, d, U, wp);
                 if (c.w != 0.0f) {                                                 // :325 (W != 0, not > 0)
                     win.color[idx] = blend(c, win.color[idx], d.blend);
                     if (d.depth_test != 0) win.depth[idx] = depth;                 // :331-332

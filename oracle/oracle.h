@@ -33,11 +33,12 @@ typedef struct OrcUniforms {
     float near_clip;         /* Rasterizer.NearClip */
     int32_t numerics_fma;    /* 1: System.Numerics Transform/Lerp fused (net9 on FMA hw) */
     int32_t tex_filter;      /* 0 nearest+repeat (reference); 1 bilinear+repeat (extension) */
-    int32_t n_extra_lights;  /* extension: extra directional lights, 0..4 */
+    int32_t n_extra_lights;  /* extension: extra lights, 0..4 */
     int32_t debug_mode;      /* Rasterizer.RenderDebugMode: 0 None, 1 Wireframe (Rasterizer.cs:419-425) */
     int32_t _pad;
-    float extra_dir[4][4];
+    float extra_dir[4][4];   /* w == 0: directional, xyz = direction; w != 0: point light, xyz = world position */
     float extra_color[4][4];
+    float extra_atten[4][4]; /* point lights: AttenuationConstant, Linear, Quadratic (Light.cs:13-15) */
 } OrcUniforms;
 
 /* One RenderMesh call (Rasterizer.cs:163-174). */

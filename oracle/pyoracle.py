@@ -22,6 +22,7 @@ class OrcUniforms(C.Structure):
         ("fog_start", C.c_float), ("fog_end", C.c_float), ("near_clip", C.c_float),
         ("numerics_fma", C.c_int32), ("tex_filter", C.c_int32), ("n_extra_lights", C.c_int32),
         ("debug_mode", C.c_int32), ("_pad", C.c_int32), ("extra_dir", (C.c_float * 4) * 4), ("extra_color", (C.c_float * 4) * 4),
+        ("extra_atten", (C.c_float * 4) * 4),
     ]
 
 
@@ -89,11 +90,15 @@ def make_uniforms(scene) -> OrcUniforms:
     u.fog_start, u.fog_end, u.near_clip = scene.fog_start, scene.fog_end, scene.near_clip
     u.numerics_fma, u.tex_filter = scene.numerics_fma, scene.tex_filter
     u.debug_mode = int(getattr(scene, "debug_mode", 0))
-    u.n_extra_lights = len(scene.extra_lights)
-    for k, (d, col) in enumerate(scene.extra_lights[:4]):
-        for i in range(3):
+    from softwarerenderer_b200.shaders import light_rows       # plain data marshalling shared with the product's binding
+    rows = light_rows(scene.extra_lights)
+    u.n_extra_lights = len(rows)
+    for k, (d, col, att) in enumerate(rows):
+        for i in range(4):
             u.extra_dir[k][i] = float(d[i])
+        for i in range(3):
             u.extra_color[k][i] = float(col[i])
+            u.extra_atten[k][i] = float(att[i])
     return u
 
 

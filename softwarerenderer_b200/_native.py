@@ -38,6 +38,7 @@ class SrbUniforms(C.Structure):
         ("_pad", C.c_int32),
         ("extra_dir", (C.c_float * 4) * 4),
         ("extra_color", (C.c_float * 4) * 4),
+        ("extra_atten", (C.c_float * 4) * 4),
     ]
 
 

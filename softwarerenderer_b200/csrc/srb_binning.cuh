@@ -54,6 +54,7 @@ __device__ __forceinline__ void agg_flush(TileAgg& a, uint32_t* __restrict__ til
         const uint32_t k = a.key[i];
         if (k) {
             const uint32_t base = atomicAdd(tileCounter + (k - 1u), a.val[i]);
+            SRB_ASSERT(MODE == 0 || base + a.val[i] >= base);
             if (MODE == 1) a.val[i] = base;
         }
     }
@@ -100,6 +101,7 @@ __device__ __forceinline__ void bin_big_body(const BigEntry* __restrict__ q, con
                 const int i = i0 + 32 * u;
                 const int yy = i / nx, xx = i - yy * nx;
                 const int tX = x0 + xx, tY = y0 + yy;
+                SRB_ASSERT(i >= n || (tX < fp.tilesX && tY >= fp.bandRow0 && tY < fp.bandRow1));
                 const bool keep = i < n && (fp.wireframe ||     // lines are not bound by the fill test; the bbox tiles are kept
                                            tile_may_cover(a.x, a.y, a.z, a.w, b.x, b.y,
                                                           max(minX, tX * kTile), min(maxX, tX * kTile + kTile - 1),
@@ -212,6 +214,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
         const unsigned long long excl = incl - mine;
         uint32_t ri = (uint32_t)base + (uint32_t)excl, bi = (uint32_t)(base >> 32) + (uint32_t)(excl >> 32);
         for (int k = 0; k < n; ++k, ++ri) {
+            SRB_ASSERT(ri < 2u * (uint32_t)fp.totalT + 64u);
             TriRef rf;
             rf.seq = out.seq[k]; rf.tx = out.tx[k]; rf.ty = out.ty[k]; rf._pad = 0;
             refs[ri] = rf;
@@ -237,7 +240,11 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
     for (int k = 0; k < out.n; ++k) {
         const int nt = tile_range_count(out.tx[k], out.ty[k]);
         if (nt <= kSmallTiles)
-            for (int j = 0; j < nt; ++j) agg_insert(agg, small_tile(out.tx[k], out.ty[k], nt, j, fp.tilesX));
+            for (int j = 0; j < nt; ++j) {
+                const int tile = small_tile(out.tx[k], out.ty[k], nt, j, fp.tilesX);
+                SRB_ASSERT(tile >= fp.bandRow0 * fp.tilesX && tile < fp.bandRow1 * fp.tilesX);
+                agg_insert(agg, tile);
+            }
     }
     __syncthreads();
     agg_flush<0>(agg, tileCount);
@@ -413,6 +420,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
                 const uint32_t extra = (c[k] + partSize - 1u) / partSize - 1u;
                 w = (extra + 1u) | (ebase << 16);          // parts (<= kMaxExtra + 1) | slice (< kMaxExtra)
                 firstEnd = excl + partSize;
+                SRB_ASSERT(ebase + extra <= kMaxExtra && extra + 1u <= 0xffffu);
                 for (uint32_t q = 1; q <= extra; ++q)
                     order[(uint32_t)nTiles + ebase + q - 1u] =
                         make_uint4((uint32_t)i, excl + q * partSize, min(excl + (q + 1u) * partSize, excl + c[k]), w);

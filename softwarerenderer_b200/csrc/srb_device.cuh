@@ -12,6 +12,16 @@
 #include <stdint.h>
 #include "../../include/srb200.h"
 
+// -DSRB_CHECKED: bounds checks of every computed index (bins, records, work items, key rows, key slices, vertex and
+// triangle indices) as device asserts.  compute-sanitizer is closed on this pool, so the whole GPU test suite is run
+// against a checked build instead (tools/checked_suite.sh); a release build compiles the checks away.
+#ifdef SRB_CHECKED
+#include <assert.h>
+#define SRB_ASSERT(c) assert(c)
+#else
+#define SRB_ASSERT(c) ((void)0)
+#endif
+
 namespace srb {
 
 constexpr int kTile = 16;                 // Rasterizer.cs:53
@@ -65,6 +75,7 @@ struct RecStore {
     float4* S;                // 2 float4 per slot
     uint32_t fan1Base;        // first slot of the second fan triangles (= total triangle count of the frame)
 };
+#define SRB_ASSERT_SLOT(st, seq) SRB_ASSERT((seq >> 1) < (st).fan1Base)
 // seq = 2*global_triangle + fan.  Fan 0 (every unclipped triangle) lives at slot global_triangle, so that a warp of
 // the setup kernel writes one contiguous run of records and the records a tile gathers sit densely in their lines;
 // the rare second triangle of a near-clipped fan lives at fan1Base + global_triangle.  (With slot = seq every other
@@ -73,6 +84,7 @@ __device__ __forceinline__ size_t rec_slot(const RecStore& st, uint32_t seq) {
     return (size_t)(seq >> 1) + ((seq & 1u) ? (size_t)st.fan1Base : 0);
 }
 __device__ __forceinline__ void store_rec(const RecStore& st, uint32_t seq, const TriRec& r) {
+    SRB_ASSERT_SLOT(st, seq);
     float4* q = st.R + 3 * rec_slot(st, seq);
     q[0] = make_float4(r.s0x, r.s0y, r.s1x, r.s1y);
     q[1] = make_float4(r.s2x, r.s2y, r.d0, r.d1);
@@ -83,6 +95,7 @@ __device__ __forceinline__ void store_rec(const RecStore& st, uint32_t seq, cons
 }
 // Coverage part only (cz/cw/meta left unset).
 __device__ __forceinline__ TriRec load_rec_raster(const RecStore& st, uint32_t seq) {
+    SRB_ASSERT_SLOT(st, seq);
     const float4* q = st.R + 3 * rec_slot(st, seq);
     float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
     TriRec r;
@@ -105,6 +118,7 @@ struct __align__(16) ClipAttr {
     float uv[3][2];
     float col[3][4];
     float wn[3][3];
+    float wpos[3][3];         // EXTENSION (point lights only): world positions, Lerp'd like the other varyings
     int32_t draw;
 };
 

@@ -312,6 +312,7 @@ struct ClipVtx {
     float uv[2];
     float col[4];
     float wn[3];
+    float wpos[3];       // EXTENSION (point lights): world position
 };
 __device__ __forceinline__ ClipVtx clipvtx_lerp(const ClipVtx& a, const ClipVtx& b, float t, bool fma) {
     ClipVtx o;                                       // Shaders.Lerp (Shaders.cs:49-95), interpolate=true
@@ -323,6 +324,8 @@ __device__ __forceinline__ ClipVtx clipvtx_lerp(const ClipVtx& a, const ClipVtx&
     for (int k = 0; k < 4; ++k) o.col[k] = lerp1(a.col[k], b.col[k], t, fma);
 #pragma unroll
     for (int k = 0; k < 3; ++k) o.wn[k] = lerp1(a.wn[k], b.wn[k], t, fma);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) o.wpos[k] = lerp1(a.wpos[k], b.wpos[k], t, fma);
     return o;
 }
 
@@ -394,6 +397,9 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int 
         v[k].uv[0] = a.w; v[k].uv[1] = b.x;
         v[k].col[0] = c.x; v[k].col[1] = c.y; v[k].col[2] = c.z; v[k].col[3] = c.w;
         v[k].wn[0] = wn.x; v[k].wn[1] = wn.y; v[k].wn[2] = wn.z;
+        const float4 wp = fma ? transform4<true>(make_float4(a.x, a.y, a.z, 1.0f), d.model)
+                              : transform4<false>(make_float4(a.x, a.y, a.z, 1.0f), d.model);      // the vertex shader's `world`
+        v[k].wpos[0] = wp.x; v[k].wpos[1] = wp.y; v[k].wpos[2] = wp.z;
     }
     atomicAdd(&cnt->nClippedTris, 1u);
     ClipVtx poly[4];
@@ -438,6 +444,8 @@ __device__ __noinline__ void setup_clipped(const DrawRec& d, int drawIndex, int 
             for (int j = 0; j < 4; ++j) ca.col[k][j] = o[k]->col[j];
 #pragma unroll
             for (int j = 0; j < 3; ++j) ca.wn[k][j] = o[k]->wn[j];
+#pragma unroll
+            for (int j = 0; j < 3; ++j) ca.wpos[k][j] = o[k]->wpos[j];
         }
         ca.draw = drawIndex;
         clipAttrs[slot] = ca;

@@ -21,7 +21,11 @@ namespace srb {
 __device__ __forceinline__ void edge_chain(const TriRec& r, const TriEq& e, int startX, int startY, int x, int y,
                                            float& w0, float& w1, float& w2) {
     row_base(r, e, startX, startY, w0, w1, w2);
+    // (unroll 4: the loop counter, compare and branch are half of a step otherwise; raster 115.4 -> 113.2 us.  A fixed
+    // 15-step loop under a predicate measured the same.)
+#pragma unroll 4
     for (int i = startY; i < y; ++i) { w0 = add(w0, e.b12); w1 = add(w1, e.b20); w2 = add(w2, e.b01); }
+#pragma unroll 4
     for (int i = startX; i < x; ++i) { w0 = add(w0, e.a12); w1 = add(w1, e.a20); w2 = add(w2, e.a01); }
 }
 
@@ -212,6 +216,7 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
     // so that lanes would run the expensive part together -- 139 -> 196 us, the lanes serialised.)
     // (Measured and rejected: a straight-line body that always computes depth and key -- 139 -> 154 us;
     // whole warps of uncovered pixels are common enough for the branch to pay.)
+    SRB_ASSERT(sx >= 0 && ex < kTile);
     for (int xx = sx; xx <= ex; ++xx) {
         // (Measured and rejected: deciding by sign bits, (s0^s1)|(s0^s2) >= 0, with the exact compares only when
         // an edge value is zero -- half the ALU-pipe work but one more branch level: 119 -> 141 us.)
@@ -329,6 +334,12 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
 #ifdef SRB_EXP_CAP_BIN
     const uint32_t be = min(be_, bs + (uint32_t)SRB_EXP_CAP_BIN);
 #endif
+    // (Measured and rejected, round 2: bins of <= 8 / 16 / 32 / 64 triangles rasterized pixel-parallel -- every
+    // thread takes its two pixels through all triangles, replaying the accumulation chain up to ITS pixel, best key in
+    // registers; no key array, scan, items or atomics, one barrier.  Raster 115 -> 119 / 123 / 135 / 151 us, gun1080
+    // 25.7 -> 26.7 / 32.6 / 42.3 / 47.1: the chain up to a pixel is dy + dx rounded adds where the row walk pays one
+    // per pixel, and the kernel is bound by instruction issue, not by the latency the variant removes.
+    // profiles/r02k_ab_light_tile_path.txt)
     const unsigned long long ckey = clear_key<MODE>();
     for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
 
@@ -373,6 +384,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         }
         {   // expand the work items: cheaper than a search per item (123 -> 121 us)
             unsigned short* it = sm.items + (woff + incl - nrows);
+            SRB_ASSERT(nrows >= 0 && nrows <= kTile && woff + incl <= kVisThreads * kTile);
             for (int r = 0; r < nrows; ++r) it[r] = (unsigned short)(tid | (r << 8));
         }
         __syncthreads();
@@ -397,6 +409,8 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
             const uint32_t pk = __float_as_uint(S[13][j]);
             const uint32_t seq = __float_as_uint(S[14][j]);
             const int sx = pk & 0xff, ex = (pk >> 8) & 0xff, row = (int)(pk >> 16) + dy;
+            SRB_ASSERT(j < kVisThreads && row >= 0 && row < kTile);
+#pragma unroll 4
             for (int k = 0; k < dy; ++k) { w0 = add(w0, b12); w1 = add(w1, b20); w2 = add(w2, b01); }
             vis_walk_row<MODE>(w0, w1, w2, a12, a20, a01, invArea, d0, d1, d2, seq, keys + row * kKeyPitch, sx, ex);
         }
@@ -410,6 +424,7 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     if (parts > 1u) {
         // One of several CTAs of a split bin: merge this part's keys into the bin's global slice; whoever arrives
         // last takes the merged keys back (leaving the slice and its counter zero for the next user) and resolves.
+        SRB_ASSERT(slice < kMaxExtra && parts <= kMaxExtra + 1u);
         unsigned long long* gk = A.gkeys + (size_t)slice * (kTile * kTile);
         for (int i = tid; i < kTile * kTile; i += kVisThreads) {
             const unsigned long long k = keys[(i >> 4) * kKeyPitch + (i & 15)];
@@ -455,6 +470,7 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     const uint4 o = __ldg(A.order + (extra ? (uint32_t)A.bandTiles + blockIdx.x : blockIdx.x - kMaxExtra));
     if (A.cnt->overflow) return;
     if (extra && blockIdx.x >= A.cnt->nExtra) return;       // unused slot (stale entry of an earlier frame)
+    SRB_ASSERT((int)o.x >= fp.bandRow0 * fp.tilesX && (int)o.x < fp.bandRow1 * fp.tilesX && o.y <= o.z && o.z <= fp.pairCap);
 #ifdef SRB_TILE_TIMING
     unsigned long long t0, t1;
     unsigned smid;

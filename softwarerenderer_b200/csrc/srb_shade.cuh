@@ -89,6 +89,7 @@ __device__ __forceinline__ float4 shade_fragment(const RasterArgs& A, const Fram
     float uv[3][2], col[3][4], wn[3][3];
     int di;
     if (r.meta & 0x80000000u) {
+        SRB_ASSERT((r.meta & 0x7fffffffu) < fp.clipCap);
         const ClipAttr& ca = A.clipAttrs[r.meta & 0x7fffffffu];
         di = ca.draw;
 #pragma unroll
@@ -103,9 +104,11 @@ __device__ __forceinline__ float4 shade_fragment(const RasterArgs& A, const Fram
         di = (int)r.meta;
         const DrawRec& d = A.draws[di];
         int t = (int)(seq >> 1) - d.tbase;
+        SRB_ASSERT(di >= 0 && di < fp.nDraws && t >= 0 && t < d.n_triangles);
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             int vi = (int)__ldg(d.idx + 3 * t + (2 - k));     // outputs {v2,v1,v0} (:367)
+            SRB_ASSERT(vi < d.n_vertices);
             float4 a = __ldg(d.vtx + 3 * vi), b = __ldg(d.vtx + 3 * vi + 1), c = __ldg(d.vtx + 3 * vi + 2);
             float4 n = __ldg(A.wn + d.vbase + vi);
             uv[k][0] = a.w; uv[k][1] = b.x;
@@ -155,8 +158,45 @@ __device__ __forceinline__ float4 shade_fragment(const RasterArgs& A, const Fram
     float k = add(0.1f, mul(0.9f, diffuse));
     float lx = mul(mul(bx, k), U.light_color[0]), ly = mul(mul(by, k), U.light_color[1]);
     float lz = mul(mul(bz, k), U.light_color[2]);
-    for (int i = 0; i < U.n_extra_lights && i < 4; ++i) {      // EXTENSION: extra directional lights
-        float di2 = net_max(0.0f, dot3(nx, ny, nz, -U.extra_dir[i][0], -U.extra_dir[i][1], -U.extra_dir[i][2]));
+    // EXTENSION (BASELINE config 5; oracle = our restatement only): extra lights add Color * max(0, N.L) * base.
+    // Directional: L = -Direction.  Point (Light.cs:9, 13-15): L = normalised (Position - world position of the
+    // fragment), scaled by 1 / (c + l*d + q*d*d); the world position is the vertex shader's `world`
+    // (Renderer.cs:832) interpolated perspective-correctly like the other Vector3 varyings (Rasterizer.cs:598-606).
+    float wpx = 0.0f, wpy = 0.0f, wpz = 0.0f;
+    bool anyPoint = false;
+    for (int i = 0; i < U.n_extra_lights && i < 4; ++i) anyPoint = anyPoint || U.extra_dir[i][3] != 0.0f;
+    if (anyPoint) {                                            // uniform over the frame; the stock path pays nothing
+        float wp[3][3];
+        if (r.meta & 0x80000000u) {
+            const ClipAttr& ca = A.clipAttrs[r.meta & 0x7fffffffu];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { wp[k][0] = ca.wpos[k][0]; wp[k][1] = ca.wpos[k][1]; wp[k][2] = ca.wpos[k][2]; }
+        } else {
+            const int t = (int)(seq >> 1) - d.tbase;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int vi = (int)__ldg(d.idx + 3 * t + (2 - k));
+                const float4 a = __ldg(d.vtx + 3 * vi);
+                const float4 w4 = fma ? transform4<true>(make_float4(a.x, a.y, a.z, 1.0f), d.model)
+                                      : transform4<false>(make_float4(a.x, a.y, a.z, 1.0f), d.model);
+                wp[k][0] = w4.x; wp[k][1] = w4.y; wp[k][2] = w4.z;
+            }
+        }
+        if (LINE) { wp[2][0] = wp[0][0]; wp[2][1] = wp[0][1]; wp[2][2] = wp[0][2]; }
+        wpx = persp(wp[0][0], wp[1][0], wp[2][0]);
+        wpy = persp(wp[0][1], wp[1][1], wp[2][1]);
+        wpz = persp(wp[0][2], wp[1][2], wp[2][2]);
+    }
+    for (int i = 0; i < U.n_extra_lights && i < 4; ++i) {
+        float lx_ = -U.extra_dir[i][0], ly_ = -U.extra_dir[i][1], lz_ = -U.extra_dir[i][2], att = 1.0f;
+        if (U.extra_dir[i][3] != 0.0f) {
+            const float Lx = sub(U.extra_dir[i][0], wpx), Ly = sub(U.extra_dir[i][1], wpy), Lz = sub(U.extra_dir[i][2], wpz);
+            const float dist = __fsqrt_rn(dot3(Lx, Ly, Lz, Lx, Ly, Lz));
+            const float inv = fdiv(1.0f, dist);
+            lx_ = mul(Lx, inv); ly_ = mul(Ly, inv); lz_ = mul(Lz, inv);
+            att = fdiv(1.0f, add(add(U.extra_atten[i][0], mul(U.extra_atten[i][1], dist)), mul(U.extra_atten[i][2], mul(dist, dist))));
+        }
+        float di2 = mul(net_max(0.0f, dot3(nx, ny, nz, lx_, ly_, lz_)), att);
         lx = add(lx, mul(mul(bx, di2), U.extra_color[i][0]));
         ly = add(ly, mul(mul(by, di2), U.extra_color[i][1]));
         lz = add(lz, mul(mul(bz, di2), U.extra_color[i][2]));

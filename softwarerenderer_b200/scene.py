@@ -356,7 +356,13 @@ def scene_stress(width: int, height: int, n_meshes: int = 155, grid: int = 181, 
     sc = Scene(width, height, draws, fog_end=80.0, name=f"stress{n_meshes}x{grid}-{width}x{height}")
     if extensions:
         sc.tex_filter = 1
-        sc.extra_lights = [((0.0, -1.0, 0.0), (0.3, 0.3, 0.5)), ((-0.7, 0.0, -0.7), (0.4, 0.2, 0.1)),
-                           ((0.6, 0.6, -0.5), (0.1, 0.3, 0.1))]
+        # 4 lights in all: the stock directional one + a directional and two point lights with
+        # the reference's attenuation fields (Light.cs:13-15), placed among the stacked meshes
+        from .shaders import Light
+        sc.extra_lights = [Light(Direction=(0.0, -1.0, 0.0), Color=(0.3, 0.3, 0.5)),
+                           Light(Type="Point", Position=(3.0, 2.0, -8.0), Color=(1.6, 0.8, 0.4),
+                                 AttenuationConstant=1.0, AttenuationLinear=0.09, AttenuationQuadratic=0.032),
+                           Light(Type="Point", Position=(-12.0, -6.0, -30.0), Color=(0.4, 1.2, 2.0),
+                                 AttenuationConstant=1.0, AttenuationLinear=0.045, AttenuationQuadratic=0.0075)]
         sc.name += "-ext"
     return sc

@@ -130,3 +130,31 @@ class Texture:
 
     def Dispose(self) -> None:
         self._handles.clear()
+
+
+class Light:
+    """Light (Light.cs:7-33): the fields the extension lights of BASELINE config 5 use.  The reference's stock
+    fragment shader has ONE directional light; extra lights are an extension: directional
+    (`Type="Directional"`, `Direction`) or point (`Type="Point"`, `Position`, attenuation 1/(c + l*d + q*d*d))."""
+
+    def __init__(self, Position=(0.0, 0.0, 0.0), Direction=(0.0, -1.0, 0.0), Color=(1.0, 1.0, 1.0), Type="Directional",
+                 AttenuationConstant=1.0, AttenuationLinear=0.0, AttenuationQuadratic=0.0):
+        self.Position, self.Direction, self.Color, self.Type = tuple(Position), tuple(Direction), tuple(Color), Type
+        self.AttenuationConstant, self.AttenuationLinear, self.AttenuationQuadratic = (
+            float(AttenuationConstant), float(AttenuationLinear), float(AttenuationQuadratic))
+
+
+def light_rows(extra_lights):
+    """Extra lights -> rows (dir_or_pos4, color3, atten3) of SrbUniforms / OrcUniforms.  Entries are Light objects or
+    (direction3, color3) pairs (directional)."""
+    rows = []
+    for l in list(extra_lights)[:4]:
+        if isinstance(l, Light):
+            if l.Type == "Point":
+                rows.append(((*l.Position, 1.0), l.Color, (l.AttenuationConstant, l.AttenuationLinear, l.AttenuationQuadratic)))
+            else:
+                rows.append(((*l.Direction, 0.0), l.Color, (1.0, 0.0, 0.0)))
+        else:
+            d, col = l
+            rows.append(((*d, 0.0), col, (1.0, 0.0, 0.0)))
+    return rows

@@ -30,7 +30,7 @@ class Uniforms:
         self.FogEnd = 25.0
         self.NumericsFma = 1
         self.TexFilter = 0            # 0 nearest (reference), 1 bilinear (extension)
-        self.ExtraLights = []         # extension: list of (direction3, color3)
+        self.ExtraLights = []         # extension: Light objects (directional or point) or (direction3, color3) pairs
 
     def to_struct(self, near_clip: float, debug_mode: int = 0) -> N.SrbUniforms:
         u = N.SrbUniforms()
@@ -42,11 +42,15 @@ class Uniforms:
         u.fog_start, u.fog_end, u.near_clip = float(self.FogStart), float(self.FogEnd), float(near_clip)
         u.numerics_fma, u.tex_filter = int(self.NumericsFma), int(self.TexFilter)
         u.debug_mode = int(debug_mode)
-        u.n_extra_lights = len(self.ExtraLights)
-        for k, (d, col) in enumerate(self.ExtraLights[:4]):
-            for i in range(3):
+        from .shaders import light_rows
+        rows = light_rows(self.ExtraLights)
+        u.n_extra_lights = len(rows)
+        for k, (d, col, att) in enumerate(rows):
+            for i in range(4):
                 u.extra_dir[k][i] = float(d[i])
+            for i in range(3):
                 u.extra_color[k][i] = float(col[i])
+                u.extra_atten[k][i] = float(att[i])
         return u
 
 

@@ -68,13 +68,74 @@ def test_stress_small(oracle, pipeline):
     print(compare(gc, gd, oc, od))
 
 
-def test_stress_extensions(oracle):
-    """Bilinear + extra lights (extensions; oracle = our restatement only)."""
+@pytest.mark.parametrize("pipeline", [1, 2])
+def test_stress_extensions(oracle, pipeline):
+    """Bilinear + extra lights, directional and point (extensions; oracle = our restatement only)."""
     from softwarerenderer_b200 import scene as S
     sc = S.scene_stress(640, 360, n_meshes=6, grid=61, extensions=True)
     oc, od, _ = oracle.render_scene(sc, threads=8)
+    plain = S.scene_stress(640, 360, n_meshes=6, grid=61)
+    pc, _, _ = oracle.render_scene(plain, threads=8)
+    assert np.abs(oc - pc).max() > 0.05                    # the lights do something
+    gc, gd, st = _render_gpu(sc, pipeline)
+    stats = compare(gc, gd, oc, od)
+    assert stats["float_max_err"] < 1e-5, stats
+
+
+def test_point_lights_on_near_clipped_and_wireframe_geometry(oracle):
+    """The world-position varying of the point-light extension goes through Shaders.Lerp in the near clipper and
+    through the DrawLine interpolation (corner 2 = corner 0) like every other varying."""
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.shaders import Light
+    for fma in (0, 1):
+        sc = S.scene_city(640, 360, n_instances=24)
+        sc.numerics_fma = fma
+        sc.fog_end = 600.0                                  # the default fog (1 -> 25) hides everything the light reaches
+        plain, _, _ = oracle.render_scene(sc, threads=8)
+        sc.extra_lights = [Light(Type="Point", Position=(182.0, 6.0, 100.0), Color=(2.0, 1.5, 1.0), AttenuationLinear=0.02,
+                                 AttenuationQuadratic=0.001),
+                           Light(Direction=(0.3, -0.8, 0.2), Color=(0.2, 0.2, 0.4))]
+        oc, od, _ = oracle.render_scene(sc, threads=8)
+        assert np.abs(oc - plain).max() > 0.2
+        for pipeline in (1, 2):
+            gc, gd, st = _render_gpu(sc, pipeline)
+            stats = compare(gc, gd, oc, od)
+            assert stats["float_max_err"] < 1e-5, stats
+        # triangles through the near clipper (one corner behind the eye), lit by a point light close to them
+        from softwarerenderer_b200 import numerics as nm
+        from softwarerenderer_b200.scene import DrawItem, Mesh, Scene, default_projection
+        from softwarerenderer_b200.shaders import Material, Shaders
+        pos = [(-1, -1, -3), (1, -1, -3), (0, 1, 2), (-2, -0.5, 0.0), (2, -0.5, 0.0), (0, 0.5, -4),
+               (-1, 0.2, -2), (1, 0.2, -2), (0, 1.0, -2), (-3, -2, -6), (3, -2, -6), (0, 0.3, 1.0)]
+        mesh = Mesh(Shaders.make_vertices(pos), np.arange(12, dtype=np.uint16), Material())
+        I = nm.identity()
+        cs = Scene(320, 192, [DrawItem(mesh, I, I, default_projection(320, 192), cull=0)], fog_end=600.0)
+        cs.numerics_fma = fma
+        cs.extra_lights = [Light(Type="Point", Position=(0.3, 0.5, -1.0), Color=(1.5, 1.0, 0.5), AttenuationQuadratic=0.1)]
+        oc, od, _ = oracle.render_scene(cs, threads=2)
+        for pipeline in (1, 2):
+            gc, gd, st = _render_gpu(cs, pipeline)
+            stats = compare(gc, gd, oc, od)
+            assert st.clipped_triangles >= 2 and stats["float_max_err"] < 1e-5, (st.clipped_triangles, stats)
+    w = S.scene_model("Gun", 640, 360)
+    w.debug_mode = 1
+    w.extra_lights = [Light(Type="Point", Position=(0.5, 0.5, 4.0), Color=(3.0, 3.0, 3.0), AttenuationQuadratic=0.2)]
+    oc, od, _ = oracle.render_scene(w, threads=4)
+    gc, gd, _ = _render_gpu(w, 0)
+    assert compare(gc, gd, oc, od)["float_max_err"] < 1e-5
+
+
+def test_stress8k_ext_full_size(oracle):
+    """BASELINE config 5 AS STATED, full size on one GPU: 10,044,000 small triangles at 7680x4320 with the bilinear
+    filter and four lights (two of them point lights).  Extensions: the oracle is our restatement only."""
+    import os
+    from softwarerenderer_b200 import scene as S
+    sc = S.scene_stress(7680, 4320, extensions=True)
+    oc, od, ost = oracle.render_scene(sc, threads=os.cpu_count() or 8)
     gc, gd, st = _render_gpu(sc, 0)
-    print(compare(gc, gd, oc, od))
+    stats = compare(gc, gd, oc, od)
+    assert st.triangles_setup + st.triangles_no_coverage == ost.triangles_drawn
+    print(stats)
 
 
 def test_bands_equal_full_frame(oracle):

@@ -340,6 +340,37 @@ def test_fragment_shader_lighting_floor_fog_and_ambient(oracle):
     assert np.allclose(c[2, 2, :3], 0.5 * np.array((1.0, 0.62, 0.5)) + 0.5 * np.array(col[:3]), atol=1e-6)
 
 
+def test_extension_point_light_attenuation_and_direction(oracle):
+    """EXTENSION (BASELINE config 5; not in the reference's shader): a point light adds
+    Color * max(0, N.L) / (c + l*d + q*d*d) * base with L from the fragment's world position to Light.Position
+    (Light.cs:9, 13-15).  Identity matrices: world position = the NDC position of the pixel."""
+    from softwarerenderer_b200.shaders import Light
+    t = [(0, 0), (15, 0), (0, 15)]
+    col = (0.8, 0.6, 0.4, 1.0)
+    sc = screen_tri_scene(16, 16, [t], colors=[col], cull=0)
+    sc.light_dir = np.array((0, 0, 1), np.float32)            # stock light from behind: the 0.25 floor, k = 0.325
+    lc = (0.9, 0.6, 0.3)
+    sc.extra_lights = [Light(Type="Point", Position=(-0.75, 0.75, 2.5), Color=lc, AttenuationConstant=1.0,
+                             AttenuationLinear=0.5, AttenuationQuadratic=0.25)]
+    c, _, _ = _render(oracle, sc)
+    # pixel (2,2): world (-0.75, 0.75, 0.5) straight below the light: d = 2, N.L = 1, attenuation 1/(1+1+1)
+    want = np.array(col[:3]) * (0.325 + np.array(lc) / 3.0)
+    assert np.allclose(c[2, 2, :3], want, atol=1e-6)
+    # pixel (6,3): off axis, in float64
+    wp = np.array([2 * 6 / 16 - 1, 1 - 2 * 3 / 16, 0.5])
+    L = np.array([-0.75, 0.75, 2.5]) - wp
+    d = np.linalg.norm(L)
+    want = np.array(col[:3]) * (0.325 + np.array(lc) * (L[2] / d) / (1.0 + 0.5 * d + 0.25 * d * d))
+    assert np.allclose(c[3, 6, :3], want, atol=2e-6)
+    # a light behind the surface adds nothing; a directional extra light ignores position and attenuation
+    sc.extra_lights = [Light(Type="Point", Position=(-0.75, 0.75, -2.5), Color=lc)]
+    c, _, _ = _render(oracle, sc)
+    assert np.allclose(c[2, 2, :3], np.array(col[:3]) * 0.325, atol=1e-6)
+    sc.extra_lights = [Light(Direction=(0, 0, -1), Color=lc, AttenuationLinear=5.0)]
+    c, _, _ = _render(oracle, sc)
+    assert np.allclose(c[2, 2, :3], np.array(col[:3]) * (0.325 + np.array(lc)), atol=1e-6)
+
+
 def test_perspective_correct_interpolation(oracle):
     """Interpolate (Rasterizer.cs:566-640): attribute = sum(A_i * r_i) / sum(r_i), r_i = bary_i / w_i."""
     from softwarerenderer_b200 import numerics as nm
