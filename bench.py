@@ -479,36 +479,52 @@ def run_gpu(args):
                 f.truncate(nbytes)                       # sparse: no page exists yet
         dist.barrier()
         shared = np.memmap(shm_path, dtype=np.float32, mode="r+", shape=(2, H, W, 3))
-        # ONE frame in shared host memory, but every rank touches ITS rows first, from a CPU next to its GPU: the
-        # pages then live on the NUMA node its PCIe link is attached to.  (With the whole frame on one node the 8
-        # links of a box shared that node's memory bandwidth: 960 frames/s at N=8, 100 GB/s into one node.)
+        # ONE frame in shared host memory; every rank touches ITS rows first, from a CPU next to its GPU, so that on a
+        # multi-socket host the pages live on the node its PCIe link is attached to.  (The 8-GPU boxes of this pool
+        # are single-node guests -- profiles/r02o_nvidia_smi_topo.txt -- and take 65-100 GB/s from all GPUs together,
+        # whatever the placement: that, not the links, bounds the 12 B/pixel frame at N >= 4.)
         numa_cpus = None if args.no_numa_bind else bind_to_gpu_numa(local)
-        regs = []
         for b in range(2):
-            shared[b, ye0:ye1] = 0.0
+            shared[b, ye0:ye1] = 0.0                     # first touch of this rank's rows
         dist.barrier()
-        page = 4096
-        for b in range(2):
-            a0 = shared[b, ye0:ye1].ctypes.data if ye1 > ye0 else 0
-            n0 = (ye1 - ye0) * W * 12
-            if n0:
-                lo = a0 // page * page
-                hi = (a0 + n0 + page - 1) // page * page
-                rc = torch.cuda.cudart().cudaHostRegister(lo, hi - lo, 0)
-                if int(rc) != 0 and regs and lo < regs[-1][1]:      # the two ranges share a page (tiny bands)
-                    continue
-                assert int(rc) == 0, "cudaHostRegister failed: %s" % rc
-                regs.append((lo, hi))
+        rc = torch.cuda.cudart().cudaHostRegister(shared.ctypes.data, nbytes, 0)
+        assert int(rc) == 0, "cudaHostRegister failed: %s" % rc
         par_count = [0]
 
+        trace = {}
+
+        def tick(name, t0):
+            t1 = time.perf_counter()
+            trace[name] = trace.get(name, 0.0) + (t1 - t0)
+            return t1
+
         def step_e2e_parallel():
+            t = time.perf_counter()
+            N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
+            N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
+            t = tick("begin+submit", t)
+            N.check(ctx, L.srb_end_frame(ctx))
+            t = tick("end_frame", t)
+            N.check(ctx, L.srb_present_fence(ctx))   # stream waits for the copies of the frames before this one
+            hard_barrier()                           # => on every rank: all bands of the previous frame have landed
+            t = tick("fence+barrier", t)
+            N.check(ctx, L.srb_present_rgb_rows_async(ctx, C.c_void_p(shared[par_count[0] & 1].ctypes.data), ye0, ye1))
+            tick("present_rows", t)
+            par_count[0] += 1
+
+        # the same frame at display precision, 4 B per pixel: the first third of each float buffer's rows serves as
+        # the RGBA8 frame (same registered pages)
+        flat8 = [shared[b].reshape(-1).view(np.uint8)[: H * W * 4].reshape(H, W, 4) for b in range(2)]
+        par8_count = [0]
+
+        def step_e2e_parallel_rgba8():
             N.check(ctx, L.srb_begin_frame(ctx, clear, N.SRB_CLEAR_COLOR | N.SRB_CLEAR_DEPTH))
             N.check(ctx, L.srb_submit_draws(ctx, N.ptr(cmds), cmds.shape[0]))
             N.check(ctx, L.srb_end_frame(ctx))
-            N.check(ctx, L.srb_present_fence(ctx))   # stream waits for the copies of the frames before this one
-            hard_barrier()                           # => on every rank: all bands of the previous frame have landed
-            N.check(ctx, L.srb_present_rgb_rows_async(ctx, C.c_void_p(shared[par_count[0] & 1].ctypes.data), ye0, ye1))
-            par_count[0] += 1
+            N.check(ctx, L.srb_present_fence(ctx))
+            hard_barrier()
+            N.check(ctx, L.srb_present_rgba8_rows_async(ctx, C.c_void_p(flat8[par8_count[0] & 1].ctypes.data), ye0, ye1))
+            par8_count[0] += 1
 
         ms_p, wall_p, _ = timed(step_e2e_parallel, Ke, 3)
         N.check(ctx, L.srb_present_wait(ctx))
@@ -518,14 +534,29 @@ def run_gpu(args):
         ok = bool(np.array_equal(shared[(par_count[0] - 1) & 1][ye0:ye1], win.ColorBuffer[ye0:ye1, :, :3]))
         oks = [None] * world
         dist.all_gather_object(oks, ok)
+        e2e_parallel_rgba8 = None
+        if True:
+            K8p = max(Ke, min(K, 4 * args.e2e_steps))
+            ms_q, wall_q, _ = timed(step_e2e_parallel_rgba8, K8p, 3)
+            N.check(ctx, L.srb_present_wait(ctx))
+            dist.barrier()
+            want8 = np.rint(np.clip(win.ColorBuffer[ye0:ye1], 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+            ok8 = bool(np.array_equal(flat8[(par8_count[0] - 1) & 1][ye0:ye1], want8))
+            oks8 = [None] * world
+            dist.all_gather_object(oks8, ok8)
+            e2e_parallel_rgba8 = {"value": K8p / max(wall_q, ms_q / 1000.0), "unit": "frames/s", "steps": K8p,
+                                  "d2h_bytes_per_step": int(W * H * 4), "rows_verified": all(oks8),
+                                  "call": "srb_present_rgba8_rows_async, every rank its own rows into one shared pinned host frame"}
         e2e_parallel = {"value": fps_p, "unit": "frames/s", "ms_per_step": 1000.0 * max(wall_p, ms_p / 1000.0) / Ke,
+                        "rgba8_present_parallel": e2e_parallel_rgba8,
                         "d2h_bytes_per_step": int(W * H * 12), "rows_verified": all(oks),
                         "cuts_tile_rows": [int(x) for x in cuts_e2e], "numa_bound_cpus": numa_cpus,
+                        "host_us_per_call_rank0": {k: round(1e6 * v / (Ke + 3), 1) for k, v in trace.items()},
                         "cuts_policy": "minimise max over ranks of (render + rows x 12 B / %.0f GB/s)" % args.pcie_gbs,
                         "result": "every band rank copies its own rows of the packed RGB float frame into one shared "
                                   "pinned host frame over its own PCIe link (srb_present_rgb_rows_async); no NVLink gather"}
-        for lo, _ in regs:
-            torch.cuda.cudart().cudaHostUnregister(lo)
+        torch.cuda.cudart().cudaHostUnregister(shared.ctypes.data)
+        del flat8
         del shared
         dist.barrier()
         if rank == 0:

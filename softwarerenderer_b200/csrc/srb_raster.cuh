@@ -231,6 +231,8 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
 #ifdef SRB_EXP_NO_ATOMIC                         /* diagnostic builds only (tools/tile_breakdown.sh): wrong images */
             krow[xx] = depth == depth ? key : 0ull;
 #else
+            // (Measured and rejected, round 2: in the second and later chunks of a bin, a plain load of the stored key
+            // first and no atomic when the fragment loses -- raster 111.2 -> 113.4 us, stress8k 1106 -> 1143.)
             atomicMax(krow + xx, depth == depth ? key : 0ull);
 #endif
         }
@@ -467,6 +469,9 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
     // The extra entries of split bins (heavy work, behind the one-per-tile entries in memory) are launched first.
     const bool extra = blockIdx.x < kMaxExtra;
+    // (Measured and rejected, round 2: the order entry carrying the tile as column | row << 16 to spare every CTA the
+    // division below -- the tile kernel did not move, the scan kernel paid 2.4 us for the division.
+    // profiles/r02r_ab_txy_precheck.txt)
     const uint4 o = __ldg(A.order + (extra ? (uint32_t)A.bandTiles + blockIdx.x : blockIdx.x - kMaxExtra));
     if (A.cnt->overflow) return;
     if (extra && blockIdx.x >= A.cnt->nExtra) return;       // unused slot (stale entry of an earlier frame)
