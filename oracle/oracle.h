@@ -68,6 +68,7 @@ float* orc_color(OrcWindow* w);   /* W*H*4 floats */
 float* orc_depth(OrcWindow* w);   /* W*H floats   */
 void  orc_clear_color(OrcWindow* w, const float rgba[4]);  /* MainWindow.cs:400-407 */
 void  orc_clear_depth(OrcWindow* w);                       /* MainWindow.cs:429-436 */
+void  orc_clear_frame_mt(OrcWindow* w, const float rgba[4], int n_threads);   /* both, Parallel.For as in the reference */
 
 /* Literal single-thread path, reference loop order (triangle -> tile row -> tile -> y -> x). */
 void orc_render_mesh(OrcWindow* w, const OrcDraw* d, const OrcUniforms* u);

@@ -65,6 +65,7 @@ def lib() -> C.CDLL:
         L.orc_depth.restype = C.POINTER(C.c_float)
         L.orc_clear_color.argtypes = [vp, C.POINTER(C.c_float)]
         L.orc_clear_depth.argtypes = [vp]
+        L.orc_clear_frame_mt.argtypes = [vp, C.POINTER(C.c_float), C.c_int]
         L.orc_render_mesh.argtypes = [vp, C.POINTER(OrcDraw), C.POINTER(OrcUniforms)]
         L.orc_render_frame_mt.argtypes = [vp, C.POINTER(OrcDraw), C.c_int, C.POINTER(OrcUniforms), C.c_int, C.c_int, C.c_int]
         L.orc_sphere_in_frustum.argtypes = [vp, vp, vp, vp, C.c_int]

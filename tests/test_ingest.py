@@ -5,6 +5,7 @@ import json
 import os
 
 import numpy as np
+import pytest
 
 
 def _write_gltf(tmp_path, with_texture=True):
@@ -90,3 +91,59 @@ def test_packed_assets_are_what_the_loader_produces():
     assert all(m.Vertices.dtype.itemsize == 48 and m.Indices.dtype == np.uint16 for m in gun.Meshes)
     tex = [m.Texture for m in gun.Meshes if m.Texture is not None]
     assert tex and tex[0].Width == 2048 and tex[0].Height == 2048
+
+
+FIXTURE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "gltf", "gordon_freeman", "scene.gltf")
+
+
+def test_bundled_gltf_fixture_loads_to_the_packed_arrays():
+    """tests/golden/gltf/gordon_freeman is the reference's own OutputAssets model (CC-BY-NC, license.txt beside it),
+    kept as a fixture so that Model.LoadModel runs on real exporter output where /root/reference does not exist.
+    The loader's arrays must be the packed ones every other test and the bench use."""
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import Model, load_pack
+    loaded = Model().LoadModel(FIXTURE).Meshes
+    packed = load_pack(os.path.join(S._repo_assets(), "gordon_freeman.npz"))
+    assert len(loaded) == len(packed) and len(loaded) >= 2
+    for a, b in zip(loaded, packed):
+        assert np.array_equal(np.ascontiguousarray(a.Vertices).view(np.float32), np.ascontiguousarray(b.Vertices).view(np.float32))
+        assert np.array_equal(a.Indices, b.Indices)
+        assert (a.Texture is None) == (b.Texture is None)
+        if a.Texture is not None:
+            assert np.array_equal(a.Texture.pixels, b.Texture.pixels)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", [1, 2])
+def test_gltf_to_device_to_oracle(oracle, pipeline):
+    """Ingest on the device side of the boundary: Model().LoadModel(glTF) -> Rasterizer.RenderMesh
+    with the loader's own arrays -> CUDA frame, against the oracle fed the same arrays (ModelLoader.cs:145-217,
+    Renderer.cs:444-459)."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import DrawItem, Model, Scene, default_projection, submit_scene
+    from tests.util import compare
+    model = Model().LoadModel(FIXTURE)
+    W, H = 960, 540
+    view = nm.create_look_at((0.5, 1.0, 1.1), (0.0, 0.9, 0.0), (0, 1, 0))
+    M = nm.create_rotation_y(0.4)
+    sc = Scene(W, H, [DrawItem(m, M, view, default_projection(W, H)) for m in model.Meshes], fog_end=60.0)
+    oc, od, ost = oracle.render_scene(sc, threads=8)
+    assert (od != od.min()).mean() > 0.02
+    win = srb.MainWindow(W, H)
+    try:
+        win.SetPipeline(pipeline)
+        submit_scene(win, sc)
+        stats = compare(win.ColorBuffer, win.DepthBuffer, oc, od)
+        # the same arrays again: served from the identity cache (no second upload), same image
+        n_meshes = len(win._mesh_by_content)
+        submit_scene(win, sc)
+        assert len(win._mesh_by_content) == n_meshes == len(model.Meshes)
+        compare(win.ColorBuffer, win.DepthBuffer, oc, od)
+        # explicit resident handles in place of the arrays
+        handles = [win.CreateMesh(m.Vertices, m.Indices) for m in model.Meshes]
+        assert [h.handle for h in handles] == [win.mesh_handle(m.Vertices, m.Indices) for m in model.Meshes]
+    finally:
+        win.Close()
+    print(stats)
