@@ -447,6 +447,14 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         __syncthreads();
     }
     // ---- resolve: shade each pixel's winner once, write colour + depth ----
+    // (Measured and rejected, round 2 -- the one TMA / bulk-async experiment the path offers: the finished tile staged
+    // in shared memory (the dead raster-constant array) and written back by the bulk-copy engine, 16 colour rows of
+    // 256 B + 16 depth rows of 64 B per tile with cp.async.bulk.global.shared::cta (UBLKCP.G.S in SASS,
+    // profiles/r02t_sass_bulk_store_experiment_UBLKCP.txt), instead of per-thread 128-bit streaming stores.  Same
+    // images (87 GPU tests), slower everywhere: raster city4k 112.7 -> 129.9 us, gun1080 25.0 -> 27.1, stress8k
+    // 1103 -> 1243 (profiles/r02t_ab_bulk_async_tile_store.txt).  The stores were never the cost -- they leave the
+    // thread at issue --, while the staging adds a barrier, a proxy fence and 32 serial bulk issues to every tile.
+    // The tile's INPUTS are gathers of 48-byte records by index, nothing a tensor map describes.)
     vis_resolve<MODE, OUT8>(keys, ckey, tx0, ty0, clearCol, A, fp, U);
 }
 
