@@ -194,7 +194,7 @@ class _DevArray:
 
 
 STAGES = ["frustum", "vertex", "setup_count", "scan", "fill", "sort", "tile_raster"]
-DRAW_REC_BYTES = 368
+DRAW_REC_BYTES = 384
 
 
 def run_gpu(args):

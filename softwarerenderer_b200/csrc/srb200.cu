@@ -22,7 +22,7 @@ namespace {
 
 thread_local std::string g_createError;
 
-struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; float4* blockSpheres = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
+struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; float4* blockSpheres = nullptr; int2* blockVRange = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
 struct TexRes { uchar4* px = nullptr; int w = 0, h = 0; bool opaque = true, alive = false; };
 
 template <typename T>
@@ -285,6 +285,10 @@ int launch_frame(SrbContext* c) {
         frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(B.dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
                                                                                 fp.bandRow1, fp.tilesY, B.dVBlocks.p, B.dTBlocks.p);
         ++launches;
+        if (!fullFrame) {                                  // band context: block tables culled to the band
+            band_blocks_kernel<<<fp.nDraws, 128, 0, gs>>>(B.dDraws.p, B.dCnt, B.dVBlocks.p, B.dTBlocks.p);
+            ++launches;
+        }
     }
     CK(c, cudaEventRecord(B.geomStarted, gs));
     mark(1);
@@ -511,7 +515,7 @@ int srb_destroy(SrbContext* c) {
     if (c->barRow) cudaFree(c->barRow);
     if (c->barTimedOut) cudaFreeHost(c->barTimedOut);
     if (c->color8) cudaFree(c->color8);
-    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); }
+    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); cudaFree(m.blockVRange); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
 
     if (c->dSliceKeys) cudaFree(c->dSliceKeys);
@@ -784,6 +788,16 @@ int srb_mesh_create(SrbContext* c, const float* vertices, int nV, const uint16_t
         }
         CK(c, cudaMalloc((void**)&m.blockSpheres, sph.size() * sizeof(float4)));
         CK(c, cudaMemcpy(m.blockSpheres, sph.data(), sph.size() * sizeof(float4), cudaMemcpyHostToDevice));
+        // lowest / highest vertex index of every run (band contexts transform only the vertex runs a kept block uses)
+        std::vector<int2> vr((size_t)std::max(nB, 1), make_int2(0, 0));
+        for (int b = 0; b < nB; ++b) {
+            const int t0 = b * kGeomBlock, t1 = std::min(nT, t0 + kGeomBlock);
+            int lo = 65535, hi = 0;
+            for (int i = 3 * t0; i < 3 * t1; ++i) { lo = std::min<int>(lo, indices[i]); hi = std::max<int>(hi, indices[i]); }
+            vr[b] = make_int2(std::min(lo, hi), hi);
+        }
+        CK(c, cudaMalloc((void**)&m.blockVRange, vr.size() * sizeof(int2)));
+        CK(c, cudaMemcpy(m.blockVRange, vr.data(), vr.size() * sizeof(int2), cudaMemcpyHostToDevice));
     }
     m.alive = true;
     std::lock_guard<std::mutex> lk(c->mu);
@@ -802,6 +816,7 @@ int srb_mesh_destroy(SrbContext* c, SrbMesh mesh) {
     cudaFree(c->meshes[mesh - 1].vtx);
     cudaFree(c->meshes[mesh - 1].idx);
     cudaFree(c->meshes[mesh - 1].blockSpheres);
+    cudaFree(c->meshes[mesh - 1].blockVRange);
     c->meshes[mesh - 1] = MeshRes();
     c->haveFrame = false;
     return SRB_OK;
@@ -926,6 +941,7 @@ int srb_end_frame(SrbContext* c) {
         d.cull = q.cull; d.depth_test = q.depth_test; d.blend = q.blend;
         d.flags = q.flags; d.visible = 1; d._pad = 0;
         d.tblockSpheres = m.blockSpheres;
+        d.tblockVRange = m.blockVRange;
         for (int k = 0; k < 4; ++k) d.planes[k] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
         totalV += m.nV; totalT += m.nI / 3;
         // Visibility path eligibility: extreme-depth winner with

@@ -153,10 +153,7 @@ setup_kernel(const DrawRec* __restrict__ draws, const int2* __restrict__ tblocks
   for (uint32_t bi = blockIdx.x; bi < nLive; bi += gridDim.x, blk = tblocks[min(bi, nLive - 1)]) {
     const int di = blk.x;
     const DrawRec& d = draws[di];
-#ifndef SRB_EXP_NO_BLOCKCULL
-    if ((fp.bandRow0 > 0 || fp.bandRow1 < fp.tilesY) && block_outside(d, blk.y / kGeomBlock))
-        continue;                                             // uniform over the CTA: the whole block is off band / off screen
-#endif
+    // (A band context's table holds only blocks that may touch the band: band_blocks_kernel.)
     agg_clear(agg);
     if (threadIdx.x == 0) sNoCover = 0u;
     __syncthreads();

@@ -209,18 +209,74 @@ __global__ void frustum_draws_kernel(DrawRec* draws, int nDraws, int fma, Counte
     // (Measured on one GPU, full frame: block culling gains nothing -- few blocks of a draw that passed the sphere
     // test are off screen -- and the planes cost the frustum kernel 2.8 us; it is a band (multi-GPU) feature.)
     const int nvb = (d.n_vertices + 127) / 128, ntb = (d.n_triangles + 127) / 128;
+    const bool banded = bandRow0 > 0 || bandRow1 < tilesY;
     uint32_t vo = 0, to = 0;
     __syncwarp();                                              // every lane has read d before lane 0 writes to it
     if (lane == 0) {
         d.visible = vis;
-        if (vis && (bandRow0 > 0 || bandRow1 < tilesY)) draw_planes(d, W, H, bandRow0, bandRow1, tilesY);
-        if (vis) { vo = atomicAdd(&cnt->nVLive, (uint32_t)nvb); to = atomicAdd(&cnt->nTLive, (uint32_t)ntb); }
+        if (vis && banded) draw_planes(d, W, H, bandRow0, bandRow1, tilesY);
+        if (vis && !banded) { vo = atomicAdd(&cnt->nVLive, (uint32_t)nvb); to = atomicAdd(&cnt->nTLive, (uint32_t)ntb); }
     }
-    if (!vis) return;
+    if (!vis || banded) return;                                // a band context's tables are built by band_blocks_kernel
     vo = __shfl_sync(0xffffffffu, vo, 0);
     to = __shfl_sync(0xffffffffu, to, 0);
     for (int k = lane; k < nvb; k += 32) vLive[vo + k] = make_int2(i, k * 128);
     for (int k = lane; k < ntb; k += 32) tLive[to + k] = make_int2(i, k * 128);
+}
+
+// Band contexts (multi-GPU): the live tables hold only what the band needs.  One CTA per visible draw tests every run
+// of kGeomBlock triangles against the band's half-spaces (block_outside) and appends the survivors to the triangle
+// table; every survivor marks the runs of kGeomBlock VERTICES its triangles index (lowest..highest index of the run,
+// recorded at mesh upload), and only marked vertex runs enter the vertex table.  Before, the vertex stage of a band
+// rank transformed every vertex of every visible draw (stress8k: 84 us on each of 8 ranks) and three quarters of the
+// setup kernel's CTAs loaded a table entry, a draw record and a sphere only to find their block off band.
+constexpr int kMaxVBlocks = 65536 / 128;                       // srb_mesh_create: at most 65536 vertices (ushort indices)
+__global__ void __launch_bounds__(128)
+band_blocks_kernel(const DrawRec* __restrict__ draws, Counters* cnt, int2* __restrict__ vLive, int2* __restrict__ tLive) {
+    __shared__ uint32_t marks[kMaxVBlocks / 32];
+    const int di = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const DrawRec& d = draws[di];
+    if (!d.visible) return;                                    // uniform over the CTA
+    if (tid < kMaxVBlocks / 32) marks[tid] = 0u;
+    __syncthreads();
+    const int ntb = (d.n_triangles + 127) / 128, nvb = (d.n_vertices + 127) / 128;
+    for (int base = 0; base < ntb; base += 128) {
+        const int k = base + tid;
+        const bool keep = k < ntb && !block_outside(d, k);
+        if (keep) {
+            const int2 vr = __ldg(d.tblockVRange + k);
+            for (int vb = vr.x >> 7; vb <= (vr.y >> 7); ++vb) atomicOr(&marks[vb >> 5], 1u << (vb & 31));
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m) {                                               // uniform over the warp
+            uint32_t wbase = 0;
+            if (lane == 0) wbase = atomicAdd(&cnt->nTLive, (uint32_t)__popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (keep) tLive[wbase + __popc(m & ((1u << lane) - 1u))] = make_int2(di, k * 128);
+        }
+    }
+    __syncthreads();
+    if (tid < 32) {                                            // the first warp writes the marked vertex runs
+        uint32_t w = tid < kMaxVBlocks / 32 ? marks[tid] : 0u;
+        if (tid * 32 >= nvb) w = 0u;
+        else if (tid * 32 + 32 > nvb) w &= (1u << (nvb - tid * 32)) - 1u;
+        uint32_t incl = (uint32_t)__popc(w);
+        const uint32_t mine = incl;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+        uint32_t vbase = 0;
+        if (lane == 31 && tot) vbase = atomicAdd(&cnt->nVLive, tot);
+        vbase = __shfl_sync(0xffffffffu, vbase, 31) + incl - mine;
+        while (w) {
+            const int b = __ffs(w) - 1;
+            w &= w - 1u;
+            vLive[vbase++] = make_int2(di, (tid * 32 + b) * 128);
+        }
+    }
 }
 
 __global__ void frustum_batch_kernel(const float* spheres, const float* models, const float* viewproj,

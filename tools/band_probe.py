@@ -19,7 +19,7 @@ r0, r1 = int(sys.argv[1]), int(sys.argv[2])
 wl = sys.argv[3] if len(sys.argv) > 3 else "city4k"
 scene = bench.build_scene(wl)
 L = N.lib()
-for split, depth in (((0, 0, 128), 2), ((0, 0, 128), 3), ((0, 0, 128), 4), ((128, 128, 64), 2), ((128, 128, 64), 3), ((128, 128, 64), 4)):
+for split, depth in (((128, 128, 64), 0),):
     win = srb.MainWindow(scene.width, scene.height)
     ctx = win._ctx
     win.SetBinSplit(*split)
