@@ -240,6 +240,9 @@ int launch_frame(SrbContext* c) {
     const uint32_t prevV = c->fb[c->slot].hCnt->nVLive, prevT = c->fb[c->slot].hCnt->nTLive;
     // Never fewer than two full waves' worth of CTAs (when the scene has that many blocks): a frame with far more live
     // blocks than the one before it (alternating passes, a camera cut) then still runs at full occupancy.
+    // (Measured, no effect, round 2: grids of the vertex / setup / count / fill kernels sized tightly from the last
+    // frame's counters instead of these floors and whole waves -- band contexts +-1 %, full frame unchanged:
+    // profiles/r02v_band_probe_lean_grids_experiment.txt.  CTAs that find nothing to do retire too quickly to matter.)
     const int floorCtas = c->smCount * 16;
     const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, std::max<int>(floorCtas, (int)(prevV + prevV / 8 + 16))) : c->nVBlocks);
     const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, std::max<int>(floorCtas, (int)(prevT + prevT / 8 + 16))) : c->nTBlocks);
