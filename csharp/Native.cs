@@ -64,6 +64,7 @@ namespace SoftwareRenderer
         [DllImport(Lib)] public static extern int srb_frame_barrier(IntPtr ctx, int slack);
         [DllImport(Lib)] public static extern int srb_set_bin_split(IntPtr ctx, int minEntriesFullFrame, int minEntriesBand, int partEntries);
         [DllImport(Lib)] public static extern int srb_set_pipeline_depth(IntPtr ctx, int bufferSets);
+        [DllImport(Lib)] public static extern int srb_set_graphs(IntPtr ctx, int enabled);
         [DllImport(Lib)] public static extern int srb_set_pipeline(IntPtr ctx, int pipeline);
         [DllImport(Lib)] public static extern int srb_export_color_handle(IntPtr ctx, byte* handleOut64);
         [DllImport(Lib)] public static extern int srb_set_color_target(IntPtr ctx, byte* handle64);

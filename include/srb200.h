@@ -132,6 +132,10 @@ int srb_set_bin_split(SrbContext* ctx, int min_entries_full_frame, int min_entri
  * frames whose tile kernel is shorter than their chain of geometry launches: small frames, and the band contexts
  * of a multi-GPU frame. */
 int srb_set_pipeline_depth(SrbContext* ctx, int buffer_sets);
+/* Tuning: replay a frame's chain of geometry launches as an instantiated CUDA graph when the frame repeats the
+ * shape (parameters, uniforms, grids, buffers) of the one before it on the same buffer set.  On by default; a
+ * context whose capture fails falls back to plain launches by itself. */
+int srb_set_graphs(SrbContext* ctx, int enabled);
 /* Multi-GPU band gather fused into the tile kernel (no reference counterpart):
  * rank 0 exports its colour buffer (CUDA IPC handle, 64 bytes); a band rank passes that handle as
  * its colour target and from then on stores its band's final colour straight into rank 0's

@@ -82,7 +82,7 @@ assert DRAW_CMD_DTYPE.itemsize == 248, DRAW_CMD_DTYPE.itemsize
 # Every symbol include/srb200.h declares (checked by tests/test_abi.py).
 EXPORTS = [
     "srb_create", "srb_destroy", "srb_resize", "srb_get_size", "srb_last_error", "srb_set_band",
-    "srb_set_pipeline", "srb_set_bin_split", "srb_set_pipeline_depth", "srb_export_color_handle", "srb_set_color_target", "srb_gather_rgba8_export", "srb_gather_rgba8_target",
+    "srb_set_pipeline", "srb_set_bin_split", "srb_set_pipeline_depth", "srb_set_graphs", "srb_export_color_handle", "srb_set_color_target", "srb_gather_rgba8_export", "srb_gather_rgba8_target",
     "srb_read_gathered_rgba8", "srb_device_gathered_rgba8_ptr", "srb_present_gathered_rgba8_async", "srb_get_tile_row_pairs",
     "srb_texture_create", "srb_texture_destroy", "srb_texture_sample",
     "srb_mesh_create", "srb_mesh_destroy", "srb_set_uniforms", "srb_begin_frame", "srb_draw",
@@ -134,6 +134,7 @@ def lib() -> C.CDLL:
     L.srb_set_pipeline.argtypes = [vp, i32]
     L.srb_set_bin_split.argtypes = [vp, i32, i32, i32]
     L.srb_set_pipeline_depth.argtypes = [vp, i32]
+    L.srb_set_graphs.argtypes = [vp, i32]
     L.srb_export_color_handle.argtypes = [vp, vp]
     L.srb_set_color_target.argtypes = [vp, vp]
     L.srb_get_tile_row_pairs.argtypes = [vp, vp, i32]

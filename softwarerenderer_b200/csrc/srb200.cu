@@ -110,11 +110,18 @@ struct SrbContext {
     // also overlap each other, which is what a band context with a short tile kernel needs (srb_set_pipeline_depth).
     static constexpr int kMaxSets = 4;
     static constexpr int nSets = kMaxSets;    // every set is allocated; `depth` says how many take turns
+    bool useGraphs = true;                    // srb_set_graphs
     int pipeDepth = 0;                        // 0 = chosen per frame (launch_frame), else 2..4
     struct FrameBufs {
         cudaStream_t geomStream = nullptr;
         cudaEvent_t geomDone = nullptr, rasterDone = nullptr, geomStarted = nullptr;
-        bool rasterRecorded = false;
+        bool rasterRecorded = false, startedValid = false;
+        // The set's geometry chain (one memset + 6..8 kernels) as an instantiated CUDA graph: a frame that repeats the
+        // shape of the set's previous frame (same parameters, grids and buffers -- graphKey) costs the host one launch
+        // instead of nine.  Captured the second time a shape is seen, dropped when it changes.
+        cudaGraphExec_t graphExec = nullptr;
+        std::vector<unsigned char> graphKey, lastKey;
+        int graphLaunches = 0;
         DevBuf<int2> dVBlocks, dTBlocks;  // block tables of the vertex / setup kernels: (draw, first element) of every run of
                                           // kGeomBlock vertices / triangles of a VISIBLE draw, compacted per frame by the frustum kernel
         DevBuf<float4> dClip;             // clip positions (vertex stage -> setup)
@@ -244,8 +251,10 @@ int launch_frame(SrbContext* c) {
     // frame's counters instead of these floors and whole waves -- band contexts +-1 %, full frame unchanged:
     // profiles/r02v_band_probe_lean_grids_experiment.txt.  CTAs that find nothing to do retire too quickly to matter.)
     const int floorCtas = c->smCount * 16;
-    const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, std::max<int>(floorCtas, (int)(prevV + prevV / 8 + 16))) : c->nVBlocks);
-    const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, std::max<int>(floorCtas, (int)(prevT + prevT / 8 + 16))) : c->nTBlocks);
+    // (Rounded up to a multiple of 256: a frame that repeats keeps its grids, and with them its graph.)
+    auto quant = [](uint32_t n) { return (int)((n + n / 8 + 16 + 255u) & ~255u); };
+    const unsigned gridV = (unsigned)std::max(1, prevV ? std::min<int>(c->nVBlocks, std::max<int>(floorCtas, quant(prevV))) : c->nVBlocks);
+    const unsigned gridT = (unsigned)std::max(1, prevT ? std::min<int>(c->nTBlocks, std::max<int>(floorCtas, quant(prevT))) : c->nTBlocks);
     // Frames in flight.  A frame whose tile kernel outlasts its geometry chain gains nothing from more than two sets
     // (measured, city4k: 5,950 frames/s with 2, 5,800 with 4 -- more geometry kernels beside the tile kernel only
     // take SMs from it); a frame with a short tile kernel is bound by the LATENCY of its chain of geometry launches,
@@ -270,7 +279,7 @@ int launch_frame(SrbContext* c) {
     if (B.rasterRecorded) CK(c, cudaStreamWaitEvent(gs, B.rasterDone, 0));   // this set's previous frame
     // Geometry chains start in frame order (a later frame's short kernels must not take the SMs from an earlier
     // frame's): behind the previous frame's frustum kernel, not behind its whole chain.
-    if (c->lastGeomStream && c->lastGeomStream != gs && c->fb[sPrev].geomStarted)
+    if (c->lastGeomStream && c->lastGeomStream != gs && c->fb[sPrev].startedValid)
         CK(c, cudaStreamWaitEvent(gs, c->fb[sPrev].geomStarted, 0));
     c->lastGeomStream = gs;
     CK(c, cudaEventRecord(c->ev0, gs));
@@ -282,69 +291,124 @@ int launch_frame(SrbContext* c) {
         c->stagingBusy[c->tableSlot] = true;
     }
     B.tableSerial = c->frameSerial;
-    CK(c, cudaMemsetAsync(B.dCntTiles.p, 0, (64 + (size_t)nTiles) * sizeof(uint32_t), gs));
-    if (c->profiling) cudaEventRecord(c->stageEv[0], gs);
-    if (fp.nDraws > 0) {
-        frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(B.dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
-                                                                                fp.bandRow1, fp.tilesY, B.dVBlocks.p, B.dTBlocks.p);
-        ++launches;
-        if (!fullFrame) {                                  // band context: block tables culled to the band
-            band_blocks_kernel<<<fp.nDraws, 128, 0, gs>>>(B.dDraws.p, B.dCnt, B.dVBlocks.p, B.dTBlocks.p);
-            ++launches;
+    const uint32_t splitMin = c->useVis ? (fullFrame ? c->splitMinFull : c->splitMinBand) : 0u;
+    const unsigned fillGrid = (unsigned)std::min<size_t>((2 * (size_t)fp.totalT + 255) / 256, (size_t)c->smCount * 8);
+    const unsigned wave = (unsigned)c->smCount * c->fillCtas;
+    // Fill: one launch or two.  The merged kernel saves a launch, which is what a small, launch-latency-bound frame
+    // wants (gun1080: 18,670 frames/s merged, 17,440 as two launches).  Its CTAs are twice as heavy, though (64+
+    // registers x 256 threads), and beside the previous frame's tile kernel a large frame does better with the two
+    // lean launches although they take 4 us longer alone (city4k: 5,690 against 5,590 frames/s).
+    // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
+    // bins up to order, which no consumer depends on).
+    const bool mergedFill = prevBig > 0 && prevRefs <= (fullFrame ? 16384u : wave * 256u);
+    const unsigned bigCountGrid = (unsigned)(c->smCount * (fullFrame ? c->bigCountCtas : 4));
+    const bool direct = c->profiling || !c->useGraphs;       // launch by launch: stage events, or graphs switched off
+
+    // Everything of the chain that goes onto the geometry stream, in order.  `live`: issued directly (events may be
+    // recorded between the launches); otherwise it is being captured into a graph.
+    auto issue_chain = [&](bool live) {
+        int n = 0;
+        cudaMemsetAsync(B.dCntTiles.p, 0, (64 + (size_t)nTiles) * sizeof(uint32_t), gs);
+        if (live && c->profiling) cudaEventRecord(c->stageEv[0], gs);
+        if (fp.nDraws > 0) {
+            frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(B.dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
+                                                                      fp.bandRow1, fp.tilesY, B.dVBlocks.p, B.dTBlocks.p);
+            ++n;
+            if (!fullFrame) {                              // band context: block tables culled to the band
+                band_blocks_kernel<<<fp.nDraws, 128, 0, gs>>>(B.dDraws.p, B.dCnt, B.dVBlocks.p, B.dTBlocks.p);
+                ++n;
+            }
         }
-    }
-    CK(c, cudaEventRecord(B.geomStarted, gs));
-    mark(1);
-    if (c->nVBlocks > 0) {
-        if (U.numerics_fma)
-            vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, B.dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
-        else
-            vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, B.dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
-        ++launches;
-    }
-    mark(2);
-    if (c->nTBlocks > 0) {
-        setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
-            B.dDraws.p, B.dTBlocks.p, fp, U, B.dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, B.dRefs.p, B.dBigQ.p,
-            B.dTileCount, B.dCnt);
-        bin_big_kernel<0><<<c->smCount * (fullFrame ? c->bigCountCtas : 4), 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCount, nullptr);
-        launches += 2;
-    }
-    mark(3);
-    if (bandTiles > 0) {
-        const uint32_t splitMin = c->useVis ? (fullFrame ? c->splitMinFull : c->splitMinBand) : 0u;
-        if (splitMin)
-            scan_tiles_kernel<true><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
-                                                               bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt);
-        else
-            scan_tiles_kernel<false><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
-                                                                bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt);
-        ++launches;
-    } else {
-        publish_counters_kernel<<<1, sizeof(Counters) / 4, 0, gs>>>(B.dCnt, (uint32_t*)B.hCnt);
-    }
-    CK(c, cudaEventRecord(B.cntReady, gs));
-    mark(4);
-    if (fp.totalT > 0 && bandTiles > 0) {
-        // grid-stride over the accepted-triangle list (its length is only known on the device)
-        size_t maxRefs = 2 * (size_t)fp.totalT;
-        unsigned grid = (unsigned)std::min<size_t>((maxRefs + 255) / 256, (size_t)c->smCount * 8);
-        const unsigned wave = (unsigned)c->smCount * c->fillCtas;
-        // One launch or two.  The merged kernel saves a launch, which is what a small, launch-latency-bound frame
-        // wants (gun1080: 18,670 frames/s merged, 17,440 as two launches).  Its CTAs are twice as heavy, though (64+
-        // registers x 256 threads), and beside the previous frame's tile kernel a large frame does better with the two
-        // lean launches although they take 4 us longer alone (city4k: 5,690 against 5,590 frames/s).
-        // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
-        // bins up to order, which no consumer depends on).
-        if (prevBig > 0 && prevRefs <= (fullFrame ? 16384u : wave * 256u)) {
-            fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(B.dRefs.p, B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p,
-                                                               B.dBins.p, wave);
+        if (live) { cudaEventRecord(B.geomStarted, gs); mark(1); }
+        if (c->nVBlocks > 0) {
+            if (U.numerics_fma)
+                vertex_kernel<true><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, B.dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
+            else
+                vertex_kernel<false><<<gridV, kGeomBlock, 0, gs>>>(B.dDraws.p, B.dVBlocks.p, B.dCnt, B.dClip.p, B.dWn.p);
+            ++n;
+        }
+        if (live) mark(2);
+        if (c->nTBlocks > 0) {
+            setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
+                B.dDraws.p, B.dTBlocks.p, fp, U, B.dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, B.dRefs.p, B.dBigQ.p,
+                B.dTileCount, B.dCnt);
+            bin_big_kernel<0><<<bigCountGrid, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCount, nullptr);
+            n += 2;
+        }
+        if (live) mark(3);
+        if (bandTiles > 0) {
+            if (splitMin)
+                scan_tiles_kernel<true><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
+                                                                   bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt);
+            else
+                scan_tiles_kernel<false><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
+                                                                    bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt);
+            ++n;
         } else {
-            fill_bins_kernel<<<grid, 256, 0, gs>>>(B.dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
-            bin_big_kernel<1><<<wave, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
-            ++launches;
+            publish_counters_kernel<<<1, sizeof(Counters) / 4, 0, gs>>>(B.dCnt, (uint32_t*)B.hCnt);
         }
-        ++launches;
+        if (live) { cudaEventRecord(B.cntReady, gs); mark(4); }    // the counters are final here
+        if (fp.totalT > 0 && bandTiles > 0) {
+            if (mergedFill) {
+                fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(B.dRefs.p, B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p, wave);
+            } else {
+                // grid-stride over the accepted-triangle list (its length is only known on the device)
+                fill_bins_kernel<<<fillGrid, 256, 0, gs>>>(B.dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
+                bin_big_kernel<1><<<wave, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
+                ++n;
+            }
+            ++n;
+        }
+        return n;
+    };
+
+    if (direct) {
+        launches += issue_chain(true);
+        B.startedValid = true;
+        B.lastKey.clear();
+    } else {
+        // the shape of this frame's chain on this set
+        std::vector<unsigned char> key;
+        auto put = [&key](const void* p, size_t n) { key.insert(key.end(), (const unsigned char*)p, (const unsigned char*)p + n); };
+        const void* ptrs[] = {B.dDraws.p, B.dVBlocks.p, B.dTBlocks.p, B.dClip.p, B.dWn.p, B.dRecsR.p, B.dRecsS.p, B.dClipAttrs.p,
+                              B.dRefs.p, B.dBigQ.p, B.dCntTiles.p, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, B.dBins.p, B.hCnt};
+        const uint32_t ints[] = {gridV, gridT, (uint32_t)c->nVBlocks, (uint32_t)c->nTBlocks, (uint32_t)mergedFill, splitMin, c->splitPart,
+                                 bigCountGrid, fillGrid, wave, (uint32_t)nTiles, (uint32_t)bandTiles};
+        put(&fp, sizeof(fp)); put(&U, sizeof(U)); put(ptrs, sizeof(ptrs)); put(ints, sizeof(ints));
+        bool done = false;
+        if (B.graphExec && key == B.graphKey) {
+            CK(c, cudaGraphLaunch(B.graphExec, gs));
+            launches += B.graphLaunches;
+            done = true;
+        } else {
+            if (B.graphExec) { cudaGraphExecDestroy(B.graphExec); B.graphExec = nullptr; B.graphKey.clear(); }
+            if (key == B.lastKey && cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                const int n = issue_chain(false);
+                cudaGraph_t g = nullptr;
+                cudaError_t e = cudaStreamEndCapture(gs, &g);
+                if (e == cudaSuccess) e = cudaGraphInstantiate(&B.graphExec, g, 0);
+                if (g) cudaGraphDestroy(g);
+                if (e == cudaSuccess) e = cudaGraphLaunch(B.graphExec, gs);
+                if (e == cudaSuccess) {
+                    B.graphKey = key;
+                    B.graphLaunches = n;
+                    launches += n;
+                    done = true;
+                } else {                                   // never fatal: this context goes back to plain launches
+                    cudaGetLastError();
+                    if (B.graphExec) { cudaGraphExecDestroy(B.graphExec); B.graphExec = nullptr; }
+                    c->useGraphs = false;
+                }
+            }
+        }
+        B.lastKey = key;
+        if (done) {
+            CK(c, cudaEventRecord(B.cntReady, gs));        // graph path: known when the whole chain is done
+            B.startedValid = false;                        // (no mid-chain event to order the next frame's chain behind)
+        } else {
+            launches += issue_chain(true);
+            B.startedValid = true;
+        }
     }
     mark(5);
     CK(c, cudaEventRecord(B.geomDone, gs));
@@ -532,6 +596,7 @@ int srb_destroy(SrbContext* c) {
         if (b.geomStream) { cudaStreamSynchronize(b.geomStream); cudaStreamDestroy(b.geomStream); }
         if (b.geomDone) cudaEventDestroy(b.geomDone);
         if (b.geomStarted) cudaEventDestroy(b.geomStarted);
+        if (b.graphExec) cudaGraphExecDestroy(b.graphExec);
         if (b.rasterDone) cudaEventDestroy(b.rasterDone);
         if (b.cntReady) cudaEventDestroy(b.cntReady);
         if (b.hCnt) cudaFreeHost(b.hCnt);
@@ -676,6 +741,12 @@ int srb_set_bin_split(SrbContext* c, int min_entries_full_frame, int min_entries
     c->splitMinFull = (uint32_t)min_entries_full_frame;
     c->splitMinBand = (uint32_t)min_entries_band;
     c->splitPart = (uint32_t)part_entries;
+    return SRB_OK;
+}
+
+int srb_set_graphs(SrbContext* c, int enabled) {
+    if (!c) return SRB_ERR_ARG;
+    c->useGraphs = enabled != 0;
     return SRB_OK;
 }
 

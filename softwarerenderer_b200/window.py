@@ -174,6 +174,10 @@ class MainWindow:
         """Tuning only: frames in flight on the device (2..4, 0 = chosen per frame)."""
         N.check(self._ctx, N.lib().srb_set_pipeline_depth(self._ctx, buffer_sets))
 
+    def SetGraphs(self, enabled: bool) -> None:
+        """Tuning only: CUDA-graph replay of the geometry chain of repeating frames (on by default)."""
+        N.check(self._ctx, N.lib().srb_set_graphs(self._ctx, 1 if enabled else 0))
+
     def SetPipeline(self, pipeline: int) -> None:
         N.check(self._ctx, N.lib().srb_set_pipeline(self._ctx, pipeline))
 

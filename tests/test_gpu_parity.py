@@ -331,3 +331,38 @@ def test_pipeline_depth_leaves_the_image_alone(oracle, depth):
         assert np.array_equal(win.DepthBuffer[160:480], oa[1][160:480])
     finally:
         win.Close()
+
+
+def test_graph_replay_of_the_geometry_chain(oracle):
+    """Frames that repeat the shape of the frame before them on the same buffer set replay their chain of geometry
+    launches as a CUDA graph (srb_set_graphs, on by default): replays, re-submissions of the same scene, a change of
+    uniforms, of the scene and of the band in between, graphs off -- always the oracle's image."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import submit_scene
+    a = S.scene_city(1280, 720, n_instances=12)
+    b = S.scene_model("Gun", 1280, 720, view=S.gun_camera(2))
+    a2 = S.scene_city(1280, 720, n_instances=12)
+    a2.fog_end = 90.0                                         # same draws, other uniforms
+    want = {id(s): oracle.render_scene(s, threads=8) for s in (a, b, a2)}
+    win = srb.MainWindow(1280, 720)
+    try:
+        for graphs in (True, False, True):
+            win.SetGraphs(graphs)
+            for sc in (a, a, a, b, b, a2, a2, a2, a):
+                submit_scene(win, sc)                         # per set: first sight, capture, replay
+                for _ in range(9):
+                    win.ReplayFrame()
+                compare(win.ColorBuffer, win.DepthBuffer, want[id(sc)][0], want[id(sc)][1])
+        launches = win.Stats().kernel_launches
+        win.SetGraphs(False)
+        win.ReplayFrame()
+        assert win.Stats().kernel_launches == launches        # the statistic counts kernels, replayed or launched
+        win.SetGraphs(True)
+        win.SetBand(10, 30)
+        submit_scene(win, a)
+        for _ in range(12):
+            win.ReplayFrame()
+        assert np.array_equal(win.DepthBuffer[160:480], want[id(a)][1][160:480])
+    finally:
+        win.Close()

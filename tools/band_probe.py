@@ -19,11 +19,12 @@ r0, r1 = int(sys.argv[1]), int(sys.argv[2])
 wl = sys.argv[3] if len(sys.argv) > 3 else "city4k"
 scene = bench.build_scene(wl)
 L = N.lib()
-for split, depth in (((128, 128, 64), 0),):
+for split, depth, graphs in (((128, 128, 64), 0, 0), ((128, 128, 64), 0, 1)):
     win = srb.MainWindow(scene.width, scene.height)
     ctx = win._ctx
     win.SetBinSplit(*split)
     win.SetPipelineDepth(depth)
+    win.SetGraphs(bool(graphs))
     if r1 > r0:
         win.SetBand(r0, r1)
     S.submit_scene(win, scene)
@@ -52,6 +53,6 @@ for split, depth in (((128, 128, 64), 0),):
         if i >= 3:
             acc += np.array(list(buf))
     N.check(ctx, L.srb_set_profiling(ctx, 0))
-    print(f"band {r0}-{r1} split {split} depth {depth}: {fps:8.0f} frames/s  parts {st.split_parts:5d}  pairs {st.tile_pairs}  host {host_us:.1f} us/frame  "
+    print(f"band {r0}-{r1} split {split} depth {depth} graphs {graphs}: {fps:8.0f} frames/s  parts {st.split_parts:5d}  pairs {st.tile_pairs}  host {host_us:.1f} us/frame  "
           + " ".join(f"{n}={a / 30 * 1000:.1f}" for n, a in zip(bench.STAGES, acc)), flush=True)
     win.Close()
