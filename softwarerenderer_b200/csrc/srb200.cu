@@ -127,7 +127,7 @@ struct SrbContext {
         DevBuf<float4> dClip;             // clip positions (vertex stage -> setup)
         DevBuf<TriRef> dRefs;             // accepted triangles (setup -> fill)
         DevBuf<BigEntry> dBigQ;           // triangles that span more than kSmallTiles tiles
-        DevBuf<uint32_t> dCntTiles;       // [64 words: Counters][per-tile counts]: one memset per frame clears both
+        DevBuf<uint32_t> dCntTiles;       // [64 words: Counters][per-tile counts][per-tile large-triangle flags]: one memset per frame
         DevBuf<DrawRec> dDraws;           // this set's copy of the draw table (the frustum kernel writes into it)
         uint64_t tableSerial = 0;         // which frame's table it holds
         DevBuf<float4> dWn;               // world normals (vertex stage -> shading)
@@ -137,6 +137,7 @@ struct SrbContext {
         DevBuf<uint4> dOrder;             // tile launch order of the visibility kernel
         Counters* dCnt = nullptr;         // = dCntTiles.p
         uint32_t* dTileCount = nullptr;   // = dCntTiles.p + 64
+        uint32_t* dTileHasBig = nullptr;  // = dTileCount + tiles
         Counters* hCnt = nullptr;         // pinned; written by the scan kernel itself (every counter is final by then)
         cudaEvent_t cntReady = nullptr;   // ... and this event follows the copy: the host learns about a capacity
                                           // overflow when the frame's GEOMETRY is done, not its rasterization
@@ -300,7 +301,9 @@ int launch_frame(SrbContext* c) {
     // lean launches although they take 4 us longer alone (city4k: 5,690 against 5,590 frames/s).
     // Decided from the last completed frame's counters (a heuristic only -- both orders of filling give the same
     // bins up to order, which no consumer depends on).
-    const bool mergedFill = prevBig > 0 && prevRefs <= (fullFrame ? 16384u : wave * 256u);
+    // Larger frames always fill in two launches, the triangles that span many tiles FIRST: they are then at the head of
+    // every bin, where the tile kernel's hi-Z wants its occluders.
+    const bool mergedFill = prevBig > 0 && prevRefs <= 16384u;
     const unsigned bigCountGrid = (unsigned)(c->smCount * (fullFrame ? c->bigCountCtas : 4));
     const bool direct = c->profiling || !c->useGraphs;       // launch by launch: stage events, or graphs switched off
 
@@ -308,7 +311,7 @@ int launch_frame(SrbContext* c) {
     // recorded between the launches); otherwise it is being captured into a graph.
     auto issue_chain = [&](bool live) {
         int n = 0;
-        cudaMemsetAsync(B.dCntTiles.p, 0, (64 + (size_t)nTiles) * sizeof(uint32_t), gs);
+        cudaMemsetAsync(B.dCntTiles.p, 0, (64 + 2 * (size_t)nTiles) * sizeof(uint32_t), gs);
         if (live && c->profiling) cudaEventRecord(c->stageEv[0], gs);
         if (fp.nDraws > 0) {
             frustum_draws_kernel<<<(fp.nDraws + 3) / 4, 128, 0, gs>>>(B.dDraws.p, fp.nDraws, U.numerics_fma, B.dCnt, fp.W, fp.H, fp.bandRow0,
@@ -332,17 +335,17 @@ int launch_frame(SrbContext* c) {
             setup_kernel<<<gridT, kGeomBlock, 0, gs>>>(
                 B.dDraws.p, B.dTBlocks.p, fp, U, B.dClip.p, B.dWn.p, RecStore{B.dRecsR.p, B.dRecsS.p, (uint32_t)fp.totalT}, B.dClipAttrs.p, B.dRefs.p, B.dBigQ.p,
                 B.dTileCount, B.dCnt);
-            bin_big_kernel<0><<<bigCountGrid, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCount, nullptr);
+            bin_big_kernel<0><<<bigCountGrid, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCount, B.dTileHasBig);
             n += 2;
         }
         if (live) mark(3);
         if (bandTiles > 0) {
             if (splitMin)
                 scan_tiles_kernel<true><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
-                                                                   bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt);
+                                                                   bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt, B.dTileHasBig);
             else
                 scan_tiles_kernel<false><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
-                                                                    bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt);
+                                                                    bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt, B.dTileHasBig);
             ++n;
         } else {
             publish_counters_kernel<<<1, sizeof(Counters) / 4, 0, gs>>>(B.dCnt, (uint32_t*)B.hCnt);
@@ -353,8 +356,8 @@ int launch_frame(SrbContext* c) {
                 fill_merged_kernel<<<2 * wave, 256, 0, gs>>>(B.dRefs.p, B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p, wave);
             } else {
                 // grid-stride over the accepted-triangle list (its length is only known on the device)
-                fill_bins_kernel<<<fillGrid, 256, 0, gs>>>(B.dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
                 bin_big_kernel<1><<<wave, 256, 0, gs>>>(B.dBigQ.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
+                fill_bins_kernel<<<fillGrid, 256, 0, gs>>>(B.dRefs.p, B.dCnt, fp, B.dTileCursor.p, B.dBins.p);
                 ++n;
             }
             ++n;
@@ -1057,9 +1060,10 @@ int srb_end_frame(SrbContext* c) {
         CK(c, b.dBins.reserve(std::max<size_t>(1u << 20, 3 * (size_t)totalT)));
         CK(c, b.dRefs.reserve(2 * (size_t)totalT + 64));
         CK(c, b.dBigQ.reserve(1u << 16));
-        CK(c, b.dCntTiles.reserve(64 + (size_t)nTiles));
+        CK(c, b.dCntTiles.reserve(64 + 2 * (size_t)nTiles));
         b.dCnt = reinterpret_cast<Counters*>(b.dCntTiles.p);
         b.dTileCount = b.dCntTiles.p + 64;
+        b.dTileHasBig = b.dTileCount + nTiles;
     }
     CK(c, c->dBinScratch.reserve(c->fb[0].dBins.cap));
     c->nVBlocks = (int)nVB; c->nTBlocks = (int)nTB;

@@ -111,8 +111,12 @@ __device__ __forceinline__ void bin_big_body(const BigEntry* __restrict__ q, con
 #pragma unroll
             for (int u = 0; u < 4; ++u)
                 if (tile[u] >= 0) {
-                    if (MODE == 0) atomicAdd(tileCounter + tile[u], 1u);
-                    else slot[u] = atomicAdd(tileCounter + tile[u], 1u);
+                    if (MODE == 0) {
+                        atomicAdd(tileCounter + tile[u], 1u);
+                        bins[tile[u]] = 1u;        // count pass: `bins` is the per-tile "holds a large triangle" flag array
+                    } else {
+                        slot[u] = atomicAdd(tileCounter + tile[u], 1u);
+                    }
                 }
             if (MODE == 1) {
 #pragma unroll
@@ -298,7 +302,7 @@ __global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
 scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
                   uint32_t* __restrict__ tileCursor, uint4* __restrict__ order, int tile0, int nTiles,
                   Counters* cnt, uint32_t pairCap, const uint32_t splitMin_, const uint32_t splitPart,
-                  uint32_t* __restrict__ hostCnt) {
+                  uint32_t* __restrict__ hostCnt, const uint32_t* __restrict__ tileHasBig) {
     const uint32_t splitMin = SPLIT ? splitMin_ : 0u;
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
@@ -350,11 +354,12 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
     for (int chunk = r0; chunk < r1; chunk += 1024 * kScanIters) {
         const int wb = chunk + wid * (32 * kScanIters);
         uint32_t c[kScanIters];
-        uint32_t sum = 0, sh = 0, smd = 0;
+        uint32_t sum = 0, sh = 0, smd = 0, bigBits = 0;
 #pragma unroll
         for (int k = 0; k < kScanIters; ++k) {
             const int i = wb + k * 32 + lane;
             c[k] = i < r1 ? __ldg(tileCount + i) : 0u;
+            bigBits |= (i < r1 && __ldg(tileHasBig + i) != 0u) ? (1u << k) : 0u;     // loaded with the counts, not later
             sum += c[k];
             sh += c[k] >= kHeavyBin;
             smd += (c[k] >= kMediumBin && c[k] < kHeavyBin);
@@ -412,10 +417,12 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
             else pos = th + tm + orest + __popc(mv & ~mh & ~mm & lt);
             // Split bins: the tile's own entry becomes part 0; the index of its first extra entry doubles as the id
             // of its key slice.
-            uint32_t w = 0u, firstEnd = excl + c[k];
+            // bit 31: a triangle that spans many tiles is in this bin (they are filled first: hi-Z has its occluders)
+            const uint32_t big = (bigBits >> k & 1u) ? 0x80000000u : 0u;
+            uint32_t w = big, firstEnd = excl + c[k];
             if (SPLIT && splitMin != 0u && c[k] >= splitMin && c[k] > partSize) {
                 const uint32_t extra = (c[k] + partSize - 1u) / partSize - 1u;
-                w = (extra + 1u) | (ebase << 16);          // parts (<= kMaxExtra + 1) | slice (< kMaxExtra)
+                w = (extra + 1u) | (ebase << 16) | big;    // parts (<= kMaxExtra + 1) | slice (< kMaxExtra) | large-triangle flag
                 firstEnd = excl + partSize;
                 SRB_ASSERT(ebase + extra <= kMaxExtra && extra + 1u <= 0xffffu);
                 for (uint32_t q = 1; q <= extra; ++q)

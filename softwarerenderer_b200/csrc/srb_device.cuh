@@ -378,6 +378,55 @@ __device__ __forceinline__ bool tile_may_cover(float s0x, float s0y, float s1x, 
 }
 
 // ---------------------------------------------------------------------------
+// Occlusion bound (hi-Z inside a tile, depth functions Less / LessEqual: the LARGEST stored depth wins).
+// Returns an upper bound of every depth value the reference can compute for this triangle at a COVERED pixel of the
+// rectangle [X0..X1] x [Y0..Y1] (the tile-clipped bbox), or +inf when no bound can be given.  A triangle whose bound
+// is below the smallest depth already stored in the tile cannot win a single pixel there and need not be walked.
+//
+// Proof sketch (notation of tile_may_cover above: W_i real affine edge functions on the float constants, B_i the
+// magnitude bound, E_i = 2^-16 B_i, every edge value the reference forms for a pixel of the rectangle within
+// 38 * 2^-24 B_i of W_i at that pixel).
+//  * At a covered pixel the three computed edge values w_i have one sign (Rasterizer.cs:493-494), so the
+//    normalised weights w_if = fl(w_i * invArea) have one sign too and sum |w_if| = |sum w_if|.
+//  * s = w_0 + w_1 + w_2 (computed values, real sum) differs from S(x,y) = W_0 + W_1 + W_2 by less than sumE / 6.
+//    S is affine, its extremes over the rectangle are at the corners; the corner values below carry a few more
+//    roundings (again a small multiple of 2^-24 B), so s lies in [smin - sumE, smax + sumE].
+//  * If that interval times invArea is entirely NEGATIVE, sum w_if < 0 at every covered pixel, hence every
+//    w_if <= 0, and |sum w_if| >= |invArea| * m * (1 - 2^-23) with m = min(|smin - sumE|, |smax + sumE|).
+//  * With all d_i >= 0: depth = fl(fl(d0 w0f + d1 w1f) + d2 w2f) is a sum of non-positive terms (no cancellation,
+//    relative rounding error < 4 * 2^-24), so depth <= -dmin * |invArea| * m * (1 - 2^-20).
+// Anything else -- a d_i that is negative or not finite, an interval that touches zero or has the other sign, NaN
+// anywhere -- gives no bound (every comparison below is written so that NaN falls to "no bound").
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float tri_depth_upper_bound(const TriRec& r, const TriEq& e, const float w0, const float w1,
+                                                       const float w2, const int X0, const int X1, const int Y0, const int Y1) {
+    const float inf = __int_as_float(0x7f800000);
+    const float dmin = fminf(fminf(r.d0, r.d1), r.d2), dmax = fmaxf(fmaxf(r.d0, r.d1), r.d2);
+    if (!(dmin >= 0.0f) || !(dmax < 1e30f) || !(r.d0 == r.d0 && r.d1 == r.d1 && r.d2 == r.d2)) return inf;
+    const float fx0 = (float)X0, fx1 = (float)X1, fy0 = (float)Y0, fy1 = (float)Y1;
+    // B_i = max |a_i (x - p_ix)| + max |b_i (y - p_iy)| over the rectangle; edge i pivots at s1, s2, s0 (row_base)
+    const float B0 = add(mul(fabsf(e.a12), fmaxf(fabsf(sub(fx0, r.s1x)), fabsf(sub(fx1, r.s1x)))),
+                         mul(fabsf(e.b12), fmaxf(fabsf(sub(fy0, r.s1y)), fabsf(sub(fy1, r.s1y)))));
+    const float B1 = add(mul(fabsf(e.a20), fmaxf(fabsf(sub(fx0, r.s2x)), fabsf(sub(fx1, r.s2x)))),
+                         mul(fabsf(e.b20), fmaxf(fabsf(sub(fy0, r.s2y)), fabsf(sub(fy1, r.s2y)))));
+    const float B2 = add(mul(fabsf(e.a01), fmaxf(fabsf(sub(fx0, r.s0x)), fabsf(sub(fx1, r.s0x)))),
+                         mul(fabsf(e.b01), fmaxf(fabsf(sub(fy0, r.s0y)), fabsf(sub(fy1, r.s0y)))));
+    const float sumE = mul(add(add(B0, B1), B2), 1.52587890625e-05f);          // 2^-16
+    if (!(sumE < 1e30f)) return inf;
+    // S at the four corners: w0 + w1 + w2 are the row-base values at (X0, Y0); S is affine with slopes sa, sb
+    const float s00 = add(add(w0, w1), w2);
+    const float sa = add(add(e.a12, e.a20), e.a01), sb = add(add(e.b12, e.b20), e.b01);
+    const float dx = mul(sa, sub(fx1, fx0)), dy = mul(sb, sub(fy1, fy0));
+    const float s10 = add(s00, dx), s01 = add(s00, dy), s11 = add(s10, dy);
+    const float smax = fmaxf(fmaxf(s00, s10), fmaxf(s01, s11)), smin = fminf(fminf(s00, s10), fminf(s01, s11));
+    const float lo = mul(sub(smin, sumE), e.invArea), hi = mul(add(smax, sumE), e.invArea);     // sum w_if lies between them
+    if (!(lo < 0.0f && hi < 0.0f)) return inf;
+    const float m = fminf(fabsf(lo), fabsf(hi));                               // |sum w_if| >= m (1 - 2^-23)
+    const float b = mul(mul(dmin, m), 0.99999904632568359375f);                // 1 - 2^-20
+    return b > 1e-30f ? -b : 0.0f;       // (below that, products may have gone denormal: only "depth <= 0" is claimed)
+}
+
+// ---------------------------------------------------------------------------
 // Conservative "covers no pixel at all" test for triangles whose clamped pixel bbox is at most
 // kSmallPx x kSmallPx: distant meshes produce many triangles that fall between pixel centres, and the
 // reference walks them without ever passing its test.  Same bound as tile_may_cover with the bbox as

@@ -201,7 +201,11 @@ ordered_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
 constexpr int kVisThreads = SRB_VIS_THREADS;
 constexpr int kVisWarps = kVisThreads / 32;
 constexpr int kVisFields = 15;
-constexpr int kKeyPitch = kTile + 1;     // 17 x 8 B = 34 banks: consecutive rows are two banks apart
+constexpr int kKeyPitch = kTile + 1;
+#ifndef SRB_HIZ_FIRST
+#define SRB_HIZ_FIRST 32
+#endif
+constexpr uint32_t kHiZFirst = SRB_HIZ_FIRST;          // entries of a long bin's first chunk (0 disables hi-Z chunking)     // 17 x 8 B = 34 banks: consecutive rows are two banks apart
 
 // Walk one row of one triangle inside a tile: replay the reference's x accumulation
 // (Rasterizer.cs:485-535) and raise the per-pixel winner keys.
@@ -284,6 +288,7 @@ struct VisSmem {
                                                 // unpadded 128-byte row pitch would put them all on the same two banks
     float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
     int warpRows[kVisWarps];
+    uint32_t warpMin[kVisWarps];           // hi-Z: per-warp minimum of the stored depth keys
     int last;                              // split bins: this CTA merged last and resolves the tile
     unsigned short items[kVisThreads * kTile];   // (triangle slot | row << 8) per work item of the chunk
 #ifdef SRB_TILE_TIMING
@@ -300,8 +305,9 @@ template <int MODE, bool OUT8>
 #define SRB_BE be
 #endif
 __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t bs, const uint32_t SRB_BE,
-                                                 const uint32_t parts, const uint32_t slice, const RasterArgs& A,
-                                                 const FrameParams& fp, const SrbUniforms& U, VisSmem& sm) {
+                                                 const uint32_t parts, const uint32_t slice, const bool hasBig,
+                                                 const RasterArgs& A, const FrameParams& fp, const SrbUniforms& U,
+                                                 VisSmem& sm) {
     unsigned long long* keys = sm.keys;
     float (*S)[kVisThreads] = sm.S;
     int* warpRows = sm.warpRows;
@@ -345,10 +351,22 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
     const unsigned long long ckey = clear_key<MODE>();
     for (int i = tid; i < kTile * kKeyPitch; i += kVisThreads) keys[i] = ckey;
 
-    for (uint32_t cb = bs; cb < be; cb += kVisThreads) {
+    // Hi-Z inside the tile (depth functions Less / LessEqual).  Between chunks the CTA takes the smallest depth stored
+    // in the tile so far; a triangle whose best possible depth over its rectangle (tri_depth_upper_bound, proven
+    // conservative against the reference's rounded arithmetic) is below it cannot win a pixel and is not walked.  The
+    // fill pass puts the triangles that span many tiles FIRST into every bin -- near walls and ground, the usual
+    // occluders -- and a long bin's first chunk is kept short so that the bound exists before the crowd behind them is
+    // looked at: on the horizon of the city frame half to four fifths of a heavy bin's triangles are hidden.
+    // Only bins that hold such a triangle take part (a flag from the binning passes): crowds of small triangles alone
+    // never close a tile early, and the extra chunk cost the 10 M-triangle frame 10 % when every long bin paid it.
+    constexpr bool kHiZmode = MODE < 2 && kHiZFirst > 0u;
+    const bool kHiZ = kHiZmode && hasBig;
+    uint32_t minHi = 0u;                                   // smallest stored depth key (high word) of the tile: 0 = unknown
+    uint32_t chunk = (kHiZ && be - bs > kHiZFirst + kHiZFirst / 2) ? kHiZFirst : (uint32_t)kVisThreads;
+    for (uint32_t cb = bs; cb < be; cb += chunk, chunk = kVisThreads) {
         // ---- one triangle per thread: derive its raster constants for this tile ----
         int nrows = 0;
-        if (cb + tid < be) {
+        if ((uint32_t)tid < chunk && cb + tid < be) {
             const uint32_t seq = __ldg(A.bins + cb + tid);
             const TriRec r = load_rec_raster(A.recs, seq);
             const TriEq e = tri_eq(r);
@@ -358,6 +376,9 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
                 nrows = endY - startY + 1;
                 float w0, w1, w2;
                 row_base(r, e, startX, startY, w0, w1, w2);
+                if (kHiZ && minHi != 0u &&
+                    f2ord(tri_depth_upper_bound(r, e, w0, w1, w2, startX, endX, startY, endY)) < minHi)
+                    nrows = 0;                             // hidden behind what the tile already holds
                 S[0][tid] = w0; S[1][tid] = w1; S[2][tid] = w2;
                 S[3][tid] = e.a12; S[4][tid] = e.a20; S[5][tid] = e.a01;
                 S[6][tid] = e.b12; S[7][tid] = e.b20; S[8][tid] = e.b01;
@@ -418,6 +439,20 @@ __device__ __forceinline__ void vis_process_tile(const int tile, const uint32_t 
         }
         // (Measured, no effect: loading the next chunk's bin entries early and prefetching their records.)
         __syncthreads();
+        if (kHiZ && cb + chunk < be) {                     // more chunks follow: the tile's smallest stored depth so far
+            uint32_t m = 0xffffffffu;
+            for (int p = tid; p < kTile * kTile; p += kVisThreads) {
+                const int px = p & 15, py = p >> 4;
+                if (tx0 + px < fp.W && ty0 + py < fp.H) m = min(m, (uint32_t)(keys[py * kKeyPitch + px] >> 32));
+            }
+            m = __reduce_min_sync(full, m);
+            if (lane == 0) sm.warpMin[wid] = m;
+            __syncthreads();
+            m = sm.warpMin[0];
+#pragma unroll
+            for (int w = 1; w < kVisWarps; ++w) m = min(m, sm.warpMin[w]);
+            minHi = m == (uint32_t)(ckey >> 32) ? 0u : m;  // an uncovered pixel holds the clear key: nothing is below it
+        }
     }
 
 #ifdef SRB_TILE_TIMING
@@ -490,7 +525,7 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
 #endif
-    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, o.w & 0xffffu, o.w >> 16, A, fp, U, sm);
+    vis_process_tile<MODE, OUT8>((int)o.x, o.y, o.z, o.w & 0xffffu, (o.w >> 16) & 0x7fffu, (o.w >> 31) != 0u, A, fp, U, sm);
 #ifdef SRB_TILE_TIMING
     __syncthreads();
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
