@@ -124,7 +124,7 @@ int srb_set_pipeline(SrbContext* ctx, int pipeline);
 /* Tuning (no reference counterpart; the image never depends on it): a tile whose bin holds at least min_entries
  * (triangle, tile) pairs is rasterized by several CTAs of part_entries (a multiple of 32) each, merged through 64-bit atomic max; one
  * threshold for contexts that render the whole frame, one for band contexts (multi-GPU).  0 = never split.
- * Defaults 0 / 128 / 64. */
+ * Defaults 0 / 256 / 128. */
 int srb_set_bin_split(SrbContext* ctx, int min_entries_full_frame, int min_entries_band, int part_entries);
 /* Tuning (the image never depends on it): how many frames may be in flight on the device, 2..4 buffer sets, or 0 =
  * chosen per frame (default).  With 2 the geometry stages of frame N+1 overlap the tile kernel of frame N; with

@@ -101,7 +101,7 @@ struct SrbContext {
     // Bins of >= splitMin entries are rasterized by several CTAs of splitPart entries each (srb_set_bin_split).
     // A full frame is bound by the sum of its tiles, not by the longest one, and splitting costs a merge, so it
     // starts late there; a band's floor IS its heaviest tile.
-    uint32_t splitMinFull = 0, splitMinBand = 128, splitPart = 64;
+    uint32_t splitMinFull = 0, splitMinBand = 256, splitPart = 128;   // (with hi-Z: profiles/r02z_band_probe_split_under_hiz.txt)
     // Frame pipelining: the geometry stages of the next frames run on their own streams while the tile kernel of
     // frame N is still running on `stream`.  Everything a frame's stages write exists once per SET; frames take the
     // sets in turn, each set has its own geometry stream, and a set is reused when the tile kernel of its previous
