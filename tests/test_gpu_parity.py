@@ -366,3 +366,43 @@ def test_graph_replay_of_the_geometry_chain(oracle):
         assert np.array_equal(win.DepthBuffer[160:480], want[id(a)][1][160:480])
     finally:
         win.Close()
+
+
+def test_mesh_cache_identity_content_and_invalidate(oracle):
+    """The mirror's mesh cache (window.mesh_handle): equal copies share one resident mesh, an array edited in place
+    keeps rendering the old upload until InvalidateMesh (documented), after which it matches the oracle again, and
+    the least recently used meshes are destroyed beyond MeshCacheCapacity without changing any result."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200 import scene as S
+    from softwarerenderer_b200.scene import submit_scene
+    sc = S.scene_stress(320, 192, n_meshes=3, grid=21)
+    win = srb.MainWindow(sc.width, sc.height)
+    try:
+        submit_scene(win, sc)
+        c0 = win.ColorBuffer.copy()
+        n0 = len(win._mesh_by_content)
+        # equal copies of every array: new identities, same content -> no new device mesh
+        for d in sc.draws:
+            d.mesh.Vertices = d.mesh.Vertices.copy()
+            d.mesh.Indices = d.mesh.Indices.copy()
+        submit_scene(win, sc)
+        assert len(win._mesh_by_content) == n0
+        assert np.array_equal(win.ColorBuffer, c0)
+        # edit in place: stale until invalidated
+        m = sc.draws[0].mesh
+        m.Vertices["Color"][:, :3] *= np.float32(0.25)       # darken the vertex colours of one mesh
+        submit_scene(win, sc)
+        assert np.array_equal(win.ColorBuffer, c0)
+        win.InvalidateMesh(m.Vertices, m.Indices)
+        submit_scene(win, sc)
+        oc, od, _ = oracle.render_scene(sc, threads=4)
+        compare(win.ColorBuffer, win.DepthBuffer, oc, od)
+        assert not np.array_equal(win.ColorBuffer, c0)
+        # eviction: capacity 1 keeps rendering correctly (every draw re-uploads what was evicted)
+        win.MeshCacheCapacity = 1
+        submit_scene(win, sc)
+        submit_scene(win, sc)
+        assert len(win._mesh_by_content) <= max(1, len({id(d.mesh) for d in sc.draws}))
+        compare(win.ColorBuffer, win.DepthBuffer, oc, od)
+    finally:
+        win.Close()
