@@ -244,10 +244,32 @@ __device__ __forceinline__ void vis_walk_row(float w0, float w1, float w2, const
     }
 }
 
+struct VisSmem {
+    unsigned long long keys[kTile * kKeyPitch]; // rows padded: lanes walk DIFFERENT rows at the same x, and an
+                                                // unpadded 128-byte row pitch would put them all on the same two banks
+    float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
+    int warpRows[kVisWarps];
+    uint32_t warpMin[kVisWarps];           // hi-Z: per-warp minimum of the stored depth keys
+    int last;                              // split bins: this CTA merged last and resolves the tile
+    unsigned short items[kVisThreads * kTile];   // (triangle slot | row << 8) per work item of the chunk
+#ifdef SRB_TILE_TIMING
+    unsigned long long phase[2];           // diagnostic: time after the first chunk's load+scan, time before resolve
+#endif
+};
+
 template <int MODE, bool OUT8>
 __device__ __forceinline__ void vis_resolve(const unsigned long long* keys, const unsigned long long ckey,
                                             const int tx0, const int ty0, const float4 clearCol, const RasterArgs& A,
                                             const FrameParams& fp, const SrbUniforms& U) {
+    // (Measured and rejected, round 2: "span resolve" -- the winner's edge values at a pixel are the end of a chain of
+    // up to 15 + 15 rounded adds, replayed below for every pixel; pixels of one row that share a winner share the chain,
+    // so one thread per SPAN (maximal run of equal winners in a row; found by ballot, compacted into shared memory)
+    // walked it once exactly as the coverage pass does and left (w0, w1, w2, invArea) per pixel in shared memory for a
+    // pixel-parallel shading pass that then needs only the 32-byte shading half of the record.  Same bits (37 GPU
+    // parity tests), fewer instructions, and slower: raster city4k 102.6 -> 108.1 us, gun1080 25.4 -> 27.0, stress8k
+    // 1111 -> 1158 (falling back to the replay above 32 / 96 / 256 spans made no difference on city4k).  Three more
+    // CTA barriers and a serial span walk on a few threads cost more than 8 warps replaying short chains in lockstep.
+    // profiles/r02zy_ab_span_resolve.txt)
     for (int p = threadIdx.x; p < kTile * kTile; p += kVisThreads) {
         const int px = p & 15, py = p >> 4;
         const int x = tx0 + px, y = ty0 + py;
@@ -283,18 +305,6 @@ __device__ __forceinline__ void vis_resolve(const unsigned long long* keys, cons
     }
 }
 
-struct VisSmem {
-    unsigned long long keys[kTile * kKeyPitch]; // rows padded: lanes walk DIFFERENT rows at the same x, and an
-                                                // unpadded 128-byte row pitch would put them all on the same two banks
-    float S[kVisFields][kVisThreads];      // raster constants of the chunk's triangles (SoA)
-    int warpRows[kVisWarps];
-    uint32_t warpMin[kVisWarps];           // hi-Z: per-warp minimum of the stored depth keys
-    int last;                              // split bins: this CTA merged last and resolves the tile
-    unsigned short items[kVisThreads * kTile];   // (triangle slot | row << 8) per work item of the chunk
-#ifdef SRB_TILE_TIMING
-    unsigned long long phase[2];           // diagnostic: time after the first chunk's load+scan, time before resolve
-#endif
-};
 
 // One 16x16 tile, whole CTA.  Ends with every thread past its last shared-memory access
 // only after the caller's __syncthreads() (heavy-list CTAs loop over several tiles).

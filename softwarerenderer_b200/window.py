@@ -234,11 +234,7 @@ class MainWindow:
                                                        C.byref(out)))
             h = out.value
             self._mesh_by_content[ckey] = h
-            while len(self._mesh_by_content) > max(1, int(self.MeshCacheCapacity)):
-                if self._draws:                                  # recorded draws may name the victim: keep it
-                    break
-                _, victim = self._mesh_by_content.popitem(last=False)
-                N.check(self._ctx, N.lib().srb_mesh_destroy(self._ctx, victim))
+            self._trim_mesh_cache()
         else:
             self._mesh_by_content.move_to_end(ckey)
         if isinstance(vertices, np.ndarray) and isinstance(indices, np.ndarray):
@@ -251,6 +247,15 @@ class MainWindow:
             except TypeError:
                 pass
         return h
+
+    def _trim_mesh_cache(self) -> None:
+        """Destroy the least recently used device meshes beyond MeshCacheCapacity.  Only between frames: recorded
+        draws may name the victim (RenderFrame calls this again once they are submitted)."""
+        if self._draws:
+            return
+        while len(self._mesh_by_content) > max(1, int(self.MeshCacheCapacity)):
+            _, victim = self._mesh_by_content.popitem(last=False)
+            N.check(self._ctx, N.lib().srb_mesh_destroy(self._ctx, victim))
 
     def CreateMesh(self, vertices, indices) -> "MeshHandle":
         """Upload once, keep the handle: RenderMesh / Physics.Raycast accept it in place of the vertex array
@@ -283,6 +288,7 @@ class MainWindow:
         N.check(self._ctx, L.srb_end_frame(self._ctx))
         self._draws = []
         self._clear_flags = 0
+        self._trim_mesh_cache()
 
     def ApplyUniforms(self, near_clip: Optional[float] = None) -> None:
         """Push the captured shader state (and the numerics_fma switch) to the device without submitting a frame:

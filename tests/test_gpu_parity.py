@@ -398,11 +398,14 @@ def test_mesh_cache_identity_content_and_invalidate(oracle):
         oc, od, _ = oracle.render_scene(sc, threads=4)
         compare(win.ColorBuffer, win.DepthBuffer, oc, od)
         assert not np.array_equal(win.ColorBuffer, c0)
-        # eviction: capacity 1 keeps rendering correctly (every draw re-uploads what was evicted)
+        # eviction: beyond the capacity the least recently used meshes are destroyed between frames, and a frame
+        # that needs them again uploads them again
+        assert len(win._mesh_by_content) == n0 + 1               # the edited mesh and its stale predecessor
         win.MeshCacheCapacity = 1
         submit_scene(win, sc)
+        assert len(win._mesh_by_content) == 1
         submit_scene(win, sc)
-        assert len(win._mesh_by_content) <= max(1, len({id(d.mesh) for d in sc.draws}))
+        assert len(win._mesh_by_content) == 1
         compare(win.ColorBuffer, win.DepthBuffer, oc, od)
     finally:
         win.Close()
