@@ -305,6 +305,16 @@ int launch_frame(SrbContext* c) {
     // every bin, where the tile kernel's hi-Z wants its occluders.
     const bool mergedFill = prevBig > 0 && prevRefs <= 16384u;
     const unsigned bigCountGrid = (unsigned)(c->smCount * (fullFrame ? c->bigCountCtas : 4));
+    // Extra CTAs at the head of the tile kernel's grid, one per part of a split bin beyond the first.  None when bins
+    // are not split (every dead CTA still costs a launch slot and two loads: 4,096 of them were 12 % of the city4k
+    // grid and half of gun1080's); otherwise what the last frame would have needed plus an eighth, in steps of 256 so
+    // that the captured chain keeps its shape.  The scan kernel sizes the parts to fit whatever it is given.
+    uint32_t extraCtas = 0u;
+    if (splitMin) {
+        // parts beyond the first of all split bins <= their entries / part size (published by the last scan kernel)
+        const uint32_t need = c->fb[sPrev].hCnt->nSplitEntries / std::max(c->splitPart, 32u);
+        extraCtas = std::min<uint32_t>(kMaxExtra, (need + need / 8u + 32u + 255u) / 256u * 256u);
+    }
     const bool direct = c->profiling || !c->useGraphs;       // launch by launch: stage events, or graphs switched off
 
     // Everything of the chain that goes onto the geometry stream, in order.  `live`: issued directly (events may be
@@ -342,10 +352,10 @@ int launch_frame(SrbContext* c) {
         if (bandTiles > 0) {
             if (splitMin)
                 scan_tiles_kernel<true><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
-                                                                   bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt, B.dTileHasBig);
+                                                                   bandTiles, B.dCnt, fp.pairCap, splitMin, c->splitPart, (uint32_t*)B.hCnt, B.dTileHasBig, extraCtas);
             else
                 scan_tiles_kernel<false><<<kScanCtas, 1024, 0, gs>>>(B.dTileCount, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, fp.bandRow0 * fp.tilesX,
-                                                                    bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt, B.dTileHasBig);
+                                                                    bandTiles, B.dCnt, fp.pairCap, 0u, c->splitPart, (uint32_t*)B.hCnt, B.dTileHasBig, 0u);
             ++n;
         } else {
             publish_counters_kernel<<<1, sizeof(Counters) / 4, 0, gs>>>(B.dCnt, (uint32_t*)B.hCnt);
@@ -376,7 +386,7 @@ int launch_frame(SrbContext* c) {
         const void* ptrs[] = {B.dDraws.p, B.dVBlocks.p, B.dTBlocks.p, B.dClip.p, B.dWn.p, B.dRecsR.p, B.dRecsS.p, B.dClipAttrs.p,
                               B.dRefs.p, B.dBigQ.p, B.dCntTiles.p, B.dTileStart.p, B.dTileCursor.p, B.dOrder.p, B.dBins.p, B.hCnt};
         const uint32_t ints[] = {gridV, gridT, (uint32_t)c->nVBlocks, (uint32_t)c->nTBlocks, (uint32_t)mergedFill, splitMin, c->splitPart,
-                                 bigCountGrid, fillGrid, wave, (uint32_t)nTiles, (uint32_t)bandTiles};
+                                 bigCountGrid, fillGrid, wave, (uint32_t)nTiles, (uint32_t)bandTiles, extraCtas};
         put(&fp, sizeof(fp)); put(&U, sizeof(U)); put(ptrs, sizeof(ptrs)); put(ints, sizeof(ints));
         bool done = false;
         if (B.graphExec && key == B.graphKey) {
@@ -418,7 +428,7 @@ int launch_frame(SrbContext* c) {
     CK(c, cudaStreamWaitEvent(c->stream, B.geomDone, 0));
     RasterArgs A;
     A.draws = B.dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
-    A.gkeys = c->dSliceKeys; A.sliceDone = c->dSliceDone; A.bandTiles = bandTiles;
+    A.gkeys = c->dSliceKeys; A.sliceDone = c->dSliceDone; A.bandTiles = bandTiles; A.extraCtas = extraCtas;
     A.clipAttrs = B.dClipAttrs.p; A.tileStart = B.dTileStart.p; A.tileEnd = B.dTileCursor.p;
     A.bins = B.dBins.p; A.color = c->color; A.depth = c->depth; A.cnt = B.dCnt;
     A.colorOut = c->colorTarget ? c->colorTarget : c->color;
@@ -432,7 +442,7 @@ int launch_frame(SrbContext* c) {
         if (c->useVis) {
             mark(6);                       // no sort stage on the visibility path
             const bool out8 = A.color8Out != nullptr;
-            const unsigned visGrid = (unsigned)bandTiles + kMaxExtra;      // the first kMaxExtra CTAs: parts of split bins
+            const unsigned visGrid = (unsigned)bandTiles + extraCtas;      // the first extraCtas CTAs: parts of split bins
             switch (c->visMode) {
                 case 0: if (out8) vis_tile_kernel<0, true><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U);
                         else vis_tile_kernel<0, false><<<visGrid, kVisThreads, 0, c->stream>>>(A, fp, U); break;

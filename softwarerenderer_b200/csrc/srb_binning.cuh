@@ -302,8 +302,9 @@ __global__ void __cluster_dims__(kScanCtas, 1, 1) __launch_bounds__(1024)
 scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__ tileStart,
                   uint32_t* __restrict__ tileCursor, uint4* __restrict__ order, int tile0, int nTiles,
                   Counters* cnt, uint32_t pairCap, const uint32_t splitMin_, const uint32_t splitPart,
-                  uint32_t* __restrict__ hostCnt, const uint32_t* __restrict__ tileHasBig) {
+                  uint32_t* __restrict__ hostCnt, const uint32_t* __restrict__ tileHasBig, const uint32_t maxExtra) {
     const uint32_t splitMin = SPLIT ? splitMin_ : 0u;
+    SRB_ASSERT(!SPLIT || (maxExtra >= 1u && maxExtra <= kMaxExtra));
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     __shared__ uint32_t wsum[4][32];
@@ -347,8 +348,9 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
         if (SPLIT) tsp += t[3];
     }
     // Entries per part: a multiple of 32, at least splitPart, and large enough that the parts beyond the first of
-    // all split bins fit kMaxExtra (sum over bins of ceil(c/ps) - 1 <= sum of c/ps).
-    const uint32_t partSize = 32u * max(max(splitPart, 32u) / 32u, (tsp + 32u * kMaxExtra - 1u) / (32u * kMaxExtra));
+    // all split bins fit maxExtra -- the extra CTAs this frame's tile kernel is launched with, sized by the host from
+    // the frames before (<= kMaxExtra) -- since sum over bins of ceil(c/ps) - 1 <= sum of c/ps.
+    const uint32_t partSize = 32u * max(max(splitPart, 32u) / 32u, (tsp + 32u * maxExtra - 1u) / (32u * maxExtra));
     cluster.sync();                                     // nobody leaves (or reuses wsum) while its totals are being read
     // phase 2: offsets and order; warp w owns kScanIters*32 consecutive tiles of each chunk
     for (int chunk = r0; chunk < r1; chunk += 1024 * kScanIters) {
@@ -424,7 +426,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
                 const uint32_t extra = (c[k] + partSize - 1u) / partSize - 1u;
                 w = (extra + 1u) | (ebase << 16) | big;    // parts (<= kMaxExtra + 1) | slice (< kMaxExtra) | large-triangle flag
                 firstEnd = excl + partSize;
-                SRB_ASSERT(ebase + extra <= kMaxExtra && extra + 1u <= 0xffffu);
+                SRB_ASSERT(ebase + extra <= maxExtra && extra + 1u <= 0xffffu);
                 for (uint32_t q = 1; q <= extra; ++q)
                     order[(uint32_t)nTiles + ebase + q - 1u] =
                         make_uint4((uint32_t)i, excl + q * partSize, min(excl + (q + 1u) * partSize, excl + c[k]), w);
@@ -441,6 +443,7 @@ scan_tiles_kernel(const uint32_t* __restrict__ tileCount, uint32_t* __restrict__
     }
     if (rank == 0 && threadIdx.x == 0) {
         cnt->nPairs = tp;
+        if (SPLIT) cnt->nSplitEntries = tsp;
         if (tp > pairCap) atomicOr(&cnt->overflow, 1u);
     }
     cluster.sync();                                     // every CTA's reservations (nExtra) are in

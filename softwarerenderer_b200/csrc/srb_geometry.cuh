@@ -37,7 +37,8 @@ struct Counters {
     uint32_t nNoCover;            // small triangles dropped because they provably cover no pixel
     uint32_t nVLive, nTLive;      // live entries of the compacted vertex / triangle block tables (frustum kernel)
     uint32_t nExtra;              // launch-order entries of split bins beyond the one-per-tile entries (scan kernel)
-    uint32_t _pad1[28];
+    uint32_t nSplitEntries;       // bin entries of the bins that were split (scan kernel): sizes the next frame's extra CTAs
+    uint32_t _pad1[27];
 };
 static_assert(sizeof(Counters) == 256, "Counters layout");
 

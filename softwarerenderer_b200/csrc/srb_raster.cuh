@@ -521,11 +521,11 @@ vis_tile_kernel(RasterArgs A, FrameParams fp, SrbUniforms U) {
     // One load gives the tile and its bin range.  (Measured and rejected: clearing the frame on a second
     // stream beside the geometry stages -- at full store bandwidth it slows them by its own duration.)
     // The extra entries of split bins (heavy work, behind the one-per-tile entries in memory) are launched first.
-    const bool extra = blockIdx.x < kMaxExtra;
+    const bool extra = blockIdx.x < A.extraCtas;
     // (Measured and rejected, round 2: the order entry carrying the tile as column | row << 16 to spare every CTA the
     // division below -- the tile kernel did not move, the scan kernel paid 2.4 us for the division.
     // profiles/r02r_ab_txy_precheck.txt)
-    const uint4 o = __ldg(A.order + (extra ? (uint32_t)A.bandTiles + blockIdx.x : blockIdx.x - kMaxExtra));
+    const uint4 o = __ldg(A.order + (extra ? (uint32_t)A.bandTiles + blockIdx.x : blockIdx.x - A.extraCtas));
     if (A.cnt->overflow) return;
     if (extra && blockIdx.x >= A.cnt->nExtra) return;       // unused slot (stale entry of an earlier frame)
     SRB_ASSERT((int)o.x >= fp.bandRow0 * fp.tilesX && (int)o.x < fp.bandRow1 * fp.tilesX && o.y <= o.z && o.z <= fp.pairCap);

@@ -12,6 +12,7 @@ struct RasterArgs {
                                   // merge into one with atomic max, the last one reads it back and zeroes it again
     uint32_t* sliceDone;          // per slice: parts that have merged so far (reset by the last one)
     int bandTiles;                // one-per-tile launch-order entries; the extra entries of split bins follow them
+    uint32_t extraCtas;           // CTAs at the head of the grid that take those extra entries (0: bins are not split)
     const float4* wn;             // world normals from vertex_kernel
     RecStore recs;
     const ClipAttr* clipAttrs;

@@ -19,7 +19,10 @@ r0, r1 = int(sys.argv[1]), int(sys.argv[2])
 wl = sys.argv[3] if len(sys.argv) > 3 else "city4k"
 scene = bench.build_scene(wl)
 L = N.lib()
-for split, depth, graphs in (((0, 0, 64), 0, 1), ((128, 128, 64), 0, 1), ((256, 256, 128), 0, 1), ((512, 512, 128), 0, 1)):
+VARIANTS = {"split": (((0, 0, 64), 0, 1), ((128, 128, 64), 0, 1), ((256, 256, 128), 0, 1), ((512, 512, 128), 0, 1)),
+            "depth": (((256, 256, 128), 0, 1), ((256, 256, 128), 2, 1), ((256, 256, 128), 3, 1), ((256, 256, 128), 4, 1)),
+            "default": (((256, 256, 128), 0, 1),)}
+for split, depth, graphs in VARIANTS[os.environ.get("PROBE", "default")]:
     win = srb.MainWindow(scene.width, scene.height)
     ctx = win._ctx
     win.SetBinSplit(*split)
