@@ -96,6 +96,10 @@ struct SrbContext {
     cudaStream_t barStream = nullptr;           // slack >= 1: the barrier kernel runs beside the raster stream
     cudaEvent_t barFrame = nullptr, barDone[2] = {};
     int barPending = -1;                        // barDone[] index of the last side-stream barrier, -1: none
+#ifdef SRB_TIMELINE
+    unsigned long long* dTimeline = nullptr;    // diagnostic builds: globaltimer at four points of every frame
+    uint32_t timelineFrame = 0;
+#endif
     unsigned long long* dSliceKeys = nullptr;   // key slices of split bins (kMaxExtra x 256), all zero between tile kernels
     uint32_t* dSliceDone = nullptr;             // per slice: parts merged so far, zero between tile kernels
     // Bins of >= splitMin entries are rasterized by several CTAs of splitPart entries each (srb_set_bin_split).
@@ -230,6 +234,20 @@ void refresh_caps(SrbContext* c) {
     c->fp.bigCap = (uint32_t)std::min<size_t>(big, 0xffffffffu);
 }
 
+#ifdef SRB_TIMELINE
+// Diagnostic builds only (tools/timeline.py): where a frame's geometry chain and tile kernel sit in time.
+constexpr uint32_t kTimelineFrames = 4096;
+__global__ void stamp_kernel(unsigned long long* out) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    *out = t;
+}
+#define SRB_STAMP(point, stream_) \
+    stamp_kernel<<<1, 1, 0, stream_>>>(c->dTimeline + 4 * (size_t)(c->timelineFrame % kTimelineFrames) + (point))
+#else
+#define SRB_STAMP(point, stream_) ((void)0)
+#endif
+
 // Launch the whole pipeline for the resident draw list.
 int launch_frame(SrbContext* c) {
     FrameParams& fp = c->fp;
@@ -284,6 +302,7 @@ int launch_frame(SrbContext* c) {
         CK(c, cudaStreamWaitEvent(gs, c->fb[sPrev].geomStarted, 0));
     c->lastGeomStream = gs;
     CK(c, cudaEventRecord(c->ev0, gs));
+    SRB_STAMP(0, gs);
     if (B.tableSerial != c->frameSerial && fp.nDraws > 0) {
         // Every set has its own device copy of the draw table, uploaded on the geometry stream the first time the
         // set renders a new frame: a new frame's geometry then does not wait for the previous frame's tile kernel.
@@ -293,6 +312,9 @@ int launch_frame(SrbContext* c) {
     }
     B.tableSerial = c->frameSerial;
     const uint32_t splitMin = c->useVis ? (fullFrame ? c->splitMinFull : c->splitMinBand) : 0u;
+    // (Measured without effect, round 2: the fill grid sized from the triangles the last frame accepted instead of
+    // the scene's total, and 1 / 2 instead of 4 CTAs per SM for a band's large-triangle count pass -- band contexts
+    // and full frames within 1 %.  profiles/r02zw_band_probe_lean_fill_grids.txt)
     const unsigned fillGrid = (unsigned)std::min<size_t>((2 * (size_t)fp.totalT + 255) / 256, (size_t)c->smCount * 8);
     const unsigned wave = (unsigned)c->smCount * c->fillCtas;
     // Fill: one launch or two.  The merged kernel saves a launch, which is what a small, launch-latency-bound frame
@@ -424,8 +446,10 @@ int launch_frame(SrbContext* c) {
         }
     }
     mark(5);
+    SRB_STAMP(1, gs);
     CK(c, cudaEventRecord(B.geomDone, gs));
     CK(c, cudaStreamWaitEvent(c->stream, B.geomDone, 0));
+    SRB_STAMP(2, c->stream);
     RasterArgs A;
     A.draws = B.dDraws.p; A.order = B.dOrder.p; A.wn = B.dWn.p; A.recs.R = B.dRecsR.p; A.recs.S = B.dRecsS.p; A.recs.fan1Base = (uint32_t)fp.totalT;
     A.gkeys = c->dSliceKeys; A.sliceDone = c->dSliceDone; A.bandTiles = bandTiles; A.extraCtas = extraCtas;
@@ -463,6 +487,10 @@ int launch_frame(SrbContext* c) {
         }
     }
     mark(7);
+    SRB_STAMP(3, c->stream);
+#ifdef SRB_TIMELINE
+    ++c->timelineFrame;
+#endif
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(B.rasterDone, c->stream));
     B.rasterRecorded = true;
@@ -576,6 +604,9 @@ int srb_create(int device, int width, int height, SrbContext** out_ctx) {
     if ((e = cudaMalloc((void**)&c->dSliceDone, (size_t)kMaxExtra * sizeof(uint32_t))) != cudaSuccess) return bail("cudaMalloc", e);
     if ((e = cudaMemsetAsync(c->dSliceKeys, 0, (size_t)kMaxExtra * kTile * kTile * sizeof(unsigned long long), c->stream)) != cudaSuccess) return bail("cudaMemset", e);
     if ((e = cudaMemsetAsync(c->dSliceDone, 0, (size_t)kMaxExtra * sizeof(uint32_t), c->stream)) != cudaSuccess) return bail("cudaMemset", e);
+#ifdef SRB_TIMELINE
+    if ((e = cudaMalloc((void**)&c->dTimeline, (size_t)kTimelineFrames * 4 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc", e);
+#endif
     int rc = alloc_framebuffer(c, width, height);
     if (rc != SRB_OK) { g_createError = c->err; delete c; return rc; }
     *out_ctx = c;
@@ -1106,6 +1137,22 @@ int srb_replay_frame(SrbContext* c) {
     }
     return launch_frame(c);
 }
+
+#ifdef SRB_TIMELINE
+// Diagnostic builds only: the last min(frames launched, max_frames) frames' stamps, 4 x uint64 ns each
+// (geometry start, geometry end, tile kernel start, tile kernel end); returns the number of frames written.
+int srb_debug_timeline(SrbContext* c, unsigned long long* out, int max_frames) {
+    if (!c || !out) return SRB_ERR_ARG;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    const uint32_t n = std::min<uint32_t>(std::min<uint32_t>(c->timelineFrame, kTimelineFrames), (uint32_t)std::max(max_frames, 0));
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t f = c->timelineFrame - n + i;
+        cudaMemcpy(out + 4 * (size_t)i, c->dTimeline + 4 * (size_t)(f % kTimelineFrames), 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    }
+    return (int)n;
+}
+#endif
 
 int srb_sync(SrbContext* c) {
     if (!c) return SRB_ERR_ARG;
