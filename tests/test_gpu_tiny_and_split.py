@@ -165,3 +165,41 @@ def test_tiny_triangles_in_bands(oracle):
             y0, y1 = r0 * 16, min(r1 * 16, sc.height)
             assert np.array_equal(bd[y0:y1], od[y0:y1])
             compare(bc[y0:y1], bd[y0:y1], oc[y0:y1], od[y0:y1])
+
+
+def test_extra_ctas_follow_the_frame(oracle):
+    """The tile kernel is launched with as many extra CTAs as the last frame's split bins wanted.  A context's first
+    split frame has 256 of them whatever it needs (the scan kernel then makes the parts larger), later frames get what
+    the one before asked for, and a frame that needs fewer again shrinks the grid: same image every time."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200.scene import submit_scene
+    rng = np.random.RandomState(11)
+    W, H = 160, 96
+
+    def crowd(n):
+        tris, cols, zs = [], [], []
+        for k in range(n):
+            c = np.array([rng.uniform(8, W - 8), rng.uniform(8, H - 8)])
+            t = c + (rng.uniform(-60, 60, (3, 2)) if k % 400 == 0 else rng.uniform(-2.2, 2.2, (3, 2)))
+            tris.append(np.round(t * 16) / 16)
+            cols.append((*rng.uniform(0.2, 1.0, 3), 1.0))
+            zs.append(float(rng.choice([0.25, 0.5, rng.uniform(0.05, 0.95)])))
+        return screen_tri_scene(W, H, tris, colors=cols, ndc_z=zs, cull=0, depth=2, blend=1)
+
+    heavy, light = crowd(20000), crowd(2400)             # ~400 / ~50 entries per tile over 60 tiles (one mesh: ushort indices)
+    oh = oracle.render_scene(heavy, threads=8)
+    ol = oracle.render_scene(light, threads=4)
+    win = srb.MainWindow(W, H)
+    try:
+        win.SetPipeline(2)
+        win.SetBinSplit(64, 64, 32)                       # heavy: ~60 x 12 parts wanted, far beyond the first 256
+        parts = []
+        for sc, (oc, od, _) in ((heavy, oh), (heavy, oh), (heavy, oh), (light, ol), (light, ol), (heavy, oh)):
+            submit_scene(win, sc)
+            compare(win.ColorBuffer, win.DepthBuffer, oc, od)
+            parts.append(win.Stats().split_parts)
+        assert parts[0] <= 256 < parts[1] == parts[2], parts
+        assert parts[4] <= parts[3] < parts[1], parts
+        assert parts[5] <= 256, parts
+    finally:
+        win.Close()
