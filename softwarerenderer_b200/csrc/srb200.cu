@@ -22,7 +22,7 @@ namespace {
 
 thread_local std::string g_createError;
 
-struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; float4* blockSpheres = nullptr; int2* blockVRange = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
+struct MeshRes { float4* vtx = nullptr; uint16_t* idx = nullptr; float4* blockBoxes = nullptr; int2* blockVRange = nullptr; int nV = 0, nI = 0; bool opaque = true, alive = false; };
 struct TexRes { uchar4* px = nullptr; int w = 0, h = 0; bool opaque = true, alive = false; };
 
 template <typename T>
@@ -626,7 +626,7 @@ int srb_destroy(SrbContext* c) {
     if (c->barRow) cudaFree(c->barRow);
     if (c->barTimedOut) cudaFreeHost(c->barTimedOut);
     if (c->color8) cudaFree(c->color8);
-    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockSpheres); cudaFree(m.blockVRange); }
+    for (auto& m : c->meshes) if (m.alive) { cudaFree(m.vtx); cudaFree(m.idx); cudaFree(m.blockBoxes); cudaFree(m.blockVRange); }
     for (auto& t : c->textures) if (t.alive) cudaFree(t.px);
 
     if (c->dSliceKeys) cudaFree(c->dSliceKeys);
@@ -881,9 +881,11 @@ int srb_mesh_create(SrbContext* c, const float* vertices, int nV, const uint16_t
     CK(c, cudaMalloc((void**)&m.idx, std::max<size_t>((size_t)nI * 2, 16)));
     CK(c, cudaMemcpy(m.vtx, vertices, (size_t)nV * 48, cudaMemcpyHostToDevice));
     if (nI > 0) CK(c, cudaMemcpy(m.idx, indices, (size_t)nI * 2, cudaMemcpyHostToDevice));
-    {   // object-space bounding sphere of every run of kGeomBlock triangles (block culling in the setup kernel)
+    {   // object-space bounding box (centre, half extents) of every run of kGeomBlock triangles: block culling of band
+        // contexts.  (A bounding sphere kept 82 % of city4k's blocks on the band that owns the upper half of the
+        // screen, the box keeps 39 %, within a point of the blocks' true screen extent: walls and floors are flat.)
         const int nT = nI / 3, nB = (nT + kGeomBlock - 1) / kGeomBlock;
-        std::vector<float4> sph((size_t)std::max(nB, 1), make_float4(0.0f, 0.0f, 0.0f, 3.0e38f));
+        std::vector<float4> box(2 * (size_t)std::max(nB, 1), make_float4(0.0f, 0.0f, 0.0f, 0.0f));
         for (int b = 0; b < nB; ++b) {
             const int t0 = b * kGeomBlock, t1 = std::min(nT, t0 + kGeomBlock);
             float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
@@ -894,18 +896,19 @@ int srb_mesh_create(SrbContext* c, const float* vertices, int nV, const uint16_t
                     finite = finite && std::isfinite(v);
                     lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v);
                 }
-            if (!finite) continue;                                        // radius stays huge: never culled
-            const double cx = 0.5 * ((double)lo[0] + hi[0]), cy = 0.5 * ((double)lo[1] + hi[1]), cz = 0.5 * ((double)lo[2] + hi[2]);
-            double r2 = 0.0;
-            for (int i = 3 * t0; i < 3 * t1; ++i) {
-                const float* v = vertices + 12 * (size_t)indices[i];
-                const double dx = v[0] - cx, dy = v[1] - cy, dz = v[2] - cz;
-                r2 = std::max(r2, dx * dx + dy * dy + dz * dz);
+            if (!finite) { box[2 * b + 1] = make_float4(3.0e38f, 3.0e38f, 3.0e38f, 0.0f); continue; }   // never culled
+            float ctr[3], half[3];
+            for (int k = 0; k < 3; ++k) {
+                const double cd = 0.5 * ((double)lo[k] + hi[k]);
+                ctr[k] = (float)cd;
+                // half extent about the ROUNDED centre, rounded up: the box contains every vertex
+                half[k] = (float)((std::max((double)hi[k] - ctr[k], (double)ctr[k] - lo[k])) * 1.0001 + 1e-6);
             }
-            sph[b] = make_float4((float)cx, (float)cy, (float)cz, (float)(std::sqrt(r2) * 1.0001 + 1e-6));
+            box[2 * b] = make_float4(ctr[0], ctr[1], ctr[2], 0.0f);
+            box[2 * b + 1] = make_float4(half[0], half[1], half[2], 0.0f);
         }
-        CK(c, cudaMalloc((void**)&m.blockSpheres, sph.size() * sizeof(float4)));
-        CK(c, cudaMemcpy(m.blockSpheres, sph.data(), sph.size() * sizeof(float4), cudaMemcpyHostToDevice));
+        CK(c, cudaMalloc((void**)&m.blockBoxes, box.size() * sizeof(float4)));
+        CK(c, cudaMemcpy(m.blockBoxes, box.data(), box.size() * sizeof(float4), cudaMemcpyHostToDevice));
         // lowest / highest vertex index of every run (band contexts transform only the vertex runs a kept block uses)
         std::vector<int2> vr((size_t)std::max(nB, 1), make_int2(0, 0));
         for (int b = 0; b < nB; ++b) {
@@ -933,7 +936,7 @@ int srb_mesh_destroy(SrbContext* c, SrbMesh mesh) {
     cudaStreamSynchronize(c->stream);
     cudaFree(c->meshes[mesh - 1].vtx);
     cudaFree(c->meshes[mesh - 1].idx);
-    cudaFree(c->meshes[mesh - 1].blockSpheres);
+    cudaFree(c->meshes[mesh - 1].blockBoxes);
     cudaFree(c->meshes[mesh - 1].blockVRange);
     c->meshes[mesh - 1] = MeshRes();
     c->haveFrame = false;
@@ -1058,7 +1061,7 @@ int srb_end_frame(SrbContext* c) {
         d.vbase = (int32_t)totalV; d.tbase = (int32_t)totalT;
         d.cull = q.cull; d.depth_test = q.depth_test; d.blend = q.blend;
         d.flags = q.flags; d.visible = 1; d._pad = 0;
-        d.tblockSpheres = m.blockSpheres;
+        d.tblockBoxes = m.blockBoxes;
         d.tblockVRange = m.blockVRange;
         for (int k = 0; k < 4; ++k) d.planes[k] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
         totalV += m.nV; totalT += m.nI / 3;

@@ -46,13 +46,13 @@ struct DrawRec {
     uint32_t flags;
     int32_t visible;          // written by the frustum kernel
     int32_t _pad;
-    const float4* tblockSpheres;  // object-space bounding sphere of every run of kGeomBlock triangles (mesh upload)
+    const float4* tblockBoxes;    // object-space bounding box (centre, half extents: 2 float4) of every run of kGeomBlock triangles (mesh upload)
     const int2* tblockVRange;     // lowest / highest vertex index used by every run of kGeomBlock triangles (mesh upload)
     float4 planes[5];         // written by the frustum kernel: object-space half-spaces left/right/top/bottom of the
                               // screen (top/bottom: of this context's band), nx,ny,nz,d normalised; inside: n.p + d >= 0.
                               // planes[4] is the half-space clip w > 0: the four screen planes describe where a vertex
                               // lands on screen only for w > 0 (for w < 0 the NDC position flips sides), so a block is
-                              // culled only when its sphere also lies entirely inside this one.
+                              // culled only when its box also lies entirely inside this one.
 };
 static_assert(sizeof(DrawRec) == 384, "DrawRec layout");
 

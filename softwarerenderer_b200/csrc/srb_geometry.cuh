@@ -129,10 +129,10 @@ __device__ bool sphere_misses_band(const float* sphere, const float* M, const fl
 }
 
 // Block culling.  The frustum kernel leaves four object-space half-spaces per draw (screen left / right, band top
-// / bottom, each pushed out by one pixel); the setup kernel drops a 128-triangle block whose object-space bounding
-// sphere (computed at mesh upload) lies entirely outside one of them.  Every triangle of such a block has an empty
+// / bottom, each pushed out by one pixel); a 128-triangle block whose object-space bounding
+// box (computed at mesh upload) lies entirely outside one of them is dropped from a band context's block table.  Every triangle of such a block has an empty
 // clamped pixel bbox (Rasterizer.cs:432-442) or misses the band, i.e. the reference walks no pixel of it, so the
-// image is unchanged.  The comparison is deliberately loose (1 % of the radius plus a relative epsilon): rounding
+// image is unchanged.  The comparison is deliberately loose (1 % of the box's extent along the plane normal plus a relative epsilon): rounding
 // in the vertex transform is five orders of magnitude below that.
 __device__ void draw_planes(DrawRec& d, int W, int H, int bandRow0, int bandRow1, int tilesY) {
     float MVP[16], VP[16];
@@ -169,20 +169,26 @@ __device__ void draw_planes(DrawRec& d, int W, int H, int bandRow0, int bandRow1
     }
 }
 __device__ __forceinline__ bool block_outside(const DrawRec& d, int block) {
-    const float4 s = __ldg(d.tblockSpheres + block);
+    const float4 c = __ldg(d.tblockBoxes + 2 * block), h = __ldg(d.tblockBoxes + 2 * block + 1);
+    // signed distance of the box's centre to a (normalised) plane and the box's extent along the plane's normal
+    auto dist = [&](const float4 p, float& ext) {
+        ext = fabsf(p.x) * h.x + fabsf(p.y) * h.y + fabsf(p.z) * h.z;
+        return p.x * c.x + p.y * c.y + p.z * c.z + p.w;
+    };
+    auto slack = [&](const float4 p, float ext) {
+        return 0.01f * ext + 1e-3f * (fabsf(p.w) + fabsf(c.x) + fabsf(c.y) + fabsf(c.z)) + 1e-4f;
+    };
     {   // every vertex of the block must have clip w > 0 for the screen planes to mean anything (see DrawRec::planes)
-        const float4 p = d.planes[4];
-        const float sd = p.x * s.x + p.y * s.y + p.z * s.z + p.w;
-        const float slack = 1.01f * s.w + 1e-3f * (fabsf(p.w) + fabsf(s.x) + fabsf(s.y) + fabsf(s.z)) + 1e-4f;
-        if (!(sd > slack)) return false;                // also for NaN
+        float ext;
+        const float sd = dist(d.planes[4], ext);
+        if (!(sd - ext > slack(d.planes[4], ext))) return false;        // also for NaN / the never-culled box
     }
     bool out = false;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const float4 p = d.planes[k];
-        const float sd = p.x * s.x + p.y * s.y + p.z * s.z + p.w;
-        const float slack = 1.01f * s.w + 1e-3f * (fabsf(p.w) + fabsf(s.x) + fabsf(s.y) + fabsf(s.z)) + 1e-4f;
-        out = out || (sd < -slack);                     // false for NaN
+        float ext;
+        const float sd = dist(d.planes[k], ext);
+        out = out || (sd + ext < -slack(d.planes[k], ext));             // false for NaN
     }
     return out;
 }
