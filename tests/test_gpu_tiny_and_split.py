@@ -203,3 +203,42 @@ def test_extra_ctas_follow_the_frame(oracle):
         assert parts[5] <= 256, parts
     finally:
         win.Close()
+
+
+def test_band_context_follows_sparse_and_dense_frames(oracle):
+    """One band context (with the RGBA8 gather frame, i.e. the tile kernel's OUT8 instance) through frames that leave
+    most of its tiles empty and frames that fill all of them, back and forth: the grids sized from the frame before
+    never change the image -- float colour and the 8-bit gather frame against the oracle's band every time."""
+    import softwarerenderer_b200 as srb
+    from softwarerenderer_b200.scene import submit_scene
+    rng = np.random.RandomState(5)
+    W, H = 512, 256                                       # 32 x 16 tiles (power-of-two target: exact screen coordinates)
+    band = (2, 14)
+
+    def crowd(n, x1, y1):
+        tris, cols, zs = [], [], []
+        for k in range(n):
+            c = np.array([rng.uniform(4, x1), rng.uniform(4, y1)])
+            t = c + (rng.uniform(-40, 40, (3, 2)) if k % 100 == 0 else rng.uniform(-3.0, 3.0, (3, 2)))
+            tris.append(np.round(t * 16) / 16)
+            cols.append((*rng.uniform(0.2, 1.0, 3), 1.0))
+            zs.append(float(rng.uniform(0.05, 0.95)))
+        return screen_tri_scene(W, H, tris, colors=cols, ndc_z=zs, cull=0, depth=2, blend=1)
+
+    sparse, dense = crowd(600, 120, 110), crowd(6000, W - 4, H - 4)
+    refs = {id(sparse): oracle.render_scene(sparse, threads=4), id(dense): oracle.render_scene(dense, threads=4)}
+    rows = slice(band[0] * 16, band[1] * 16)
+    win = srb.MainWindow(W, H)
+    try:
+        win.SetPipeline(2)
+        win.SetBand(*band)
+        win.ExportGatherRgba8()                            # the tile kernel's OUT8 instance, as on a band rank
+        for sc in (sparse, sparse, sparse, dense, dense, sparse, sparse):
+            submit_scene(win, sc)
+            oc, od, _ = refs[id(sc)]
+            gc, gd = win.ColorBuffer, win.DepthBuffer
+            compare(gc[rows], gd[rows], oc[rows], od[rows])
+            want8 = np.rint(np.clip(gc[rows], 0.0, 1.0) * np.float32(255.0)).astype(np.uint8)
+            assert np.array_equal(win.GatheredRgba8()[rows], want8)
+    finally:
+        win.Close()
