@@ -240,6 +240,7 @@ def run_gpu(args):
     fused = world > 1 and args.gather == "fused"
     rgba8_gather = fused and args.gather_format == "rgba8"
     box = box8 = [None]
+    refine_log = None
 
     def use_gather(fmt):
         """Band ranks: where the tile kernel stores final colour.  'rgba8': 4-byte peer stores into rank 0's RGBA8
@@ -264,6 +265,47 @@ def run_gpu(args):
             dist.broadcast_object_list(box8, src=0)
             use_gather(args.gather_format)
         S.submit_scene(win, scene)              # settle band-sized capacities
+        if args.bands == "balanced" and args.refine_cuts > 0:
+            # The model behind the first cuts (bin pairs + a constant per tile) knows nothing of a band's geometry
+            # work or of what its stores cost over NVLink.  Measure instead: every rank times its own band, uncoupled
+            # (no barrier), the periods are exchanged, each band's period is spread over its rows like the model's
+            # weights, and the cuts are balanced again on that; the best cuts seen (smallest worst period) are kept.
+            # Every rank computes the same cuts from the same gathered numbers.
+            def band_period(k=48):
+                for _ in range(16):
+                    N.check(ctx, L.srb_replay_frame(ctx))
+                win.Sync()
+                t0 = time.perf_counter()
+                for _ in range(k):
+                    N.check(ctx, L.srb_replay_frame(ctx))
+                win.Sync()
+                return (time.perf_counter() - t0) / k * 1e3
+
+            best_worst, best_cuts, tried = None, list(cuts), []
+            for it in range(args.refine_cuts + 1):
+                ts = [None] * world
+                dist.all_gather_object(ts, float(band_period()))
+                tried.append({"cuts": [int(x) for x in cuts], "period_ms": [round(float(x), 4) for x in ts]})
+                if best_worst is None or max(ts) < best_worst:
+                    best_worst, best_cuts = max(ts), list(cuts)
+                if it == args.refine_cuts:
+                    break
+                cost = np.zeros(tiles_y)
+                for r in range(world):
+                    a, b = cuts[r], cuts[r + 1]
+                    cost[a:b] = ts[r] * w_rows[a:b] / max(float(w_rows[a:b].sum()), 1e-9)
+                new = balanced_cuts(cost, world)
+                if list(new) == list(cuts):
+                    break
+                cuts = list(new)
+                win.SetBand(cuts[rank], cuts[rank + 1])
+                S.submit_scene(win, scene)
+            if list(cuts) != best_cuts:
+                cuts = best_cuts
+                win.SetBand(cuts[rank], cuts[rank + 1])
+                S.submit_scene(win, scene)
+            r0, r1 = cuts[rank], cuts[rank + 1]
+            refine_log = tried
         st = win.Stats()
     y0, y1 = r0 * 16, min(r1 * 16, H)
     # host-side command array for the e2e loop (what the C# shim would pin and pass)
@@ -675,9 +717,10 @@ def run_gpu(args):
                               "parallelism": f"bands{world}" if world > 1 else "single",
                               "bands": {"cuts_tile_rows": [int(x) for x in cuts], "policy": args.bands,
                                         "gather": (("RGBA8 (4 B/pixel) " if rgba8_gather else "float4 (16 B/pixel) ") +
-                                                   "peer stores from the tile kernel into rank 0's frame over NVLink + 4-byte "
-                                                   "NCCL all-reduce as frame barrier") if fused else "NCCL grouped send/recv of float4 bands",
-                                        "gather_format": args.gather_format if fused else "float4", "gather_verified": gather_verified}
+                                                   "peer stores from the tile kernel into rank 0's frame over NVLink; frame barrier: "
+                                                   + args.frame_barrier) if fused else "NCCL grouped send/recv of float4 bands",
+                                        "gather_format": args.gather_format if fused else "float4", "gather_verified": gather_verified,
+                                        "cuts_refinement": refine_log}
                               if world > 1 else None},
             "e2e": {"value": fps_e, "unit": "frames/s", "h2d_bytes_per_step": int(cmds.shape[0] * DRAW_REC_BYTES),
                     "d2h_bytes_per_step": int(W * H * 12), "steps": Ke,
@@ -796,6 +839,8 @@ def main():
                     help="N>1, fused gather: where the per-frame 4-byte all-reduce runs (see frame_barrier)")
     ap.add_argument("--no-numa-bind", action="store_true", help="N>1 e2e: do not pin the rank to the CPUs next to its GPU")
     ap.add_argument("--pcie-gbs", type=float, default=50.0, help="N>1 e2e: host link rate assumed by the band cuts of the e2e loop")
+    ap.add_argument("--refine-cuts", type=int, default=4,
+                    help="N>1, balanced bands: rounds of re-balancing the cuts on the ranks' measured band periods (0: model only)")
     ap.add_argument("--remote-cost", type=float, default=12.0,
                     help="N>1, fused gather: extra cost of a tile whose pixels are stored to rank 0 over NVLink, in bin pairs")
     ap.add_argument("--bands", default="balanced", choices=["balanced", "equal"], help="N>1: band cut policy")
