@@ -55,7 +55,7 @@ def build_scene(name):
     return S.scene_stress(w["width"], w["height"], extensions=w["kind"] == "stress_ext")
 
 
-from softwarerenderer_b200.bands import balanced_cuts, band_rows, gather_bands  # noqa: E402
+from softwarerenderer_b200.bands import balanced_cuts, band_rows, gather_bands, rebalance_from_periods  # noqa: E402
 
 
 class ClockSampler:
@@ -290,11 +290,7 @@ def run_gpu(args):
                     best_worst, best_cuts = max(ts), list(cuts)
                 if it == args.refine_cuts:
                     break
-                cost = np.zeros(tiles_y)
-                for r in range(world):
-                    a, b = cuts[r], cuts[r + 1]
-                    cost[a:b] = ts[r] * w_rows[a:b] / max(float(w_rows[a:b].sum()), 1e-9)
-                new = balanced_cuts(cost, world)
+                new = rebalance_from_periods(cuts, ts, w_rows)
                 if list(new) == list(cuts):
                     break
                 cuts = list(new)

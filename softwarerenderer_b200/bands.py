@@ -72,6 +72,26 @@ def balanced_cuts(row_weights, n: int, remote_extra: float = 0.0):
     return cuts
 
 
+def rebalance_from_periods(cuts, periods, row_weights):
+    """One round of measured re-balancing.  `periods[r]` is the time rank r needed for its band `cuts[r]..cuts[r+1]`
+    (any unit); it is spread over the band's rows in proportion to the model's `row_weights`, and the cuts are balanced
+    again on those measured row costs.  Deterministic: every rank computes the same cuts from the same gathered
+    periods.  Returns the new cuts (possibly the old ones: a fixed point)."""
+    n = len(periods)
+    if len(cuts) != n + 1:
+        raise ValueError("rebalance_from_periods: need one period per band")
+    w = [float(x) for x in row_weights]
+    if cuts[0] != 0 or cuts[-1] != len(w) or any(cuts[k + 1] <= cuts[k] for k in range(n)):
+        raise ValueError("rebalance_from_periods: cuts must be increasing from 0 to the number of rows")
+    cost = [0.0] * len(w)
+    for r in range(n):
+        a, b = cuts[r], cuts[r + 1]
+        tot = sum(w[a:b])
+        for i in range(a, b):
+            cost[i] = float(periods[r]) * (w[i] / tot if tot > 0.0 else 1.0 / (b - a))
+    return balanced_cuts(cost, n)
+
+
 def band_pixels(height: int, n: int, r: int):
     """Pixel-row range [y0, y1) of rank r of n for a target `height` rows tall."""
     tiles_y = (height + TILE - 1) // TILE

@@ -111,3 +111,41 @@ def test_balanced_cuts():
     assert balanced_cuts([0, 0, 0], 2) == [0, 2, 3]       # no information -> plain row split
     assert balanced_cuts([5.0, 1.0], 2) == [0, 1, 2]
     assert len(balanced_cuts([1.0] * 135, 8)) == 9
+
+
+def test_rebalance_from_periods_converges_on_a_hidden_cost():
+    """bench.py --refine-cuts: the model's row weights miss part of the true cost (here: a constant per row nine times
+    the model's, and a fixed cost per band); re-balancing on the bands' measured periods must bring the worst band
+    down, keep the cuts valid, be a pure function of its inputs (every rank computes the same cuts) and reach a fixed
+    point."""
+    import numpy as np
+    import pytest
+    from softwarerenderer_b200.bands import balanced_cuts, rebalance_from_periods
+    rng = np.random.RandomState(3)
+    rows = 135
+    pairs = np.r_[rng.uniform(0, 40, 66), [4000, 9000, 8000, 5000], rng.uniform(200, 900, 20), rng.uniform(0, 30, 45)]
+    model = pairs + 0.85 * 240                        # what bench.py starts from
+    true_row = 0.34e-3 * pairs + 2.5e-3 * 240         # the tile kernel's real cost per row (us), see DESIGN.md 6
+
+    def periods(c):
+        return [20.0 + float(true_row[a:b].sum()) for a, b in zip(c, c[1:])]
+
+    for n in (2, 4, 8):
+        cuts = balanced_cuts(model, n)
+        first = max(periods(cuts))
+        best = first
+        for _ in range(6):
+            new = rebalance_from_periods(cuts, periods(cuts), model)
+            assert new == rebalance_from_periods(list(cuts), list(periods(cuts)), model.copy())
+            assert new[0] == 0 and new[-1] == rows and all(b > a for a, b in zip(new, new[1:]))
+            if new == cuts:
+                break
+            cuts = new
+            best = min(best, max(periods(cuts)))
+        assert best <= first + 1e-9
+        if n == 8:
+            assert best < 0.9 * first, (first, best)   # the sky band sheds rows: the hidden per-tile cost is found
+    with pytest.raises(ValueError):
+        rebalance_from_periods([0, 3, 3, 5], [1.0, 1.0, 1.0], [1.0] * 5)
+    with pytest.raises(ValueError):
+        rebalance_from_periods([0, 5], [1.0, 2.0], [1.0] * 5)
