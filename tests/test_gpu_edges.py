@@ -235,3 +235,44 @@ def test_bands_with_a_projection_that_keeps_negative_w(oracle):
         bc, bd, _ = _render_gpu(sc, 0, band=(r0, r1))
         y0, y1 = r0 * 16, min(r1 * 16, H)
         assert np.array_equal(bd[y0:y1], fd[y0:y1]) and np.array_equal(bc[y0:y1], fc[y0:y1])
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_band_block_culling_by_boxes_on_random_slabs(oracle, seed):
+    """Band contexts drop 128-triangle blocks whose object-space bounding box lies outside the band (block_outside).
+    Flat, long and rotated blocks -- the shapes a box bounds tightly and a sphere does not -- under rotated, scaled
+    and translated model matrices, some of them through the near plane and behind the eye: every band must reproduce
+    its rows of the full frame bit for bit, and the full frame the oracle."""
+    from softwarerenderer_b200 import numerics as nm
+    from softwarerenderer_b200.scene import DrawItem, Mesh, Scene, default_projection
+    from softwarerenderer_b200.shaders import Material, Shaders
+    W, H = 480, 272
+    rng = np.random.RandomState(100 + seed)
+    proj = default_projection(W, H)
+    view = nm.create_look_at((0.0, 1.5, 6.0), (0.0, 0.5, 0.0), (0.0, 1.0, 0.0))
+    draws = []
+    for _ in range(7):
+        pos, col = [], []
+        for _blk in range(rng.randint(2, 5)):             # every run of 128 triangles is a slab of its own
+            ext = np.array([rng.uniform(0.5, 6.0), rng.uniform(0.02, 0.4), rng.uniform(0.3, 4.0)])[rng.permutation(3)]
+            c0 = rng.uniform(-5, 5, 3) * (1.0, 0.5, 1.0)
+            for _t in range(128):
+                a = c0 + rng.uniform(-0.5, 0.5, 3) * ext
+                pos += [a, a + rng.uniform(-0.25, 0.25, 3) * ext, a + rng.uniform(-0.25, 0.25, 3) * ext]
+                col += [(*rng.uniform(0.2, 1.0, 3), 1.0)] * 3
+        v = Shaders.make_vertices(pos, color=col)
+        model = nm.matmul(nm.create_scale(rng.uniform(0.4, 1.6)),
+                          nm.create_from_yaw_pitch_roll(*rng.uniform(-3.1, 3.1, 3)),
+                          nm.create_translation(rng.uniform(-3, 3), rng.uniform(-1, 2), rng.uniform(-8, 7)))
+        draws.append(DrawItem(Mesh(v, np.arange(len(pos), dtype=np.uint16), Material()), model, view, proj, cull=0))
+    sc = Scene(W, H, draws)
+    oc, od, _ = oracle.render_scene(sc, threads=8)
+    fc, fd, _ = _render_gpu(sc, 0)
+    compare(fc, fd, oc, od)
+    assert (fd != fd.min()).mean() > 0.05                  # something is on screen
+    tiles_y = (H + 15) // 16
+    cuts = [0] + sorted(rng.choice(np.arange(1, tiles_y), 4, replace=False).tolist()) + [tiles_y]
+    for r0, r1 in zip(cuts[:-1], cuts[1:]):
+        bc, bd, _ = _render_gpu(sc, 0, band=(r0, r1))
+        y0, y1 = r0 * 16, min(r1 * 16, H)
+        assert np.array_equal(bd[y0:y1], fd[y0:y1]) and np.array_equal(bc[y0:y1], fc[y0:y1])
