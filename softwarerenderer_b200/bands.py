@@ -92,6 +92,27 @@ def rebalance_from_periods(cuts, periods, row_weights):
     return balanced_cuts(cost, n)
 
 
+def relieve_worst_band(cuts, periods):
+    """Local search step after the model-based rounds: candidate cuts that take ONE tile row off the band with the
+    longest measured period, handing it to a neighbour -- the faster neighbour first.  Returns a list of 0..2 candidate
+    cut lists (empty when the worst band is a single row: a tile row cannot be divided).  Deterministic."""
+    n = len(periods)
+    if len(cuts) != n + 1:
+        raise ValueError("relieve_worst_band: need one period per band")
+    r = max(range(n), key=lambda k: (periods[k], -k))
+    if cuts[r + 1] - cuts[r] <= 1:
+        return []
+    cands = []
+    if r > 0:
+        c = list(cuts); c[r] += 1                      # first row to the band above
+        cands.append((periods[r - 1], c))
+    if r < n - 1:
+        c = list(cuts); c[r + 1] -= 1                  # last row to the band below
+        cands.append((periods[r + 1], c))
+    cands.sort(key=lambda t: t[0])
+    return [c for _, c in cands]
+
+
 def band_pixels(height: int, n: int, r: int):
     """Pixel-row range [y0, y1) of rank r of n for a target `height` rows tall."""
     tiles_y = (height + TILE - 1) // TILE

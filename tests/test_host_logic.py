@@ -149,3 +149,32 @@ def test_rebalance_from_periods_converges_on_a_hidden_cost():
         rebalance_from_periods([0, 3, 3, 5], [1.0, 1.0, 1.0], [1.0] * 5)
     with pytest.raises(ValueError):
         rebalance_from_periods([0, 5], [1.0, 2.0], [1.0] * 5)
+
+
+def test_relieve_worst_band_local_search():
+    """The local search that follows the model-based rounds in bench.py: one tile row at a time off the slowest band,
+    faster neighbour first, never from a single-row band; with a cost the proportional model cannot see (a fixed part
+    per band) it still walks to cuts no single move improves."""
+    import numpy as np
+    from softwarerenderer_b200.bands import relieve_worst_band
+    assert relieve_worst_band([0, 70, 135], [116.0, 93.0]) == [[0, 69, 135]]
+    assert relieve_worst_band([0, 10, 20, 30], [1.0, 3.0, 2.0]) == [[0, 11, 20, 30], [0, 10, 19, 30]]
+    assert relieve_worst_band([0, 10, 20, 30], [2.0, 3.0, 1.0]) == [[0, 10, 19, 30], [0, 11, 20, 30]]
+    assert relieve_worst_band([0, 10, 11, 30], [1.0, 3.0, 2.0]) == []          # a tile row cannot be divided
+    row = np.r_[np.full(60, 0.6), [30.0, 36.0, 32.0, 20.0], np.full(20, 2.0), np.full(51, 0.5)]
+
+    def periods(c):
+        return [45.0 + float(row[a:b].sum()) for a, b in zip(c, c[1:])]
+
+    cuts = [0, 70, 135]
+    worst = max(periods(cuts))
+    for _ in range(20):
+        moved = False
+        for cand in relieve_worst_band(cuts, periods(cuts)):
+            if max(periods(cand)) < worst:
+                cuts, worst, moved = cand, max(periods(cand)), True
+                break
+        if not moved:
+            break
+    assert all(max(periods(c)) >= worst for c in ([0, cuts[1] - 1, 135], [0, cuts[1] + 1, 135]))
+    assert cuts[0] == 0 and cuts[-1] == 135 and 0 < cuts[1] < 135
